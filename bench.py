@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""Benchmark of the correlation hot path: frame-pairs/sec for corr build + K lookups.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [--steps K] [--warmup W]      # the reference's CPU path
+
+Workload (BASELINE.json metric, config[1] geometry): Sintel 436x1024 padded to 440x1024
+(feature grid 55x128, D=256), batch 8 frame pairs per GPU, CorrBlock with 4 levels and r=4,
+one build + 12 lookups per step.  Synthetic data (seeded randn feature maps; lookup
+coordinates = pixel grid + a random-walk flow field), since datasets/checkpoints are offline.
+
+One JSON line on stdout (rank 0); everything else goes to stderr.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frame-pairs/sec, corr build+12 lookups @440x1024"
+UNIT = "frame-pairs/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="frame pairs per GPU per step")
+    ap.add_argument("--height", type=int, default=440)
+    ap.add_argument("--width", type=int, default=1024)
+    ap.add_argument("--dim", type=int, default=256)
+    ap.add_argument("--iters", type=int, default=12, help="lookups per build")
+    ap.add_argument("--levels", type=int, default=4)
+    ap.add_argument("--radius", type=int, default=4)
+    ap.add_argument("--precision", default=os.environ.get("RAFT_CORR_PRECISION", "bf16x3"),
+                    choices=["fp32", "bf16x3", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0)
+    return ap.parse_args()
+
+
+def algorithmic_bytes(B, N, D, h, w, L, r, K):
+    """read both fmaps once, write every pyramid element once, and per
+    lookup read the (2r+2)^2 integer patch per level, write L*(2r+1)^2 fp32, read 2 coords."""
+    pyr = sum(N * (h >> l) * (w >> l) for l in range(L)) * 4
+    build = B * (2 * N * D * 4 + pyr)
+    lookup = B * N * (L * (2 * r + 2) ** 2 * 4 + L * (2 * r + 1) ** 2 * 4 + 8)
+    return build, lookup, build + K * lookup
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    """Samples SM clock + throttle reasons DURING the timed region (NVML, 50 ms period)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # pragma: no cover
+            log(f"[bench] NVML unavailable: {e}")
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+            "hw_power_brake": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join(timeout=2)
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ----------------------------------------------------------------------------- CPU (reference) arm
+def cpu_reference_run(args, steps, warmup, budget_s):
+    """The reference's CPU CorrBlock path (torch CPU kernels: MKL sgemm, avg_pool2d,
+    grid_sample), via oracle/torch_port.py (op-for-op port; the reference checkout itself is not
+    on the GPU box).  One step = ONE frame pair of the workload: build + K lookups."""
+    import torch
+    from oracle import torch_port as TP
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    h, w = args.height // 8, args.width // 8
+    g = torch.Generator().manual_seed(1234)
+    f1 = torch.randn(1, args.dim, h, w, generator=g)
+    f2 = torch.randn(1, args.dim, h, w, generator=g)
+    ys, xs = torch.meshgrid(torch.arange(h).float(), torch.arange(w).float(), indexing="ij")
+    base = torch.stack([xs, ys], 0)[None]
+    flows = torch.cumsum(0.5 * torch.randn(args.iters, 1, 2, h, w, generator=g), 0)
+
+    def step():
+        pyr = TP.build_pyramid(f1, f2, args.levels)
+        s = 0.0
+        for k in range(args.iters):
+            s += float(TP.lookup(pyr, base + flows[k], args.radius)[0, 0, 0, 0])
+        return s
+
+    t_start = time.perf_counter()
+    with torch.no_grad():
+        for _ in range(max(1, warmup)):
+            step()
+            if time.perf_counter() - t_start > budget_s * 0.4:
+                break
+        times = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            step()
+            times.append(time.perf_counter() - t0)
+            if time.perf_counter() - t_start > budget_s:
+                break
+    mean = sum(times) / len(times)
+    return {"pairs_per_s": 1.0 / mean, "ms_per_step": mean * 1e3, "steps_timed": len(times), "cores": cores,
+            "threads": torch.get_num_threads(),
+            "sample": f"1 frame pair per step (of the {args.batch}-pair batch): build + {args.iters} lookups, fp32, "
+                      f"{len(times)} timed steps, mean"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # the CPU arm runs once, on rank 0
+    r = cpu_reference_run(args, args.steps, min(args.warmup, 2), args.cpu_budget_s)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["pairs_per_s"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "steps_timed": r["steps_timed"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, "cpu"),
+        "cpu_baseline": {"value": r["pairs_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["pairs_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, where):
+    h, w = args.height // 8, args.width // 8
+    return {
+        "workload": f"sintel 436x1024 padded to {args.height}x{args.width}: feature grid {h}x{w}, D={args.dim}, "
+                    f"batch {args.batch} frame pairs per GPU, CorrBlock {args.levels} levels r={args.radius}, "
+                    f"1 build + {args.iters} lookups per step",
+        "batch_per_gpu": args.batch, "iters": args.iters, "levels": args.levels, "radius": args.radius,
+        "feature_grid": [h, w], "dim": args.dim,
+        "l2": "pyramid per step (2.09 GB fp32 at batch 8) far exceeds the 126 MB L2; no explicit flush",
+        "where": where,
+    }
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import raft_ros_b200 as rr
+    from raft_ros_b200 import _lib
+    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw
+
+    _lib.build()
+    _lib.lib()  # fail loudly if the CUDA library is missing
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+
+    B, D, L, r, K = args.batch, args.dim, args.levels, args.radius, args.iters
+    h, w = args.height // 8, args.width // 8
+    N = h * w
+    # every rank owns its own shard of frame pairs: no data-path collective
+    g = torch.Generator().manual_seed(1234 + rank)
+    f1_host = torch.randn(B, D, h, w, generator=g).pin_memory()
+    f2_host = torch.randn(B, D, h, w, generator=g).pin_memory()
+    base = rr.coords_grid(B, h, w, "cpu")
+    flows = torch.cumsum(0.5 * torch.randn(K, B, 2, h, w, generator=g), 0)
+    coords_host = (base[None] + flows).contiguous().pin_memory()  # (K,B,2,h,w)
+    f1, f2 = f1_host.to(dev), f2_host.to(dev)
+    coords = coords_host.to(dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    build_ev, look_ev = [], []
+
+    def step(timed):
+        if timed:
+            e0, e1, e2 = ev(), ev(), ev()
+            e0.record()
+        levels = build_pyramid_raw(f1, f2, L, args.precision)
+        if timed:
+            e1.record()
+        out = None
+        for k in range(K):
+            out = lookup_raw(levels, coords[k], r)
+        if timed:
+            e2.record()
+            build_ev.append((e0, e1))
+            look_ev.append((e1, e2))
+        return out
+
+    for _ in range(max(args.warmup, 3)):
+        step(False)
+    torch.cuda.synchronize()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    t0, t1 = ev(), ev()
+    t0.record()
+    for _ in range(args.steps):
+        step(True)
+    t1.record()
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = t0.elapsed_time(t1)
+    ms_step = ms_total / args.steps
+    build_ms = sum(a.elapsed_time(b) for a, b in build_ev) / len(build_ev)
+    look_ms = sum(a.elapsed_time(b) for a, b in look_ev) / len(look_ev) / K  # per launch
+    if world > 1:
+        tt = torch.tensor([ms_step], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step = float(tt.item())
+    value = world * B / (ms_step * 1e-3)
+
+    # ---- end to end through the public API with HOST buffers (H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        out_host = torch.empty((B, L * (2 * r + 1) ** 2, h, w), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            a = f1_host.to(dev, non_blocking=True)
+            b = f2_host.to(dev, non_blocking=True)
+            blk = rr.CorrBlock(a, b, num_levels=L, radius=r, precision=args.precision)
+            for k in range(K):
+                c = coords_host[k].to(dev, non_blocking=True)
+                out_host.copy_(blk(c), non_blocking=True)
+
+        n_e2e = max(3, min(args.steps, 10))
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        barrier()
+        s0, s1 = ev(), ev()
+        s0.record()
+        for _ in range(n_e2e):
+            e2e_step()
+        s1.record()
+        torch.cuda.synchronize()
+        barrier()
+        e_ms = s0.elapsed_time(s1) / n_e2e
+        if world > 1:
+            tt = torch.tensor([e_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            e_ms = float(tt.item())
+        e2e = {"value": world * B / (e_ms * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(2 * f1_host.numel() * 4 + K * coords_host[0].numel() * 4),
+               "d2h_bytes_per_step": int(K * out_host.numel() * 4), "ms_per_step": e_ms, "steps": n_e2e}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = peaks()
+    b_build, b_look, b_total = algorithmic_bytes(B, N, D, h, w, L, r, K)
+    kern = {
+        "build": {"launches_per_step": 2, "ms": build_ms, "alg_bytes": b_build, "gbs": b_build / (build_ms * 1e-3) / 1e9,
+                  "share_of_step": build_ms / ms_step, "flops": 2.0 * B * N * N * D * (3 if args.precision == "bf16x3" else 1),
+                  "tflops": 2.0 * B * N * N * D * (3 if args.precision == "bf16x3" else 1) / (build_ms * 1e-3) / 1e12},
+        "lookup": {"launches_per_step": K, "ms": look_ms, "alg_bytes": b_look, "gbs": b_look / (look_ms * 1e-3) / 1e9,
+                   "share_of_step": look_ms * K / ms_step},
+    }
+    dom = "build" if build_ms >= look_ms * K else "lookup"
+    roofline = {"bound": "hbm", "kernel": "build_tc_kernel (prep + fused volume/pyramid)" if dom == "build" else "lookup_fwd_kernel",
+                "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kern[dom]["gbs"] / peak,
+                "traffic": None, "peak_source": peak_src,
+                "whole_step": {"alg_bytes": b_total, "gbs": b_total / (ms_step * 1e-3) / 1e9,
+                               "frac": b_total / (ms_step * 1e-3) / 1e9 / peak}}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup"}[args.precision],
+        "data": "synthetic", "config": workload_config(args, "gpu"), "precision": args.precision,
+        "roofline": roofline, "kernels": kern, "clocks": clocks, "gpu_launches": int(args.steps * (2 + K)),
+    }
+    if e2e is not None:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            c = cpu_reference_run(args, 2, 1, min(args.cpu_budget_s, 60.0))
+            line["cpu_baseline"] = {"value": c["pairs_per_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"]}
+        except Exception as e:
+            log(f"[bench] cpu baseline failed: {e}")
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

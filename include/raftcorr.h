@@ -1,0 +1,152 @@
+/*
+ * raftcorr.h -- C ABI of libraftcorr.so: RAFT's correlation hot path on B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Every entry point takes plain device pointers, sizes and a
+ * CUDA stream (as void*, i.e. a cudaStream_t); there are no torch types in any signature and
+ * the library links nothing but the CUDA runtime.  Outputs are CALLER-allocated.  The
+ * reference's extension instead allocates its outputs with torch::zeros
+ * (alt_cuda_corr/correlation_kernel.cu:272-273,304-307); the Python host layer
+ * (raft_ros_b200/) does that allocation with torch and then calls in here.
+ *
+ * Conventions
+ *   - return value: RC_OK (0) or an RC_ERR_* code; rc_last_error() returns a thread-local
+ *     message for the last failing call on this thread.  The reference signals errors by
+ *     TORCH_CHECK -> RuntimeError (alt_cuda_corr/correlation.cpp:19-21); the Python layer
+ *     turns a non-zero code into RuntimeError with the same wording where one exists.
+ *   - all kernels are launched on `stream` of the CURRENT device; the library never
+ *     synchronises the device and never allocates device memory.  (The reference launches
+ *     on the legacy default stream, correlation_kernel.cu:278,313.)
+ *   - all tensors are contiguous fp32 unless stated.  Level l of a pyramid built from an
+ *     h x w feature grid is (B*h*w, h>>l, w>>l): floor-mode 2x2 average pooling, exactly
+ *     F.avg_pool2d(x, 2, stride=2) at core/corr.py:26.
+ *   - window channel order of a lookup: channel = l*(2r+1)^2 + i*(2r+1) + j where i is the
+ *     x offset and j the y offset (core/corr.py:37-43; the same `iy + rd*ix` order as
+ *     alt_cuda_corr/correlation_kernel.cu:92-95).
+ */
+#ifndef RAFTCORR_H_
+#define RAFTCORR_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RC_OK 0
+#define RC_ERR_INVALID 1     /* bad argument (null pointer, non-positive size, ...) */
+#define RC_ERR_CUDA 2        /* a CUDA runtime / driver call failed */
+#define RC_ERR_UNSUPPORTED 3 /* valid in the reference but outside what this build covers */
+#define RC_ERR_WORKSPACE 4   /* workspace missing or too small */
+
+#define RC_MAX_LEVELS 8
+#define RC_MAX_RADIUS 8
+
+/* arithmetic used for the all-pairs contraction (the `precision` argument of the build) */
+#define RC_PREC_FP32 0   /* fp32 FMA on CUDA cores; matches cuBLAS SGEMM to ~1e-6        */
+#define RC_PREC_BF16X3 1 /* tcgen05, bf16 hi/lo split operands, 3 MMAs, fp32 accumulate;  */
+                         /* normwise error ~1e-5: the fp32-class tensor-core path         */
+#define RC_PREC_BF16 2   /* tcgen05, single bf16 pass, fp32 accumulate; ~2e-3 normwise    */
+
+int rc_version(void);
+const char *rc_last_error(void);
+
+/* h_l, w_l of level `level` (h>>level, w>>level); RC_ERR_INVALID if it would be empty. */
+int rc_level_dims(int h, int w, int level, int *hl, int *wl);
+
+/* Bytes of scratch rc_corr_build_pyramid needs for this problem (0 for RC_PREC_FP32). */
+size_t rc_corr_build_workspace_bytes(int B, int D, int h, int w, int precision);
+
+/*
+ * CorrBlock.corr + the pyramid of CorrBlock.__init__ in one pass.
+ * Replaces: core/corr.py:52-60 (view, matmul, /sqrt(D)) and core/corr.py:21-27
+ * (reshape to (B*h*w,1,h,w), num_levels-1 x F.avg_pool2d).
+ *   fmap1, fmap2 : (B, D, h, w) fp32 NCHW
+ *   level_ptrs   : HOST array of num_levels DEVICE pointers; level l is written as
+ *                  (B*h*w, h>>l, w>>l) fp32, every element exactly once
+ *   scale        : multiplies the contraction; pass 0 for the reference's 1/sqrt(D)
+ *   workspace    : device scratch of >= rc_corr_build_workspace_bytes(...) (may be NULL when 0)
+ */
+int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
+                          float *const *level_ptrs, int num_levels, int precision, float scale,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * CorrBlock.__call__: the (2r+1)^2 bilinear window of every level around coords / 2^l.
+ * Replaces: core/corr.py:29-50 and, through it, core/utils/utils.py:57-71
+ * (bilinear_sampler -> F.grid_sample bilinear, zeros padding, align_corners=True).
+ *   level_ptrs : HOST array of num_levels DEVICE pointers (as written by the build)
+ *   coords     : (B, 2, h, w) fp32, channel 0 = x, 1 = y (core/utils/utils.py:74-77)
+ *   out        : (B, num_levels*(2r+1)^2, h, w) fp32, fully overwritten
+ */
+int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
+                       int h, int w, int num_levels, int radius, void *stream);
+
+/*
+ * Gradient of the lookup w.r.t. the pyramid (coords carry no gradient: they are detached at
+ * core/raft.py:123).  Replaces what autograd does through core/corr.py:45 /
+ * F.grid_sample's backward, but deterministically: row p of every level is only ever
+ * touched by query p, so the scatter needs no atomics.
+ *   grad_out        : (B, num_levels*(2r+1)^2, h, w) fp32
+ *   grad_level_ptrs : HOST array of DEVICE pointers; gradients are ACCUMULATED (+=) so the
+ *                     K iterations of one step add up in stream order; zero them once per step
+ */
+int rc_corr_lookup_bwd(const float *grad_out, const float *coords, float *const *grad_level_ptrs,
+                       int B, int h, int w, int num_levels, int radius, void *stream);
+
+/* Bytes of scratch rc_corr_build_bwd needs. */
+size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w);
+
+/*
+ * Gradient of the build: folds the grad pyramid back to level 0 (avg_pool2d backward,
+ * core/corr.py:26), applies 1/sqrt(D) (:60) and the two contractions of matmul's backward
+ * (:58):  dfmap1[d,p] = sum_q dC[p,q] fmap2[d,q],  dfmap2[d,q] = sum_p dC[p,q] fmap1[d,p].
+ *   dfmap1, dfmap2 : (B, D, h, w) fp32, fully overwritten
+ */
+int rc_corr_build_bwd(const float *const *grad_level_ptrs, const float *fmap1, const float *fmap2,
+                      float *dfmap1, float *dfmap2, int B, int D, int h, int w, int num_levels,
+                      float scale, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * alt_cuda_corr.forward: windowed dot products computed on the fly (no volume).
+ * Replaces: alt_cuda_corr/correlation.cpp:23-33 -> correlation_kernel.cu:260-286 -> :18-119.
+ *   fmap1  : (B, H1, W1, C) fp32 NHWC      fmap2 : (B, H2, W2, C) fp32 NHWC
+ *   coords : (B, N, H1, W1, 2) fp32 [x, y]
+ *   corr   : (B, N, (2r+1)^2, H1, W1) fp32, fully overwritten (no pre-zeroing needed);
+ *            tap index = oy + (2r+1)*ox; NOT scaled by 1/sqrt(C) (the caller does that,
+ *            core/corr.py:91)
+ */
+int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords, float *corr,
+                    int B, int N, int H1, int W1, int H2, int W2, int C, int radius, void *stream);
+
+/*
+ * alt_cuda_corr.backward.
+ * Replaces: alt_cuda_corr/correlation.cpp:36-48 -> correlation_kernel.cu:288-324 -> :122-256.
+ *   corr_grad  : (B, N, (2r+1)^2, H1, W1)
+ *   fmap1_grad : (B, H1, W1, C)  fully overwritten
+ *   fmap2_grad : (B, H2, W2, C)  MUST be zero-filled by the caller; accumulated into
+ * coords_grad is identically zero in the reference (:307, never written); the Python shim
+ * returns zeros for it and this entry point does not take it.
+ */
+int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
+                    const float *corr_grad, float *fmap1_grad, float *fmap2_grad, int B, int N,
+                    int H1, int W1, int H2, int W2, int C, int radius, void *stream);
+
+/*
+ * bilinear_sampler: pixel-coordinate bilinear sampling with zeros outside.
+ * Replaces: core/utils/utils.py:57-71 (normalise to [-1,1], F.grid_sample(..., align_corners=True),
+ * optional in-bounds mask at :67-69).
+ *   img    : (M, C, H, W)      coords : (M, Ho, Wo, 2) [x, y] in pixels
+ *   out    : (M, C, Ho, Wo)    mask   : (M, Ho, Wo, 1) or NULL; 1 where 0<x<W-1 and 0<y<H-1
+ */
+int rc_bilinear_sampler_fwd(const float *img, const float *coords, float *out, float *mask, int M,
+                            int C, int H, int W, int Ho, int Wo, void *stream);
+
+/* Gradient of the sampler w.r.t. img (what autograd produces through F.grid_sample at
+ * core/utils/utils.py:65); grad_img (M, C, H, W) MUST be zero-filled by the caller. */
+int rc_bilinear_sampler_bwd(const float *grad_out, const float *coords, float *grad_img, int M, int C,
+                            int H, int W, int Ho, int Wo, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFTCORR_H_ */

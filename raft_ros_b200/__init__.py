@@ -1,0 +1,13 @@
+"""raft_ros_b200: RAFT's correlation hot path, B200-native (sm_100a), as a drop-in.
+
+    from raft_ros_b200 import CorrBlock, AlternateCorrBlock, bilinear_sampler, coords_grid
+    from raft_ros_b200 import alt_cuda_corr          # forward / backward, reference signatures
+
+Only the correlation path of the reference (core/corr.py, core/utils/utils.py:57-77,
+alt_cuda_corr/) lives here; everything else of RAFT stays the reference's own torch code.
+"""
+from . import alt_cuda_corr  # noqa: F401
+from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION  # noqa: F401
+from .utils import bilinear_sampler, coords_grid  # noqa: F401
+
+__all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr"]

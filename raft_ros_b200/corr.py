@@ -1,0 +1,254 @@
+"""Drop-in replacements for the reference's correlation operators.
+
+Same names, constructor arguments, attributes and call convention as the reference's
+`core/corr.py` (CorrBlock :12-60, AlternateCorrBlock :63-91), so `core/raft.py:104-107,124`
+works unchanged with `from raft_ros_b200.corr import CorrBlock, AlternateCorrBlock`.
+
+Host code here is PyTorch only for device memory, streams and autograd plumbing; all the
+arithmetic runs in hand-written sm_100a kernels behind the C ABI of libraftcorr.so
+(include/raftcorr.h).  There is no CPU or eager fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+_PRECISIONS = {"fp32": _lib.RC_PREC_FP32, "bf16x3": _lib.RC_PREC_BF16X3, "bf16": _lib.RC_PREC_BF16}
+
+#: arithmetic of the all-pairs contraction when the caller does not say: "bf16x3" is the
+#: fp32-class tensor-core path (error-compensated bf16 operands, ~1e-5 normwise), "bf16" the
+#: single-pass fast path, "fp32" plain fp32 FMA on CUDA cores.
+DEFAULT_PRECISION = os.environ.get("RAFT_CORR_PRECISION", "bf16x3")
+
+
+def _precision_code(precision: Optional[str]) -> int:
+    name = DEFAULT_PRECISION if precision is None else precision
+    if name not in _PRECISIONS:
+        raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {name!r}")
+    return _PRECISIONS[name]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(t: torch.Tensor, name: str) -> None:
+    # wording of the reference's CHECK_CUDA (alt_cuda_corr/correlation.cpp:19)
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().float().contiguous()
+
+
+def level_shapes(h: int, w: int, num_levels: int):
+    shapes = [(h >> l, w >> l) for l in range(num_levels)]
+    if shapes[-1][0] < 1 or shapes[-1][1] < 1:
+        raise RuntimeError(f"level {num_levels - 1} of a {h}x{w} feature grid is empty")
+    return shapes
+
+
+# --------------------------------------------------------------------------- raw ops
+def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int, precision: Optional[str] = None,
+                      scale: float = 0.0) -> List[torch.Tensor]:
+    """rc_corr_build_pyramid: (B,D,h,w) x2 -> list of (B*h*w, 1, h_l, w_l) fp32, one launch."""
+    _require_cuda(fmap1, "fmap1")
+    _require_cuda(fmap2, "fmap2")
+    if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
+        raise RuntimeError(f"fmap1/fmap2 must both be (B,D,h,w); got {tuple(fmap1.shape)} and {tuple(fmap2.shape)}")
+    if fmap1.device != fmap2.device:
+        raise RuntimeError("fmap1 and fmap2 must be on the same device")
+    f1, f2 = _f32c(fmap1), _f32c(fmap2)
+    B, D, h, w = f1.shape
+    shapes = level_shapes(h, w, num_levels)
+    prec = _precision_code(precision)
+    L = _lib.lib()
+    with torch.cuda.device(f1.device):
+        # one allocation for the whole pyramid; levels are views into it
+        sizes = [B * h * w * hl * wl for hl, wl in shapes]
+        # keep every level 256-byte aligned (TMA stores want 16 B; be generous)
+        offs, total = [], 0
+        for s in sizes:
+            offs.append(total)
+            total += (s + 63) // 64 * 64
+        flat = torch.empty(total, dtype=torch.float32, device=f1.device)
+        levels = [flat[o:o + s].view(B * h * w, 1, hl, wl) for o, s, (hl, wl) in zip(offs, sizes, shapes)]
+        ws_bytes = int(L.rc_corr_build_workspace_bytes(B, D, h, w, prec))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=f1.device) if ws_bytes else None
+        rc = L.rc_corr_build_pyramid(f1.data_ptr(), f2.data_ptr(), B, D, h, w,
+                                     _lib.ptr_array([lv.data_ptr() for lv in levels]), num_levels, prec,
+                                     float(scale), ws.data_ptr() if ws is not None else None, ws_bytes, _stream())
+        _lib.check(rc, "rc_corr_build_pyramid")
+        if ws is not None:
+            ws.record_stream(torch.cuda.current_stream())
+    return levels
+
+
+def lookup_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radius: int) -> torch.Tensor:
+    """rc_corr_lookup_fwd: (B,2,h,w) coords -> (B, L*(2r+1)^2, h, w) fp32, one launch."""
+    _require_cuda(coords, "coords")
+    if coords.dim() != 4 or coords.shape[1] != 2:
+        raise RuntimeError(f"coords must be (B,2,h,w); got {tuple(coords.shape)}")
+    c = _f32c(coords)
+    B, _, h, w = c.shape
+    nl = len(levels)
+    shapes = level_shapes(h, w, nl)
+    lv = []
+    for l, (t, (hl, wl)) in enumerate(zip(levels, shapes)):
+        _require_cuda(t, f"corr_pyramid[{l}]")
+        if t.numel() != B * h * w * hl * wl:
+            raise RuntimeError(f"corr_pyramid[{l}] has {t.numel()} elements, expected {B * h * w * hl * wl}")
+        lv.append(t if (t.dtype == torch.float32 and t.is_contiguous()) else _f32c(t))
+    rd = 2 * radius + 1
+    with torch.cuda.device(c.device):
+        out = torch.empty((B, nl * rd * rd, h, w), dtype=torch.float32, device=c.device)
+        rc = _lib.lib().rc_corr_lookup_fwd(_lib.ptr_array([t.data_ptr() for t in lv]), c.data_ptr(), out.data_ptr(),
+                                           B, h, w, nl, radius, _stream())
+        _lib.check(rc, "rc_corr_lookup_fwd")
+    return out
+
+
+def lookup_bwd_raw(grad_out: torch.Tensor, coords: torch.Tensor, grad_levels: Sequence[torch.Tensor], radius: int) -> None:
+    """rc_corr_lookup_bwd: accumulate d(out)/d(pyramid) into grad_levels (deterministic)."""
+    g, c = _f32c(grad_out), _f32c(coords)
+    B, _, h, w = c.shape
+    with torch.cuda.device(c.device):
+        rc = _lib.lib().rc_corr_lookup_bwd(g.data_ptr(), c.data_ptr(), _lib.ptr_array([t.data_ptr() for t in grad_levels]),
+                                           B, h, w, len(grad_levels), radius, _stream())
+        _lib.check(rc, "rc_corr_lookup_bwd")
+
+
+def build_bwd_raw(grad_levels: Sequence[torch.Tensor], fmap1: torch.Tensor, fmap2: torch.Tensor, scale: float = 0.0):
+    """rc_corr_build_bwd: grad pyramid -> (dfmap1, dfmap2), both (B,D,h,w)."""
+    f1, f2 = _f32c(fmap1), _f32c(fmap2)
+    B, D, h, w = f1.shape
+    L = _lib.lib()
+    with torch.cuda.device(f1.device):
+        df1, df2 = torch.empty_like(f1), torch.empty_like(f2)
+        ws_bytes = int(L.rc_corr_build_bwd_workspace_bytes(B, D, h, w))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=f1.device)
+        rc = L.rc_corr_build_bwd(_lib.ptr_array([t.data_ptr() for t in grad_levels]), f1.data_ptr(), f2.data_ptr(),
+                                 df1.data_ptr(), df2.data_ptr(), B, D, h, w, len(grad_levels), float(scale),
+                                 ws.data_ptr(), ws_bytes, _stream())
+        _lib.check(rc, "rc_corr_build_bwd")
+        ws.record_stream(torch.cuda.current_stream())
+    return df1, df2
+
+
+# --------------------------------------------------------------------------- autograd
+class _BuildPyramidFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, num_levels, precision):
+        ctx.save_for_backward(fmap1, fmap2)
+        levels = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
+        return tuple(levels)
+
+    @staticmethod
+    def backward(ctx, *grad_levels):
+        fmap1, fmap2 = ctx.saved_tensors
+        B, D, h, w = fmap1.shape
+        shapes = level_shapes(h, w, len(grad_levels))
+        gl = []
+        for g, (hl, wl) in zip(grad_levels, shapes):
+            if g is None:
+                g = torch.zeros((B * h * w, 1, hl, wl), dtype=torch.float32, device=fmap1.device)
+            gl.append(_f32c(g))
+        df1, df2 = build_bwd_raw(gl, fmap1, fmap2)
+        return df1.to(fmap1.dtype), df2.to(fmap2.dtype), None, None
+
+
+class _LookupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, coords, radius, *levels):
+        ctx.radius = radius
+        ctx.save_for_backward(coords)
+        ctx.level_shapes = [tuple(lv.shape) for lv in levels]
+        return lookup_raw(levels, coords, radius)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (coords,) = ctx.saved_tensors
+        grads = [torch.zeros(s, dtype=torch.float32, device=grad_out.device) for s in ctx.level_shapes]
+        lookup_bwd_raw(grad_out, coords, grads, ctx.radius)
+        # coords carry no gradient (they are detached at core/raft.py:123)
+        return (None, None) + tuple(grads)
+
+
+# --------------------------------------------------------------------------- public classes
+class CorrBlock:
+    """All-pairs correlation volume + pyramid + windowed lookup (reference core/corr.py:12-60).
+
+    `corr_pyramid` is a list of `num_levels` fp32 tensors shaped (B*h*w, 1, h>>l, w>>l), as in
+    the reference; it is produced by ONE kernel launch (contraction, 1/sqrt(D) scale and every
+    pooling level fused, each level written once).  `precision` is an extension: see
+    DEFAULT_PRECISION.
+    """
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None):
+        self.num_levels = num_levels
+        self.radius = radius
+        self.precision = precision
+        if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            self.corr_pyramid = list(_BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision))
+        else:
+            self.corr_pyramid = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
+
+    def __call__(self, coords):
+        if torch.is_grad_enabled() and any(lv.requires_grad for lv in self.corr_pyramid):
+            return _LookupFn.apply(coords, self.radius, *self.corr_pyramid)
+        return lookup_raw(self.corr_pyramid, coords, self.radius)
+
+    @staticmethod
+    def corr(fmap1, fmap2, precision=None):
+        """(B,D,h,w) x2 -> (B,h,w,1,h,w): fmap1^T fmap2 / sqrt(D) (reference core/corr.py:52-60)."""
+        B, _, h, w = fmap1.shape
+        if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            (vol,) = _BuildPyramidFn.apply(fmap1, fmap2, 1, precision)
+        else:
+            (vol,) = build_pyramid_raw(fmap1, fmap2, 1, precision)
+        return vol.view(B, h, w, 1, h, w)
+
+
+class AlternateCorrBlock:
+    """On-the-fly windowed correlation, no materialised volume (reference core/corr.py:63-91).
+
+    `pyramid` keeps the reference's attribute: num_levels+1 pairs of average-pooled feature
+    maps.  Unlike the reference, the NHWC copies the kernel needs are made once here instead
+    of on every call (core/corr.py:82-83), and each level is one launch of the sm_100a kernel
+    behind `alt_cuda_corr.forward`.  Forward only, as in the reference.
+    """
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4):
+        from torch.nn import functional as F
+
+        self.num_levels = num_levels
+        self.radius = radius
+        _require_cuda(fmap1, "fmap1")
+        _require_cuda(fmap2, "fmap2")
+        self.pyramid = [(fmap1, fmap2)]
+        for _ in range(self.num_levels):
+            fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
+            fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
+            self.pyramid.append((fmap1, fmap2))
+        self._f1_nhwc = _f32c(self.pyramid[0][0].permute(0, 2, 3, 1))
+        self._f2_nhwc = [_f32c(self.pyramid[i][1].permute(0, 2, 3, 1)) for i in range(self.num_levels)]
+
+    def __call__(self, coords):
+        from . import alt_cuda_corr
+
+        coords = coords.permute(0, 2, 3, 1)
+        B, H, W, _ = coords.shape
+        dim = self.pyramid[0][0].shape[1]
+        corr_list = []
+        for i in range(self.num_levels):
+            coords_i = (coords / 2 ** i).reshape(B, 1, H, W, 2).contiguous()
+            (corr,) = alt_cuda_corr.forward(self._f1_nhwc, self._f2_nhwc[i], coords_i, self.radius)
+            corr_list.append(corr.squeeze(1))
+        corr = torch.stack(corr_list, dim=1).reshape(B, -1, H, W)
+        # the reference divides by torch.sqrt(torch.tensor(dim).float()): an fp32 square root
+        return corr / float(torch.sqrt(torch.tensor(float(dim))))

@@ -1,0 +1,176 @@
+// extern "C" surface of libraftcorr.so (declared in include/raftcorr.h).
+// Argument validation + dispatch only; kernels live in the other translation units.
+#include <cstdarg>
+#include <cstdio>
+#include <cmath>
+
+#include "common.cuh"
+
+namespace rc {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return RC_ERR_CUDA;
+}
+
+static int check_geometry(const char *fn, int B, int h, int w, int L) {
+  RC_CHECK_ARG(B > 0 && h > 0 && w > 0, "%s: B, h, w must be positive (got %d, %d, %d)", fn, B, h, w);
+  RC_CHECK_ARG(L >= 1 && L <= RC_MAX_LEVELS, "%s: num_levels %d outside 1..%d", fn, L, RC_MAX_LEVELS);
+  RC_CHECK_ARG((h >> (L - 1)) >= 1 && (w >> (L - 1)) >= 1,
+               "%s: level %d of a %dx%d grid is empty", fn, L - 1, h, w);
+  RC_CHECK_ARG((long long)h * w <= 0x7fffffffLL / 4, "%s: feature grid too large", fn);
+  return RC_OK;
+}
+
+}  // namespace rc
+
+using namespace rc;
+
+extern "C" {
+
+int rc_version(void) { return 100; }
+
+const char *rc_last_error(void) { return g_err; }
+
+int rc_level_dims(int h, int w, int level, int *hl, int *wl) {
+  RC_CHECK_ARG(hl && wl, "rc_level_dims: null output");
+  RC_CHECK_ARG(level >= 0 && level < RC_MAX_LEVELS && h > 0 && w > 0, "rc_level_dims: bad arguments");
+  *hl = h >> level;
+  *wl = w >> level;
+  RC_CHECK_ARG(*hl >= 1 && *wl >= 1, "rc_level_dims: level %d of %dx%d is empty", level, h, w);
+  return RC_OK;
+}
+
+size_t rc_corr_build_workspace_bytes(int B, int D, int h, int w, int precision) {
+  if (precision == RC_PREC_FP32) return 0;
+  return build_tc_workspace_bytes(B, D, h, w, precision);
+}
+
+int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
+                          float *const *level_ptrs, int num_levels, int precision, float scale,
+                          void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_geometry("rc_corr_build_pyramid", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && level_ptrs, "rc_corr_build_pyramid: null pointer");
+  RC_CHECK_ARG(D > 0, "rc_corr_build_pyramid: D must be positive");
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_build_pyramid: level %d pointer is null", l);
+    lv.p[l] = level_ptrs[l];
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (precision) {
+    case RC_PREC_FP32:
+      return launch_build_simt(fmap1, fmap2, B, D, h, w, lv, num_levels, scale, st);
+    case RC_PREC_BF16X3:
+    case RC_PREC_BF16:
+      return launch_build_tc(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale, workspace,
+                             workspace_bytes, st);
+    default:
+      set_error("rc_corr_build_pyramid: unknown precision %d", precision);
+      return RC_ERR_INVALID;
+  }
+}
+
+int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
+                       int h, int w, int num_levels, int radius, void *stream) {
+  if (int rc = check_geometry("rc_corr_lookup_fwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(level_ptrs && coords && out, "rc_corr_lookup_fwd: null pointer");
+  RC_CHECK_ARG(radius >= 1, "rc_corr_lookup_fwd: radius must be >= 1");
+  ConstLevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_lookup_fwd: level %d pointer is null", l);
+    lv.p[l] = level_ptrs[l];
+  }
+  return launch_lookup_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_lookup_bwd(const float *grad_out, const float *coords, float *const *grad_level_ptrs,
+                       int B, int h, int w, int num_levels, int radius, void *stream) {
+  if (int rc = check_geometry("rc_corr_lookup_bwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(grad_level_ptrs && coords && grad_out, "rc_corr_lookup_bwd: null pointer");
+  RC_CHECK_ARG(radius >= 1, "rc_corr_lookup_bwd: radius must be >= 1");
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(grad_level_ptrs[l] != nullptr, "rc_corr_lookup_bwd: level %d pointer is null", l);
+    lv.p[l] = grad_level_ptrs[l];
+  }
+  return launch_lookup_bwd(grad_out, coords, lv, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
+}
+
+size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w) {
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return 0;
+  return build_bwd_workspace_bytes(B, D, h, w);
+}
+
+int rc_corr_build_bwd(const float *const *grad_level_ptrs, const float *fmap1, const float *fmap2,
+                      float *dfmap1, float *dfmap2, int B, int D, int h, int w, int num_levels,
+                      float scale, void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_geometry("rc_corr_build_bwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(grad_level_ptrs && fmap1 && fmap2 && dfmap1 && dfmap2, "rc_corr_build_bwd: null pointer");
+  RC_CHECK_ARG(D > 0, "rc_corr_build_bwd: D must be positive");
+  ConstLevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(grad_level_ptrs[l] != nullptr, "rc_corr_build_bwd: level %d pointer is null", l);
+    lv.p[l] = grad_level_ptrs[l];
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  return launch_build_bwd(lv, fmap1, fmap2, dfmap1, dfmap2, B, D, h, w, num_levels, scale, workspace,
+                          workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+static int check_alt(const char *fn, int B, int N, int H1, int W1, int H2, int W2, int C, int radius) {
+  RC_CHECK_ARG(B > 0 && N > 0 && H1 > 0 && W1 > 0 && H2 > 0 && W2 > 0 && C > 0,
+               "%s: all sizes must be positive", fn);
+  RC_CHECK_ARG(radius >= 1, "%s: radius must be >= 1", fn);
+  if (C % 4 != 0) {
+    set_error("%s: C=%d must be a multiple of 4 (the reference needs a multiple of 32)", fn, C);
+    return RC_ERR_UNSUPPORTED;
+  }
+  return RC_OK;
+}
+
+int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords, float *corr,
+                    int B, int N, int H1, int W1, int H2, int W2, int C, int radius, void *stream) {
+  if (int rc = check_alt("rc_alt_corr_fwd", B, N, H1, W1, H2, W2, C, radius)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && coords && corr, "rc_alt_corr_fwd: null pointer");
+  return launch_alt_fwd(fmap1, fmap2, coords, corr, B, N, H1, W1, H2, W2, C, radius,
+                        static_cast<cudaStream_t>(stream));
+}
+
+int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
+                    const float *corr_grad, float *fmap1_grad, float *fmap2_grad, int B, int N,
+                    int H1, int W1, int H2, int W2, int C, int radius, void *stream) {
+  if (int rc = check_alt("rc_alt_corr_bwd", B, N, H1, W1, H2, W2, C, radius)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && coords && corr_grad && fmap1_grad && fmap2_grad,
+               "rc_alt_corr_bwd: null pointer");
+  return launch_alt_bwd(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, N, H1, W1, H2,
+                        W2, C, radius, static_cast<cudaStream_t>(stream));
+}
+
+int rc_bilinear_sampler_fwd(const float *img, const float *coords, float *out, float *mask, int M,
+                            int C, int H, int W, int Ho, int Wo, void *stream) {
+  RC_CHECK_ARG(img && coords && out, "rc_bilinear_sampler_fwd: null pointer");
+  RC_CHECK_ARG(M > 0 && C > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0,
+               "rc_bilinear_sampler_fwd: all sizes must be positive");
+  return launch_bilinear_fwd(img, coords, out, mask, M, C, H, W, Ho, Wo, static_cast<cudaStream_t>(stream));
+}
+
+int rc_bilinear_sampler_bwd(const float *grad_out, const float *coords, float *grad_img, int M, int C,
+                            int H, int W, int Ho, int Wo, void *stream) {
+  RC_CHECK_ARG(grad_out && coords && grad_img, "rc_bilinear_sampler_bwd: null pointer");
+  RC_CHECK_ARG(M > 0 && C > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0,
+               "rc_bilinear_sampler_bwd: all sizes must be positive");
+  return launch_bilinear_bwd(grad_out, coords, grad_img, M, C, H, W, Ho, Wo, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,558 @@
+// Tensor-core build: all-pairs volume on tcgen05 (UMMA) with the 1/sqrt(D) scale and the whole
+// average-pool pyramid fused into the epilogue.  sm_100a only.
+//
+// Replaces CorrBlock.corr + the pyramid loop of CorrBlock.__init__ (reference
+// core/corr.py:52-60 and :21-27): cuBLAS SGEMM + divide + 3x avg_pool2d, which write the
+// 198 MB (440x1024) volume, re-read and re-write it for the scale and re-read each level for
+// pooling.  Here every pyramid element is written to HBM exactly once and never re-read.
+//
+// Data flow
+//   prep kernel : fmap (B,D,h,w) fp32 NCHW -> (B,h,w,Dp) bf16 K-major "hi" (+ "lo" residual
+//                 for RC_PREC_BF16X3: x ~= hi + lo, 16 mantissa bits), Dp = D rounded up to 64.
+//   main kernel : persistent, one CTA per SM, 6 warps:
+//                   warp 0  TMA producer  (A: 128 query pixels x 64 ch; B: an 8x32 SPATIAL patch
+//                           of fmap2 x 64 ch via a 4-D box, so the 256 columns of a tile are a
+//                           spatial patch and every 2x2/4x4/8x8 pooling window is tile-local)
+//                   warp 1  MMA issuer    (tcgen05.mma 128x256x16, bf16 -> fp32 in TMEM; BF16X3
+//                           issues hi*hi + hi*lo + lo*hi into the same accumulator)
+//                   warps 2-5 epilogue    (tcgen05.ld one spatial row pair at a time; thread <->
+//                           query pixel so all pooling is in registers; rows are transposed
+//                           through a per-warp padded smem tile and written as 128 B lines)
+//                 TMEM holds two 128x256 fp32 accumulators (all 512 columns): the MMAs of tile
+//                 i+1 overlap the epilogue of tile i.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace rc {
+
+namespace tc {
+
+constexpr int TM = 128;        // query pixels per tile (TMEM lanes)
+constexpr int PH = 8;          // patch rows
+constexpr int PW = 32;         // patch cols
+constexpr int TN = PH * PW;    // 256 target pixels per tile (TMEM columns)
+constexpr int TK = 64;         // channels per stage: 128 B rows, SWIZZLE_128B
+constexpr int UK = 16;         // K of one tcgen05.mma (bf16)
+constexpr int A_BYTES = TM * TK * 2;
+constexpr int B_BYTES = TN * TK * 2;
+constexpr int kThreads = 192;
+constexpr int kEpiWarps = 4;
+constexpr int kStageFloats = 32 * 33;  // per-warp transposition tile
+constexpr int kTmemCols = 512;
+
+struct Params {
+  int B, N, h, w, L;
+  int k_blocks;                 // Dp / 64
+  int m_tiles, nt_x, nt_y;      // tiles along query pixels / patch grid
+  long long total_tiles;
+  float scale;
+  LevelPtrs lv;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1,
+                                            int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap *tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 operands, fp32 accumulate, issued by ONE thread
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier once every previously issued MMA of this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t *u = reinterpret_cast<uint32_t *>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+        "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]),
+        "=r"(u[16]), "=r"(u[17]), "=r"(u[18]), "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]),
+        "=r"(u[24]), "=r"(u[25]), "=r"(u[26]), "=r"(u[27]), "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, SWIZZLE_128B shared-memory operand descriptor (rows of 128 B, 8-row atoms 1024 B apart)
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) /*LBO (unused for swizzled K-major)*/ |
+         ((uint64_t)(1024 >> 4) << 32) /*SBO*/ | (1ull << 46) /*sm100 descriptor version*/ |
+         (2ull << 61) /*SWIZZLE_128B*/;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=256
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+template <int NPASS>
+struct Cfg {
+  static constexpr int kOps = (NPASS == 3) ? 2 : 1;          // hi (+ lo)
+  static constexpr int kStageBytes = kOps * (A_BYTES + B_BYTES);
+  static constexpr int kStages = (NPASS == 3) ? 2 : 4;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes +
+                                    kEpiWarps * kStageFloats * 4 + 256 /*barriers*/;
+};
+
+// write one transposed chunk: this warp's 32 rows x NC floats, staged [row][NC+1], as
+// (32/NC... ) contiguous segments of NC floats per row
+template <int NC>
+__device__ __forceinline__ void store_chunk(float *stg, const float *vals, int lane, float *__restrict__ gbase,
+                                            size_t row_pitch, int rows_valid, int cols_valid) {
+  constexpr int S = NC + 1;
+  constexpr int RPI = 32 / NC;  // rows per store instruction
+#pragma unroll
+  for (int i = 0; i < NC; ++i) stg[lane * S + i] = vals[i];
+  __syncwarp();
+  const int rsub = lane / NC, c = lane - rsub * NC;
+  if (c < cols_valid) {
+#pragma unroll 8
+    for (int rr = 0; rr < 32; rr += RPI) {
+      const int r = rr + rsub;
+      if (r < rows_valid) st_stream(gbase + (size_t)r * row_pitch + c, stg[r * S + c]);
+    }
+  }
+  __syncwarp();
+}
+
+template <int NPASS>
+__global__ void __launch_bounds__(kThreads, 1)
+build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+                const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                const Params P) {
+  using C = Cfg<NPASS>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t *stage_base = smem;
+  float *stg_all = reinterpret_cast<float *>(smem + C::kStages * C::kStageBytes);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(stg_all + kEpiWarps * kStageFloats);
+  uint64_t *full = bars;                       // [kStages]
+  uint64_t *empty = bars + C::kStages;         // [kStages]
+  uint64_t *tfull = bars + 2 * C::kStages;     // [2]
+  uint64_t *tempty = tfull + 2;                // [2]
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], kEpiWarps);
+    }
+    fence_barrier_init();
+    prefetch_tmap(&tmA_hi);
+    prefetch_tmap(&tmB_hi);
+    if (NPASS == 3) {
+      prefetch_tmap(&tmA_lo);
+      prefetch_tmap(&tmB_lo);
+    }
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long tiles_per_item = (long long)P.m_tiles * P.nt_x * P.nt_y;
+  const int nt = P.nt_x * P.nt_y;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+        const int b = (int)(t / tiles_per_item);
+        const int rem = (int)(t - (long long)b * tiles_per_item);
+        const int m = rem / nt, n = rem - m * nt;
+        const int ny = n / P.nt_x, nx = n - ny * P.nt_x;
+        for (int kb = 0; kb < P.k_blocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t *sp = stage_base + stage * C::kStageBytes;
+          mbar_expect_tx(&full[stage], C::kStageBytes);
+          tma_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
+          tma_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, ny * PH, b);
+          if (NPASS == 3) {
+            tma_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
+            tma_load_4d(sp + C::kOps * A_BYTES + B_BYTES, &tmB_lo, &full[stage], kb * TK, nx * PW, ny * PH, b);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
+        for (int kb = 0; kb < P.k_blocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+          const uint64_t a_hi = make_sw128_desc(sa);
+          const uint64_t b_hi = make_sw128_desc(sa + C::kOps * A_BYTES);
+          const uint64_t a_lo = make_sw128_desc(sa + A_BYTES);
+          const uint64_t b_lo = make_sw128_desc(sa + C::kOps * A_BYTES + B_BYTES);
+#pragma unroll
+          for (int k = 0; k < TK / UK; ++k) {
+            const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);  // 32 B per K step inside the 128 B row
+            umma_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdesc, (kb | k) != 0 ? 1u : 0u);
+            if (NPASS == 3) {
+              umma_bf16(d_tmem, a_hi + koff, b_lo + koff, kIdesc, 1u);
+              umma_bf16(d_tmem, a_lo + koff, b_hi + koff, kIdesc, 1u);
+            }
+          }
+          umma_commit(&empty[stage]);  // smem slot reusable once these MMAs have read it
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps, thread <-> query pixel) =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    float *stg = stg_all + (warp - 2) * kStageFloats;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const int h = P.h, w = P.w, N = P.N, L = P.L;
+    const size_t pitch0 = (size_t)h * w;
+    const size_t pitch1 = (size_t)(h >> 1) * (w >> 1);
+    const size_t pitch2 = (size_t)(h >> 2) * (w >> 2);
+    const size_t pitch3 = (size_t)(h >> 3) * (w >> 3);
+    float *const lv0 = P.lv.p[0];
+    float *const lv1 = P.lv.p[1];
+    float *const lv2 = P.lv.p[2];
+    float *const lv3 = P.lv.p[3];
+    for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      const int b = (int)(t / tiles_per_item);
+      const int rem = (int)(t - (long long)b * tiles_per_item);
+      const int m = rem / nt, n = rem - m * nt;
+      const int ny = n / P.nt_x, nx = n - ny * P.nt_x;
+      const int prow0 = m * TM + q * 32;                 // first query pixel of this warp
+      const int rows_valid = min(32, N - prow0);         // may be <= 0
+      const size_t grow0 = (size_t)b * N + prow0;        // global row of the volume
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN);
+      float l1prev[16], l2prev[8];
+#pragma unroll
+      for (int j = 0; j < PH / 2; ++j) {
+        float v0[32], v1[32];
+        tmem_ld32(taddr + j * 64, v0);
+        tmem_ld32(taddr + j * 64 + 32, v1);
+        tmem_ld_wait();
+        if (j == PH / 2 - 1) {
+          // all TMEM reads of this tile are done: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[acc]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          v0[i] *= P.scale;
+          v1[i] *= P.scale;
+        }
+        const int y0 = ny * PH + 2 * j, x0 = nx * PW;
+        if (y0 < h)
+          store_chunk<32>(stg, v0, lane, lv0 + grow0 * pitch0 + (size_t)y0 * w + x0, pitch0, rows_valid, w - x0);
+        if (y0 + 1 < h)
+          store_chunk<32>(stg, v1, lane, lv0 + grow0 * pitch0 + (size_t)(y0 + 1) * w + x0, pitch0, rows_valid, w - x0);
+        if (L > 1) {
+          float l1[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float s = v0[2 * i] + v0[2 * i + 1];
+            s += v1[2 * i];
+            s += v1[2 * i + 1];
+            l1[i] = s * 0.25f;
+          }
+          const int h1 = h >> 1, w1 = w >> 1, y1 = ny * (PH / 2) + j, x1 = nx * (PW / 2);
+          if (y1 < h1)
+            store_chunk<16>(stg, l1, lane, lv1 + grow0 * pitch1 + (size_t)y1 * w1 + x1, pitch1, rows_valid, w1 - x1);
+          if (L > 2) {
+            if ((j & 1) == 0) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) l1prev[i] = l1[i];
+            } else {
+              float l2[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                float s = l1prev[2 * i] + l1prev[2 * i + 1];
+                s += l1[2 * i];
+                s += l1[2 * i + 1];
+                l2[i] = s * 0.25f;
+              }
+              const int h2 = h >> 2, w2 = w >> 2, y2 = ny * (PH / 4) + (j >> 1), x2 = nx * (PW / 4);
+              if (y2 < h2)
+                store_chunk<8>(stg, l2, lane, lv2 + grow0 * pitch2 + (size_t)y2 * w2 + x2, pitch2, rows_valid, w2 - x2);
+              if (L > 3) {
+                if (j == 1) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) l2prev[i] = l2[i];
+                } else {
+                  float l3[4];
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    float s = l2prev[2 * i] + l2prev[2 * i + 1];
+                    s += l2[2 * i];
+                    s += l2[2 * i + 1];
+                    l3[i] = s * 0.25f;
+                  }
+                  const int h3 = h >> 3, w3 = w >> 3, y3 = ny, x3 = nx * (PW / 8);
+                  if (y3 < h3)
+                    store_chunk<4>(stg, l3, lane, lv3 + grow0 * pitch3 + (size_t)y3 * w3 + x3, pitch3, rows_valid, w3 - x3);
+                }
+              }
+            }
+          }
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------ prep: NCHW fp32 -> NHWC bf16 hi/lo
+__global__ void __launch_bounds__(256)
+prep_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __nv_bfloat16 *__restrict__ a_hi,
+            __nv_bfloat16 *__restrict__ a_lo, __nv_bfloat16 *__restrict__ b_hi, __nv_bfloat16 *__restrict__ b_lo,
+            int D, int Dp, int N, int with_lo) {
+  __shared__ float tile[32][33];
+  const int which = blockIdx.z & 1, b = blockIdx.z >> 1;
+  const float *src = (which ? f2 : f1) + (size_t)b * D * N;
+  __nv_bfloat16 *hi = (which ? b_hi : a_hi) + (size_t)b * N * Dp;
+  __nv_bfloat16 *lo = (which ? b_lo : a_lo) + (size_t)b * N * Dp;
+  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int d = d0 + ty + 8 * i, p = p0 + tx;
+    tile[ty + 8 * i][tx] = (d < D && p < N) ? __ldg(src + (size_t)d * N + p) : 0.0f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, d = d0 + tx;
+    if (p < N && d < Dp) {
+      const float x = tile[tx][ty + 8 * i];
+      const __nv_bfloat16 xh = __float2bfloat16_rn(x);
+      hi[(size_t)p * Dp + d] = xh;
+      if (with_lo) lo[(size_t)p * Dp + d] = __float2bfloat16_rn(x - __bfloat162float(xh));
+    }
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+static int make_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides,
+                    const cuuint32_t *box) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return RC_ERR_CUDA;
+  }
+  cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims, strides, box, ones,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return RC_ERR_CUDA;
+  }
+  return RC_OK;
+}
+
+static int sm_count() {
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+  return n;
+}
+
+template <int NPASS>
+static int launch(const CUtensorMap &ah, const CUtensorMap &al, const CUtensorMap &bh, const CUtensorMap &bl,
+                  const Params &P, cudaStream_t st) {
+  using C = Cfg<NPASS>;
+  static_assert(C::kSmemBytes <= 227 * 1024, "shared memory budget");
+  RC_CUDA(cudaFuncSetAttribute(build_tc_kernel<NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  const long long sms = sm_count();
+  const unsigned grid = (unsigned)(P.total_tiles < sms ? P.total_tiles : sms);
+  build_tc_kernel<NPASS><<<grid, kThreads, C::kSmemBytes, st>>>(ah, al, bh, bl, P);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+}  // namespace tc
+
+static inline int round_up64(int d) { return (d + 63) / 64 * 64; }
+
+size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision) {
+  if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return 0;
+  const size_t per_map = (size_t)B * h * w * round_up64(D) * 2;  // bf16
+  const size_t aligned = (per_map + 255) / 256 * 256;
+  return aligned * 2 * (precision == RC_PREC_BF16X3 ? 2 : 1);
+}
+
+int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv, int L,
+                    int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st) {
+  using namespace tc;
+  const size_t need = build_tc_workspace_bytes(B, D, h, w, precision);
+  if (ws == nullptr || ws_bytes < need) {
+    set_error("rc_corr_build_pyramid: workspace too small (%zu < %zu bytes)", ws_bytes, need);
+    return RC_ERR_WORKSPACE;
+  }
+  if ((reinterpret_cast<uintptr_t>(ws) & 255) != 0) {
+    set_error("rc_corr_build_pyramid: workspace must be 256-byte aligned");
+    return RC_ERR_INVALID;
+  }
+  const int N = h * w, Dp = round_up64(D);
+  const bool x3 = precision == RC_PREC_BF16X3;
+  const size_t per_map = ((size_t)B * N * Dp * 2 + 255) / 256 * 256;
+  uint8_t *base = static_cast<uint8_t *>(ws);
+  __nv_bfloat16 *a_hi = reinterpret_cast<__nv_bfloat16 *>(base);
+  __nv_bfloat16 *b_hi = reinterpret_cast<__nv_bfloat16 *>(base + per_map);
+  __nv_bfloat16 *a_lo = x3 ? reinterpret_cast<__nv_bfloat16 *>(base + 2 * per_map) : a_hi;
+  __nv_bfloat16 *b_lo = x3 ? reinterpret_cast<__nv_bfloat16 *>(base + 3 * per_map) : b_hi;
+
+  {
+    dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 32), (unsigned)(2 * B));
+    prep_kernel<<<grid, 256, 0, st>>>(f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0);
+    RC_CUDA(cudaGetLastError());
+  }
+
+  CUtensorMap tmAh, tmAl, tmBh, tmBl;
+  {
+    const cuuint64_t dims[3] = {(cuuint64_t)Dp, (cuuint64_t)N, (cuuint64_t)B};
+    const cuuint64_t strides[2] = {(cuuint64_t)Dp * 2, (cuuint64_t)N * Dp * 2};
+    const cuuint32_t box[3] = {TK, TM, 1};
+    if (int rc = make_map(&tmAh, a_hi, 3, dims, strides, box)) return rc;
+    if (int rc = make_map(&tmAl, a_lo, 3, dims, strides, box)) return rc;
+  }
+  {
+    const cuuint64_t dims[4] = {(cuuint64_t)Dp, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
+    const cuuint64_t strides[3] = {(cuuint64_t)Dp * 2, (cuuint64_t)w * Dp * 2, (cuuint64_t)N * Dp * 2};
+    const cuuint32_t box[4] = {TK, PW, PH, 1};
+    if (int rc = make_map(&tmBh, b_hi, 4, dims, strides, box)) return rc;
+    if (int rc = make_map(&tmBl, b_lo, 4, dims, strides, box)) return rc;
+  }
+
+  Params P{};
+  P.B = B; P.N = N; P.h = h; P.w = w; P.L = L;
+  P.k_blocks = Dp / TK;
+  P.m_tiles = (N + TM - 1) / TM;
+  P.nt_x = (w + PW - 1) / PW;
+  P.nt_y = (h + PH - 1) / PH;
+  P.total_tiles = (long long)B * P.m_tiles * P.nt_x * P.nt_y;
+  P.scale = scale;
+  P.lv = lv;
+  for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
+
+  int rc = x3 ? tc::launch<3>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1>(tmAh, tmAl, tmBh, tmBl, P, st);
+  if (rc) return rc;
+  if (L > 4) return launch_pool_tail(lv, B, h, w, 4, L, st);
+  return RC_OK;
+}
+
+}  // namespace rc

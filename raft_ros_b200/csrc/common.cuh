@@ -1,0 +1,96 @@
+// Shared host/device helpers for libraftcorr (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/raftcorr.h"
+
+namespace rc {
+
+// thread-local last-error string (set by the host entry points)
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+
+#define RC_CHECK_ARG(cond, ...)          \
+  do {                                   \
+    if (!(cond)) {                       \
+      rc::set_error(__VA_ARGS__);        \
+      return RC_ERR_INVALID;             \
+    }                                    \
+  } while (0)
+
+#define RC_CUDA(call)                                        \
+  do {                                                       \
+    cudaError_t e__ = (call);                                \
+    if (e__ != cudaSuccess) return rc::cuda_fail(e__, #call); \
+  } while (0)
+
+struct LevelPtrs {
+  float *p[RC_MAX_LEVELS];
+};
+struct ConstLevelPtrs {
+  const float *p[RC_MAX_LEVELS];
+};
+
+// host launchers implemented in the .cu files (all return RC_* codes)
+int launch_build_simt(const float *f1, const float *f2, int B, int D, int h, int w,
+                      const LevelPtrs &lv, int L, float scale, cudaStream_t st);
+int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w,
+                    const LevelPtrs &lv, int L, int precision, float scale, void *ws,
+                    size_t ws_bytes, cudaStream_t st);
+size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision);
+int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
+                      int w, int L, int r, cudaStream_t st);
+int launch_lookup_bwd(const float *gout, const float *coords, const LevelPtrs &glv, int B, int h,
+                      int w, int L, int r, cudaStream_t st);
+size_t build_bwd_workspace_bytes(int B, int D, int h, int w);
+int launch_build_bwd(const ConstLevelPtrs &glv, const float *f1, const float *f2, float *df1,
+                     float *df2, int B, int D, int h, int w, int L, float scale, void *ws,
+                     size_t ws_bytes, cudaStream_t st);
+int launch_alt_fwd(const float *f1, const float *f2, const float *coords, float *corr, int B,
+                   int N, int H1, int W1, int H2, int W2, int C, int r, cudaStream_t st);
+int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const float *cg,
+                   float *g1, float *g2, int B, int N, int H1, int W1, int H2, int W2, int C,
+                   int r, cudaStream_t st);
+
+int launch_pool_tail(const LevelPtrs &lv, int B, int h, int w, int first, int L, cudaStream_t st);
+int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
+                        int H, int W, int Ho, int Wo, cudaStream_t st);
+int launch_bilinear_bwd(const float *gout, const float *coords, float *gimg, int M, int C, int H,
+                        int W, int Ho, int Wo, cudaStream_t st);
+
+// ---------------------------------------------------------------- device helpers
+#ifdef __CUDACC__
+// kernel-parameter pointer tables are selected with an unrolled compare chain: a dynamic index
+// would make the compiler copy the whole table to local memory
+template <typename P>
+__device__ __forceinline__ auto pick_level(const P &t, int lvl) {
+  auto r = t.p[0];
+#pragma unroll
+  for (int l = 1; l < RC_MAX_LEVELS; ++l)
+    if (lvl == l) r = t.p[l];
+  return r;
+}
+
+// floor() of a coordinate as an int that is safe for any float (NaN/Inf/huge -> far outside)
+__device__ __forceinline__ int safe_floor_int(float v, float *frac) {
+  float f = floorf(v);
+  *frac = v - f;
+  // clamp before the cast: everything beyond +-2^24 is outside any feature grid anyway
+  if (!(f > -16777216.0f)) { *frac = 0.0f; return -16777216; }
+  if (!(f < 16777216.0f)) { *frac = 0.0f; return 16777216; }
+  return (int)f;
+}
+
+__device__ __forceinline__ float ld_stream(const float *p) {
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream(float *p, float v) {
+  asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+#endif
+
+}  // namespace rc

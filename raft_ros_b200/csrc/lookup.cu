@@ -1,0 +1,248 @@
+// Pyramid lookup (forward) and its deterministic backward.
+//
+// Forward replaces CorrBlock.__call__ (reference core/corr.py:29-50) and the
+// bilinear_sampler/grid_sample chain under it (core/utils/utils.py:57-71): ~80 torch launches
+// and a materialised (B*h*w, 9, 9, 2) grid per level become ONE launch.
+//
+// HBM-bound gather.  Per query pixel p and level l the (2r+1)^2 bilinear taps only touch the
+// (2r+2)^2 integer patch of row p of level l, so the kernel reads that patch once (100 values
+// for r=4, not 81*4), forms the taps from shared memory and writes them in the final
+// (B, L*(2r+1)^2, h, w) layout with 128-byte coalesced stores (lanes <-> adjacent pixels).
+//
+// Work split: one CTA = 32 consecutive query pixels of one batch item x one level.
+//   phase 1 (warp per pixel, lanes <-> patch elements): issue all patch loads of 4 pixels
+//            (16 independent loads per lane in flight), park them in a per-warp patch buffer,
+//            lanes <-> taps compute the bilinear sums into a [tap][33] tile (conflict-free).
+//   phase 2 (lanes <-> pixels): one coalesced 128 B store per tap channel.
+#include "common.cuh"
+
+namespace rc {
+
+constexpr int kLookupThreads = 128;
+constexpr int kLookupWarps = kLookupThreads / 32;
+constexpr int kTilePix = 32;
+constexpr int kPixPerWarp = kTilePix / kLookupWarps;  // 8
+constexpr int kUnroll = 4;                            // pixels in flight per warp
+
+template <int R>
+__global__ void __launch_bounds__(kLookupThreads)
+lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__restrict__ out,
+                  int B, int h, int w, int L, int tiles_per_item) {
+  constexpr int RD = 2 * R + 1;
+  constexpr int PN = RD + 1;
+  constexpr int NPATCH = PN * PN;
+  constexpr int NTAP = RD * RD;
+  constexpr int NE = (NPATCH + 31) / 32;
+  constexpr int NT = (NTAP + 31) / 32;
+  constexpr int TS = kTilePix + 1;  // padded tile stride
+
+  extern __shared__ float smem[];
+  float *tile = smem;                                  // [NTAP][TS]
+  float *patch_all = smem + NTAP * TS;                 // [warps][kUnroll][NPATCH]
+
+  const int lvl = blockIdx.y;
+  const int b = blockIdx.x / tiles_per_item;
+  const int p0 = (blockIdx.x - b * tiles_per_item) * kTilePix;
+  const int N = h * w;
+  const int hl = h >> lvl, wl = w >> lvl;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float inv = 1.0f / (float)(1 << lvl);  // exact: same value as coords / 2**lvl
+  const float *__restrict__ vol = pick_level(lv, lvl);
+  float *patch = patch_all + warp * (kUnroll * NPATCH);
+
+#pragma unroll 1
+  for (int g = 0; g < kPixPerWarp; g += kUnroll) {
+    float v[kUnroll][NE];
+    float fx[kUnroll], fy[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int pix = warp * kPixPerWarp + g + u;
+      const int p = p0 + pix;
+      const bool pvalid = p < N;
+      float cx = 0.f, cy = 0.f;
+      if (pvalid) {
+        cx = __ldg(coords + ((size_t)b * 2 + 0) * N + p) * inv;
+        cy = __ldg(coords + ((size_t)b * 2 + 1) * N + p) * inv;
+      }
+      const int x0 = safe_floor_int(cx, &fx[u]) - R;
+      const int y0 = safe_floor_int(cy, &fy[u]) - R;
+      const float *row = vol + ((size_t)b * N + (pvalid ? p : 0)) * ((size_t)hl * wl);
+#pragma unroll
+      for (int k = 0; k < NE; ++k) {
+        const int e = lane + 32 * k;
+        const int py = e / PN, px = e - py * PN;
+        const int gy = y0 + py, gx = x0 + px;
+        const bool ok = pvalid && (e < NPATCH) && gy >= 0 && gy < hl && gx >= 0 && gx < wl;
+        v[u][k] = ok ? ld_stream(row + (size_t)gy * wl + gx) : 0.0f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+      for (int k = 0; k < NE; ++k) {
+        const int e = lane + 32 * k;
+        if (e < NPATCH) patch[u * NPATCH + e] = v[u][k];
+      }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int pix = warp * kPixPerWarp + g + u;
+      const float dx = fx[u], dy = fy[u];
+      const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
+      const float w10 = dy * (1.0f - dx), w11 = dy * dx;
+      const float *pp = patch + u * NPATCH;
+#pragma unroll
+      for (int k = 0; k < NT; ++k) {
+        const int t = lane + 32 * k;
+        if (t < NTAP) {
+          const int i = t / RD, j = t - i * RD;  // i: x offset, j: y offset
+          const float *q = pp + j * PN + i;
+          float s = q[0] * w00;
+          s = fmaf(q[1], w01, s);
+          s = fmaf(q[PN], w10, s);
+          s = fmaf(q[PN + 1], w11, s);
+          tile[t * TS + pix] = s;
+        }
+      }
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+
+  const int CH = L * NTAP;
+  const int p = p0 + lane;
+  if (p < N) {
+    float *o = out + ((size_t)b * CH + (size_t)lvl * NTAP) * N + p;
+#pragma unroll 4
+    for (int t = warp; t < NTAP; t += kLookupWarps) st_stream(o + (size_t)t * N, tile[t * TS + lane]);
+  }
+}
+
+// ------------------------------------------------------------------ backward
+// Deterministic scatter-add: warp per (pixel, level); the (2r+2)^2 patch gradient is formed
+// in shared memory from the (2r+1)^2 output cotangents in a fixed order and added to row p
+// of the grad pyramid with plain read-modify-write (no other query touches that row).
+template <int R>
+__global__ void __launch_bounds__(kLookupThreads)
+lookup_bwd_kernel(LevelPtrs glv, const float *__restrict__ coords, const float *__restrict__ gout,
+                  int B, int h, int w, int L, int tiles_per_item) {
+  constexpr int RD = 2 * R + 1;
+  constexpr int PN = RD + 1;
+  constexpr int NPATCH = PN * PN;
+  constexpr int NTAP = RD * RD;
+  constexpr int NE = (NPATCH + 31) / 32;
+  constexpr int TS = kTilePix + 1;
+
+  extern __shared__ float smem[];
+  float *tile = smem;  // [NTAP][TS] cotangents of this level, transposed in via coalesced loads
+
+  const int lvl = blockIdx.y;
+  const int b = blockIdx.x / tiles_per_item;
+  const int p0 = (blockIdx.x - b * tiles_per_item) * kTilePix;
+  const int N = h * w;
+  const int hl = h >> lvl, wl = w >> lvl;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float inv = 1.0f / (float)(1 << lvl);
+  const int CH = L * NTAP;
+
+  {
+    const int p = p0 + lane;
+    const float *gi = gout + ((size_t)b * CH + (size_t)lvl * NTAP) * N + p;
+    for (int t = warp; t < NTAP; t += kLookupWarps)
+      tile[t * TS + lane] = (p < N) ? ld_stream(gi + (size_t)t * N) : 0.0f;
+  }
+  __syncthreads();
+
+  float *__restrict__ gvol = pick_level(glv, lvl);
+#pragma unroll 1
+  for (int u = 0; u < kPixPerWarp; ++u) {
+    const int pix = warp * kPixPerWarp + u;
+    const int p = p0 + pix;
+    if (p >= N) break;  // warp-uniform
+    float dx, dy;
+    const float cx = __ldg(coords + ((size_t)b * 2 + 0) * N + p) * inv;
+    const float cy = __ldg(coords + ((size_t)b * 2 + 1) * N + p) * inv;
+    const int x0 = safe_floor_int(cx, &dx) - R;
+    const int y0 = safe_floor_int(cy, &dy) - R;
+    const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
+    const float w10 = dy * (1.0f - dx), w11 = dy * dx;
+    float *row = gvol + ((size_t)b * N + p) * ((size_t)hl * wl);
+#pragma unroll
+    for (int k = 0; k < NE; ++k) {
+      const int e = lane + 32 * k;
+      const int py = e / PN, px = e - py * PN;
+      const int gy = y0 + py, gx = x0 + px;
+      if (e < NPATCH && gy >= 0 && gy < hl && gx >= 0 && gx < wl) {
+        // patch cell (py,px) receives from taps (i,j) in {px-1,px} x {py-1,py}
+        float s = 0.0f;
+        if (py < RD && px < RD) s = tile[(px * RD + py) * TS + pix] * w00;
+        if (py < RD && px > 0) s = fmaf(tile[((px - 1) * RD + py) * TS + pix], w01, s);
+        if (py > 0 && px < RD) s = fmaf(tile[(px * RD + py - 1) * TS + pix], w10, s);
+        if (py > 0 && px > 0) s = fmaf(tile[((px - 1) * RD + py - 1) * TS + pix], w11, s);
+        float *dst = row + (size_t)gy * wl + gx;
+        *dst += s;
+      }
+    }
+  }
+}
+
+template <int R>
+static int launch_fwd_r(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
+                        int w, int L, cudaStream_t st) {
+  constexpr int RD = 2 * R + 1, PN = RD + 1;
+  const int N = h * w;
+  const int tiles = (N + kTilePix - 1) / kTilePix;
+  const size_t smem = sizeof(float) * (RD * RD * (kTilePix + 1) + kLookupWarps * kUnroll * PN * PN);
+  if (smem > 48 * 1024)
+    RC_CUDA(cudaFuncSetAttribute(lookup_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)(B * tiles), (unsigned)L);
+  lookup_fwd_kernel<R><<<grid, kLookupThreads, smem, st>>>(lv, coords, out, B, h, w, L, tiles);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+template <int R>
+static int launch_bwd_r(const float *gout, const float *coords, const LevelPtrs &glv, int B, int h,
+                        int w, int L, cudaStream_t st) {
+  constexpr int RD = 2 * R + 1;
+  const int N = h * w;
+  const int tiles = (N + kTilePix - 1) / kTilePix;
+  const size_t smem = sizeof(float) * (RD * RD * (kTilePix + 1));
+  if (smem > 48 * 1024)
+    RC_CUDA(cudaFuncSetAttribute(lookup_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)(B * tiles), (unsigned)L);
+  lookup_bwd_kernel<R><<<grid, kLookupThreads, smem, st>>>(glv, coords, gout, B, h, w, L, tiles);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+#define RC_RADIUS_SWITCH(r, CALL)          \
+  switch (r) {                             \
+    case 1: return CALL(1);                \
+    case 2: return CALL(2);                \
+    case 3: return CALL(3);                \
+    case 4: return CALL(4);                \
+    case 5: return CALL(5);                \
+    case 6: return CALL(6);                \
+    case 7: return CALL(7);                \
+    case 8: return CALL(8);                \
+    default:                               \
+      set_error("radius %d unsupported (1..%d)", r, RC_MAX_RADIUS); \
+      return RC_ERR_UNSUPPORTED;           \
+  }
+
+int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
+                      int w, int L, int r, cudaStream_t st) {
+#define CALL(R) launch_fwd_r<R>(lv, coords, out, B, h, w, L, st)
+  RC_RADIUS_SWITCH(r, CALL)
+#undef CALL
+}
+
+int launch_lookup_bwd(const float *gout, const float *coords, const LevelPtrs &glv, int B, int h,
+                      int w, int L, int r, cudaStream_t st) {
+#define CALL(R) launch_bwd_r<R>(gout, coords, glv, B, h, w, L, st)
+  RC_RADIUS_SWITCH(r, CALL)
+#undef CALL
+}
+
+}  // namespace rc

@@ -1,0 +1,68 @@
+"""Sampling helpers of the hot path (reference core/utils/utils.py:57-77)."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+
+class _BilinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, coords, want_mask):
+        im = img.detach().float().contiguous()
+        co = coords.detach().float().contiguous()
+        M, C, H, W = im.shape
+        _, Ho, Wo, _ = co.shape
+        with torch.cuda.device(im.device):
+            out = torch.empty((M, C, Ho, Wo), dtype=torch.float32, device=im.device)
+            mask = torch.empty((M, Ho, Wo, 1), dtype=torch.float32, device=im.device) if want_mask else None
+            rc = _lib.lib().rc_bilinear_sampler_fwd(im.data_ptr(), co.data_ptr(), out.data_ptr(),
+                                                    mask.data_ptr() if want_mask else None, M, C, H, W, Ho, Wo,
+                                                    torch.cuda.current_stream().cuda_stream)
+            _lib.check(rc, "rc_bilinear_sampler_fwd")
+        ctx.save_for_backward(co)
+        ctx.img_shape = (M, C, H, W)
+        if want_mask:
+            ctx.mark_non_differentiable(mask)
+            return out, mask
+        return out, None
+
+    @staticmethod
+    def backward(ctx, gout, _gmask):
+        (co,) = ctx.saved_tensors
+        M, C, H, W = ctx.img_shape
+        _, Ho, Wo, _ = co.shape
+        g = gout.detach().float().contiguous()
+        with torch.cuda.device(g.device):
+            gimg = torch.zeros((M, C, H, W), dtype=torch.float32, device=g.device)
+            rc = _lib.lib().rc_bilinear_sampler_bwd(g.data_ptr(), co.data_ptr(), gimg.data_ptr(), M, C, H, W, Ho, Wo,
+                                                    torch.cuda.current_stream().cuda_stream)
+            _lib.check(rc, "rc_bilinear_sampler_bwd")
+        return gimg, None, None
+
+
+def bilinear_sampler(img, coords, mode='bilinear', mask=False):
+    """Pixel-coordinate bilinear sampling, zeros outside (reference core/utils/utils.py:57-71).
+
+    img (M,C,H,W), coords (M,Ho,Wo,2) [x,y] in pixels -> (M,C,Ho,Wo); with mask=True also the
+    in-bounds mask (M,Ho,Wo,1) of utils.py:67-69.  `mode` is accepted and ignored, as in the
+    reference.  Gradients flow to `img` only: the one caller on the hot path detaches coords
+    (core/raft.py:123).
+    """
+    if not img.is_cuda:
+        raise RuntimeError("img must be a CUDA tensor")
+    if img.dim() != 4 or coords.dim() != 4 or coords.shape[-1] != 2 or coords.shape[0] != img.shape[0]:
+        raise RuntimeError(f"expected img (M,C,H,W) and coords (M,Ho,Wo,2); got {tuple(img.shape)}, {tuple(coords.shape)}")
+    if coords.requires_grad and torch.is_grad_enabled():
+        raise RuntimeError("bilinear_sampler: gradients w.r.t. coords are not provided (detach them, as core/raft.py:123 does)")
+    out, m = _BilinearFn.apply(img, coords, bool(mask))
+    if mask:
+        return out, m
+    return out
+
+
+def coords_grid(batch, ht, wd, device):
+    """(B,2,h,w) pixel grid, channel 0 = x (column), 1 = y (row) (reference utils.py:74-77)."""
+    ys = torch.arange(ht, device=device, dtype=torch.float32).view(1, 1, ht, 1).expand(batch, 1, ht, wd)
+    xs = torch.arange(wd, device=device, dtype=torch.float32).view(1, 1, 1, wd).expand(batch, 1, ht, wd)
+    return torch.cat([xs, ys], dim=1).contiguous()

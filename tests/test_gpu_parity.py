@@ -1,0 +1,319 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the Python host layer and the
+C ABI of libraftcorr.so, against (a) the fixtures produced by the reference's own Python,
+(b) the CPU oracle on seeded inputs, (c) size-independent properties at full size.
+
+Tolerances (values cross zero, so always relative to the largest reference magnitude or
+normwise, never element-wise relative):
+  fp32 build          relmax <= 3e-6   (fp32 FMA vs the reference's SGEMM / double oracle)
+  bf16x3 build        relmax <= 1e-4, normwise <= 3e-5   (the "<=1e-4" fp32-class bound)
+  bf16 build          normwise <= 6e-3 (single-pass bf16 operands, 8-bit mantissa)
+  lookup (same pyramid) relmax <= 5e-6 (pixel-space sampling vs grid_sample's round trip)
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import corr_oracle as O
+import zlib
+
+from tests.helpers import cotangent, make_coords, normwise, relmax
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+BUILD_TOL = {"fp32": dict(rel=3e-6, norm=2e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
+PRECISIONS = ["fp32", "bf16x3", "bf16"]
+
+
+@pytest.fixture(scope="module")
+def rr():
+    import raft_ros_b200
+    from raft_ros_b200 import _lib
+    _lib.build()
+    _lib.lib()  # raises if the CUDA library is missing: no fallback
+    assert torch.cuda.is_available()
+    return raft_ros_b200
+
+
+def seed_of(*args):
+    return zlib.crc32(repr(args).encode())
+
+
+def t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def n(x):
+    return x.detach().float().cpu().numpy()
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+def _kinds(z):
+    return sorted(k[len("coords_"):] for k in z.files if k.startswith("coords_"))
+
+
+GOLDEN = ["corrblock_17x20_r4", "corrblock_16x18_r3"]
+
+
+# ----------------------------------------------------------------------------- golden fixtures
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_build(rr, golden_dir, name, precision):
+    z = _load(golden_dir, name)
+    L, r = int(z["num_levels"]), int(z["radius"])
+    blk = rr.CorrBlock(t(z["fmap1"]), t(z["fmap2"]), num_levels=L, radius=r, precision=precision)
+    assert blk.num_levels == L and blk.radius == r and len(blk.corr_pyramid) == L
+    tol = BUILD_TOL[precision]
+    for l in range(L):
+        ref = z[f"level{l}"]
+        got = blk.corr_pyramid[l]
+        assert tuple(got.shape) == ref.shape and got.dtype == torch.float32 and got.is_contiguous()
+        assert relmax(n(got), ref) <= tol["rel"], (name, l, precision)
+        assert normwise(n(got), ref) <= tol["norm"], (name, l, precision)
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_lookup_on_reference_pyramid(rr, golden_dir, name):
+    """Lookup alone: feed the reference's own pyramid, compare with the reference's output."""
+    z = _load(golden_dir, name)
+    L, r = int(z["num_levels"]), int(z["radius"])
+    from raft_ros_b200.corr import lookup_raw
+    levels = [t(z[f"level{l}"]) for l in range(L)]
+    for kind in _kinds(z):
+        out = lookup_raw(levels, t(z[f"coords_{kind}"]), r)
+        ref = z[f"out_{kind}"]
+        assert tuple(out.shape) == ref.shape and out.dtype == torch.float32 and out.is_contiguous()
+        assert relmax(n(out), ref) <= 5e-6, (name, kind)
+        # and bit-for-layout against the oracle in the same (pixel-space) arithmetic
+        orc = O.corr_lookup([z[f"level{l}"] for l in range(L)], z[f"coords_{kind}"], r, roundtrip=False)
+        assert relmax(n(out), orc) <= 1e-6, (name, kind)
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_end_to_end_and_backward(rr, golden_dir, name):
+    """CorrBlock(fmaps)(coords) and autograd through it vs the reference's autograd."""
+    z = _load(golden_dir, name)
+    L, r = int(z["num_levels"]), int(z["radius"])
+    f1 = t(z["fmap1"]).requires_grad_(True)
+    f2 = t(z["fmap2"]).requires_grad_(True)
+    blk = rr.CorrBlock(f1, f2, num_levels=L, radius=r, precision="fp32")
+    total = None
+    for kind in _kinds(z):
+        out = blk(t(z[f"coords_{kind}"]))
+        assert relmax(n(out), z[f"out_{kind}"]) <= 8e-6, (name, kind)
+        g = t(cotangent(name, kind, z[f"out_{kind}"].shape))
+        total = (out * g).sum() if total is None else total + (out * g).sum()
+    total.backward()
+    assert relmax(n(f1.grad), z["dfmap1"]) <= 1e-5
+    assert relmax(n(f2.grad), z["dfmap2"]) <= 1e-5
+
+
+# ----------------------------------------------------------------------------- seeded vs oracle
+SHAPES = [
+    # (B, D, h, w, L, r)  -- ragged against every tile size: 8x16 / 8x32 patches, 32-pixel tiles
+    (2, 64, 27, 40, 4, 4),
+    (1, 256, 23, 39, 3, 4),     # odd everywhere; D of the real network
+    (3, 32, 16, 16, 4, 3),      # exact multiples, raft-small radius
+    (1, 128, 33, 67, 4, 4),     # one past multiples
+    (1, 48, 9, 130, 2, 2),      # wide and flat, D not a multiple of 64
+]
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("shape", SHAPES)
+def test_build_vs_oracle(rr, shape, precision):
+    B, D, h, w, L, r = shape
+    rng = np.random.default_rng(seed_of(shape))
+    f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    want = O.corr_build(f1, f2, L)
+    blk = rr.CorrBlock(t(f1), t(f2), num_levels=L, radius=r, precision=precision)
+    tol = BUILD_TOL[precision]
+    for l in range(L):
+        got = n(blk.corr_pyramid[l])
+        assert got.shape == want[l].shape
+        assert np.isfinite(got).all()
+        assert relmax(got, want[l]) <= tol["rel"], (shape, l, relmax(got, want[l]))
+        assert normwise(got, want[l]) <= tol["norm"], (shape, l, normwise(got, want[l]))
+
+
+@pytest.mark.parametrize("kind", ["grid", "sigma0.5", "sigma4", "sigma32", "oob", "border", "huge"])
+@pytest.mark.parametrize("shape", SHAPES[:4])
+def test_lookup_vs_oracle(rr, shape, kind):
+    B, D, h, w, L, r = shape
+    from raft_ros_b200.corr import lookup_raw
+    rng = np.random.default_rng(seed_of(shape, kind))
+    shapes = O.level_shapes(h, w, L)
+    levels = [rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32) for hl, wl in shapes]
+    coords = make_coords(kind, B, h, w, rng)
+    want = O.corr_lookup(levels, coords, r)
+    got = n(lookup_raw([t(lv) for lv in levels], t(coords), r))
+    assert got.shape == want.shape
+    assert relmax(got, want) <= 1e-6, (shape, kind)
+    if kind == "huge":
+        assert np.isfinite(got).all()
+
+
+@pytest.mark.parametrize("shape", SHAPES[:3])
+def test_lookup_bwd_vs_oracle_and_determinism(rr, shape):
+    B, D, h, w, L, r = shape
+    from raft_ros_b200.corr import lookup_bwd_raw
+    rng = np.random.default_rng(99)
+    coords = make_coords("sigma4", B, h, w, rng)
+    g = rng.standard_normal((B, L * (2 * r + 1) ** 2, h, w)).astype(np.float32)
+    want = O.corr_lookup_bwd(g, coords, L, r)
+    runs = []
+    for _ in range(2):
+        grads = [torch.zeros(B * h * w, 1, hl, wl, device=DEV) for hl, wl in O.level_shapes(h, w, L)]
+        lookup_bwd_raw(t(g), t(coords), grads, r)
+        runs.append([n(x) for x in grads])
+    for l in range(L):
+        assert relmax(runs[0][l], want[l]) <= 2e-6, (shape, l)
+        assert np.array_equal(runs[0][l], runs[1][l]), "lookup backward must be bit-reproducible"
+    # accumulation semantics: a second call adds on top
+    grads = [torch.zeros(B * h * w, 1, hl, wl, device=DEV) for hl, wl in O.level_shapes(h, w, L)]
+    lookup_bwd_raw(t(g), t(coords), grads, r)
+    lookup_bwd_raw(t(g), t(coords), grads, r)
+    assert relmax(n(grads[0]), 2 * want[0]) <= 2e-6
+
+
+def test_build_bwd_vs_oracle(rr):
+    from raft_ros_b200.corr import build_bwd_raw
+    B, D, h, w, L = 2, 48, 18, 21, 4
+    rng = np.random.default_rng(5)
+    f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    gl = [rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32) for hl, wl in O.level_shapes(h, w, L)]
+    w1, w2 = O.corr_build_bwd(gl, f1, f2)
+    d1, d2 = build_bwd_raw([t(g) for g in gl], t(f1), t(f2))
+    assert relmax(n(d1), w1) <= 5e-6 and relmax(n(d2), w2) <= 5e-6
+
+
+# ----------------------------------------------------------------------------- alt (on the fly)
+ALT_SHAPES = [(2, 1, 13, 18, 13, 18, 64, 4), (1, 2, 9, 11, 4, 5, 32, 3), (1, 1, 16, 16, 8, 8, 256, 4), (1, 1, 7, 33, 7, 33, 36, 2)]
+
+
+@pytest.mark.parametrize("shape", ALT_SHAPES)
+def test_alt_fwd_bwd_vs_oracle(rr, shape):
+    B, N, H1, W1, H2, W2, C, r = shape
+    rng = np.random.default_rng(seed_of(shape))
+    f1 = rng.standard_normal((B, H1, W1, C)).astype(np.float32)
+    f2 = rng.standard_normal((B, H2, W2, C)).astype(np.float32)
+    base = make_coords("sigma4", B, H1, W1, rng).transpose(0, 2, 3, 1)[:, None] * (W2 / W1)
+    coords = (base + rng.standard_normal((B, N, H1, W1, 2))).astype(np.float32)
+    coords[0, 0, 0, 0] = (-3.5, 2.25)          # window straddling the border
+    coords[0, 0, -1, -1] = (W2 + 40.0, -77.0)  # far outside -> zeros
+    (corr,) = rr.alt_cuda_corr.forward(t(f1), t(f2), t(coords), r)
+    want = O.alt_fwd(f1, f2, coords, r)
+    assert tuple(corr.shape) == want.shape
+    assert relmax(n(corr), want) <= 2e-6
+    g = rng.standard_normal(want.shape).astype(np.float32)
+    g1, g2, gc = rr.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(g), r)
+    w1, w2, _ = O.alt_bwd(f1, f2, coords, g, r)
+    assert relmax(n(g1), w1) <= 3e-6 and relmax(n(g2), w2) <= 1e-5
+    assert tuple(gc.shape) == coords.shape and not bool(gc.any())
+
+
+def test_alternate_block_equals_corrblock(rr):
+    """AlternateCorrBlock(coords) == CorrBlock(coords) (reference README.md:109-114)."""
+    B, D, h, w = 2, 64, 24, 32
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    f2 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    coords = rr.coords_grid(B, h, w, DEV) + 3.0 * torch.randn(B, 2, h, w, generator=g).to(DEV)
+    a = rr.CorrBlock(f1, f2, radius=4, precision="fp32")(coords)
+    b = rr.AlternateCorrBlock(f1, f2, radius=4)(coords)
+    assert a.shape == b.shape == (B, 324, h, w)
+    assert relmax(n(b), n(a)) <= 5e-6
+
+
+# ----------------------------------------------------------------------------- bilinear_sampler
+def test_bilinear_sampler_vs_grid_sample(rr):
+    g = torch.Generator(device="cpu").manual_seed(3)
+    img = torch.randn(5, 3, 11, 17, generator=g).to(DEV).requires_grad_(True)
+    coords = (torch.rand(5, 9, 9, 2, generator=g) * torch.tensor([20.0, 14.0]) - 2.0).to(DEV)
+    out, mask = rr.bilinear_sampler(img, coords, mask=True)
+    H, W = 11, 17
+    grid = torch.stack([2 * coords[..., 0] / (W - 1) - 1, 2 * coords[..., 1] / (H - 1) - 1], -1)
+    ref = torch.nn.functional.grid_sample(img.detach(), grid, align_corners=True)
+    assert relmax(n(out), n(ref)) <= 5e-6
+    refmask = ((grid[..., :1] > -1) & (grid[..., 1:] > -1) & (grid[..., :1] < 1) & (grid[..., 1:] < 1)).float()
+    assert mask.shape == refmask.shape and (mask != refmask).float().mean().item() < 0.01
+    go = torch.randn(out.shape, generator=g).to(DEV)
+    out.backward(go)
+    img2 = img.detach().clone().requires_grad_(True)
+    torch.nn.functional.grid_sample(img2, grid, align_corners=True).backward(go)
+    assert relmax(n(img.grad), n(img2.grad)) <= 1e-5
+
+
+# ----------------------------------------------------------------------------- full-size properties
+FULL = [(1, 256, 55, 128), (1, 256, 47, 156), (1, 256, 50, 90)]
+
+
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("shape", FULL)
+def test_full_size_properties(rr, shape, precision):
+    """BASELINE.json shapes: volume vs an fp32 torch contraction (TF32 off), pooling consistency,
+    transpose symmetry, lookup identities.  The oracle is too slow here; these are its
+    size-independent consequences."""
+    B, D, h, w = shape
+    N = h * w
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    f2 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    blk = rr.CorrBlock(f1, f2, num_levels=4, radius=4, precision=precision)
+    ref0 = (torch.matmul(f1.view(B, D, N).double().transpose(1, 2), f2.view(B, D, N).double()) / 16.0).float()
+    tol = BUILD_TOL[precision]
+    l0 = blk.corr_pyramid[0].view(B, N, N)
+    err = float((l0 - ref0).abs().max() / ref0.abs().max())
+    nerr = float((l0 - ref0).norm() / ref0.norm())
+    assert err <= tol["rel"] and nerr <= tol["norm"], (err, nerr)
+    # pooling consistency: level l+1 == floor-mode 2x2 mean of level l (core/corr.py:26)
+    for l in range(3):
+        pooled = torch.nn.functional.avg_pool2d(blk.corr_pyramid[l], 2, stride=2)
+        assert tuple(pooled.shape) == tuple(blk.corr_pyramid[l + 1].shape)
+        assert float((pooled - blk.corr_pyramid[l + 1]).abs().max()) <= 2e-6 * float(ref0.abs().max())
+    # transpose symmetry: corr(f1,f2)[p,q] == corr(f2,f1)[q,p]
+    blk_t = rr.CorrBlock(f2, f1, num_levels=1, radius=4, precision=precision)
+    assert torch.equal(blk_t.corr_pyramid[0].view(B, N, N).transpose(1, 2), l0) or \
+        float((blk_t.corr_pyramid[0].view(B, N, N).transpose(1, 2) - l0).abs().max()) <= 2e-6 * float(ref0.abs().max())
+    # lookup at integer coords is a pure gather of level 0 (channel i*9+j <-> (x+i-4, y+j-4))
+    coords = rr.coords_grid(B, h, w, DEV)
+    out = blk(coords)
+    assert out.shape == (B, 324, h, w) and out.dtype == torch.float32 and out.is_contiguous()
+    vol = blk.corr_pyramid[0].view(B, h, w, h, w)
+    for (i, j) in [(4, 4), (0, 0), (8, 8), (2, 7)]:
+        ys = torch.arange(h, device=DEV).view(h, 1).expand(h, w)
+        xs = torch.arange(w, device=DEV).view(1, w).expand(h, w)
+        yy, xx = ys + (j - 4), xs + (i - 4)
+        ok = (yy >= 0) & (yy < h) & (xx >= 0) & (xx < w)
+        want = torch.where(ok, vol[0, ys, xs, yy.clamp(0, h - 1), xx.clamp(0, w - 1)], torch.zeros((), device=DEV))
+        assert torch.equal(out[0, i * 9 + j], want), (i, j)
+    # far out-of-bounds coords give exact zeros; idempotence of repeated lookups
+    far = coords + 10000.0
+    assert not bool(blk(far).any())
+    assert torch.equal(blk(coords), out)
+
+
+# ----------------------------------------------------------------------------- host-side errors
+def test_error_conventions(rr):
+    f = torch.zeros(1, 8, 8, 32, device=DEV)
+    c = torch.zeros(1, 1, 8, 8, 2, device=DEV)
+    with pytest.raises(RuntimeError, match="fmap2 must be contiguous"):
+        rr.alt_cuda_corr.forward(f, f.permute(0, 2, 1, 3), c, 4)
+    with pytest.raises(RuntimeError, match="coords must be a CUDA tensor"):
+        rr.alt_cuda_corr.forward(f, f, c.cpu(), 4)
+    with pytest.raises(RuntimeError, match="empty"):
+        rr.CorrBlock(torch.zeros(1, 32, 4, 64, device=DEV), torch.zeros(1, 32, 4, 64, device=DEV), num_levels=4)
+    blk = rr.CorrBlock(torch.zeros(1, 32, 16, 16, device=DEV), torch.zeros(1, 32, 16, 16, device=DEV), precision="fp32")
+    with pytest.raises(RuntimeError):
+        blk(torch.zeros(1, 2, 8, 8, device=DEV))  # coords grid does not match the pyramid
+    with pytest.raises(RuntimeError, match="radius"):
+        rr.CorrBlock(torch.zeros(1, 32, 16, 16, device=DEV), torch.zeros(1, 32, 16, 16, device=DEV), radius=9, precision="fp32")(
+            torch.zeros(1, 2, 16, 16, device=DEV))
