@@ -33,7 +33,7 @@ def log(*a):
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=8, help="frame pairs per GPU per step")
@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--radius", type=int, default=4)
     ap.add_argument("--precision", default=os.environ.get("RAFT_CORR_PRECISION", "bf16x3"),
                     choices=["fp32", "bf16x3", "bf16"])
+    ap.add_argument("--l2-fetch", type=int, default=int(os.environ.get("RAFT_CORR_L2_FETCH", "0")),
+                    help="set cudaLimitMaxL2FetchGranularity (32/64/128); 0 = leave the driver default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
@@ -73,7 +75,7 @@ def peaks():
 
 # ----------------------------------------------------------------------------- clocks sampler
 class ClockSampler:
-    """Samples SM clock + throttle reasons DURING the timed region (NVML, 50 ms period)."""
+    """Samples SM clock + throttle reasons DURING the timed region (NVML, 10 ms period)."""
 
     def __init__(self, index):
         self.index = index
@@ -113,7 +115,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.01)
 
     def start(self):
         if self.nv is not None:
@@ -224,6 +226,13 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
+
+    if args.l2_fetch:
+        _lib.check(_lib.lib().rc_set_l2_fetch_granularity(args.l2_fetch), "rc_set_l2_fetch_granularity")
+    import ctypes as _ct
+    _g = _ct.c_int(0)
+    _lib.lib().rc_get_l2_fetch_granularity(_ct.byref(_g))
+    l2_fetch = int(_g.value)
 
     B, D, L, r, K = args.batch, args.dim, args.levels, args.radius, args.iters
     h, w = args.height // 8, args.width // 8
@@ -347,6 +356,7 @@ def run_ours(args):
         "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup"}[args.precision],
         "data": "synthetic", "config": workload_config(args, "gpu"), "precision": args.precision,
         "roofline": roofline, "kernels": kern, "clocks": clocks, "gpu_launches": int(args.steps * (2 + K)),
+        "l2_fetch_granularity": l2_fetch,
     }
     if e2e is not None:
         line["e2e"] = e2e

@@ -50,6 +50,17 @@ extern "C" {
 int rc_version(void);
 const char *rc_last_error(void);
 
+/*
+ * Tuning knob, no counterpart in the reference: the L2 fetch granularity of the CURRENT device's
+ * context (cudaLimitMaxL2FetchGranularity; 32, 64 or 128 bytes, the driver default is 64).  The
+ * lookup reads (2r+2)-float row segments (40 B for r=4) scattered over the volume, so a 64 B
+ * granule over-fetches by ~1.5x; 32 B cuts the lookup's DRAM reads.  It is a context-wide hint
+ * that also applies to every other kernel of the process, so the library never sets it by
+ * itself: the host layer does so only when asked (RAFT_CORR_L2_FETCH=32).
+ */
+int rc_set_l2_fetch_granularity(int bytes);
+int rc_get_l2_fetch_granularity(int *bytes);
+
 /* h_l, w_l of level `level` (h>>level, w>>level); RC_ERR_INVALID if it would be empty. */
 int rc_level_dims(int h, int w, int level, int *hl, int *wl);
 

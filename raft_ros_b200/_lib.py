@@ -73,6 +73,8 @@ _sz = ctypes.c_size_t
 SIGNATURES = {
     "rc_version": (_i, []),
     "rc_last_error": (ctypes.c_char_p, []),
+    "rc_set_l2_fetch_granularity": (_i, [_i]),
+    "rc_get_l2_fetch_granularity": (_i, [ctypes.POINTER(_i)]),
     "rc_level_dims": (_i, [_i, _i, _i, ctypes.POINTER(_i), ctypes.POINTER(_i)]),
     "rc_corr_build_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rc_corr_build_pyramid": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),

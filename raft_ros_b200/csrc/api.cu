@@ -41,6 +41,20 @@ int rc_version(void) { return 100; }
 
 const char *rc_last_error(void) { return g_err; }
 
+int rc_set_l2_fetch_granularity(int bytes) {
+  RC_CHECK_ARG(bytes == 32 || bytes == 64 || bytes == 128, "rc_set_l2_fetch_granularity: bytes must be 32, 64 or 128");
+  RC_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
+  return RC_OK;
+}
+
+int rc_get_l2_fetch_granularity(int *bytes) {
+  RC_CHECK_ARG(bytes != nullptr, "rc_get_l2_fetch_granularity: null output");
+  size_t v = 0;
+  RC_CUDA(cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity));
+  *bytes = (int)v;
+  return RC_OK;
+}
+
 int rc_level_dims(int h, int w, int level, int *hl, int *wl) {
   RC_CHECK_ARG(hl && wl, "rc_level_dims: null output");
   RC_CHECK_ARG(level >= 0 && level < RC_MAX_LEVELS && h > 0 && w > 0, "rc_level_dims: bad arguments");

@@ -9,15 +9,16 @@
 // Data flow
 //   prep kernel : fmap (B,D,h,w) fp32 NCHW -> (B,h,w,Dp) bf16 K-major "hi" (+ "lo" residual
 //                 for RC_PREC_BF16X3: x ~= hi + lo, 16 mantissa bits), Dp = D rounded up to 64.
-//   main kernel : persistent, one CTA per SM, 6 warps:
-//                   warp 0  TMA producer  (A: 128 query pixels x 64 ch; B: an 8x32 SPATIAL patch
+//   main kernel : persistent, one CTA per SM, 10 warps:
+//                   warp 8  TMA producer  (A: 128 query pixels x 64 ch; B: an 8x32 SPATIAL patch
 //                           of fmap2 x 64 ch via a 4-D box, so the 256 columns of a tile are a
 //                           spatial patch and every 2x2/4x4/8x8 pooling window is tile-local)
-//                   warp 1  MMA issuer    (tcgen05.mma 128x256x16, bf16 -> fp32 in TMEM; BF16X3
+//                   warp 9  MMA issuer    (tcgen05.mma 128x256x16, bf16 -> fp32 in TMEM; BF16X3
 //                           issues hi*hi + hi*lo + lo*hi into the same accumulator)
-//                   warps 2-5 epilogue    (tcgen05.ld one spatial row pair at a time; thread <->
-//                           query pixel so all pooling is in registers; rows are transposed
-//                           through a per-warp padded smem tile and written as 128 B lines)
+//                   warps 0-7 epilogue    (warp = TMEM lane quarter x upper/lower half of the patch;
+//                           tcgen05.ld one spatial row pair at a time; thread <-> query pixel so
+//                           all pooling is in registers; rows are transposed through a swizzled
+//                           per-warp smem buffer and written with st.global.v4, 512 B/instruction)
 //                 TMEM holds two 128x256 fp32 accumulators (all 512 columns): the MMAs of tile
 //                 i+1 overlap the epilogue of tile i.
 #include <cuda.h>
@@ -39,9 +40,11 @@ constexpr int TK = 64;         // channels per stage: 128 B rows, SWIZZLE_128B
 constexpr int UK = 16;         // K of one tcgen05.mma (bf16)
 constexpr int A_BYTES = TM * TK * 2;
 constexpr int B_BYTES = TN * TK * 2;
-constexpr int kThreads = 192;
-constexpr int kEpiWarps = 4;
-constexpr int kStageFloats = 32 * 33;  // per-warp transposition tile
+constexpr int kEpiWarps = 8;           // warps 0..7
+constexpr int kProducerWarp = 8;
+constexpr int kMmaWarp = 9;
+constexpr int kThreads = 320;
+constexpr int kStgBytesPerWarp = 4096;  // one 32x32 fp32 transposition buffer per epilogue warp
 constexpr int kTmemCols = 512;
 
 struct Params {
@@ -50,6 +53,7 @@ struct Params {
   int m_tiles, nt_x, nt_y;      // tiles along query pixels / patch grid
   long long total_tiles;
   float scale;
+  int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
   LevelPtrs lv;
 };
 
@@ -75,12 +79,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
       "@p bra WAIT_DONE;\n\t"
       "bra WAIT_LOOP;\n\t"
       "WAIT_DONE:\n\t"
       "}" ::"r"(smem_u32(bar)),
-      "r"(parity)
+      "r"(parity), "r"(0x989680u) /* suspend-time hint: sleep in hardware instead of spinning */
       : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1,
@@ -153,34 +157,97 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=256
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
+// ---- small shared / global access helpers (explicit state spaces: no generic addressing)
+__device__ __forceinline__ void sts128(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, float x) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(x) : "memory");
+}
+__device__ __forceinline__ float lds32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void stg128(float *p, float4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void stg64(float *p, float x, float y) {
+  asm volatile("st.global.L1::no_allocate.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t *u = reinterpret_cast<uint32_t *>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+        "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 template <int NPASS>
 struct Cfg {
   static constexpr int kOps = (NPASS == 3) ? 2 : 1;          // hi (+ lo)
   static constexpr int kStageBytes = kOps * (A_BYTES + B_BYTES);
   static constexpr int kStages = (NPASS == 3) ? 2 : 4;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes +
-                                    kEpiWarps * kStageFloats * 4 + 256 /*barriers*/;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kEpiWarps * kStgBytesPerWarp +
+                                    256 /*barriers*/;
 };
 
-// write one transposed chunk: this warp's 32 rows x NC floats, staged [row][NC+1], as
-// (32/NC... ) contiguous segments of NC floats per row
+// Write this warp's 32 rows x NC columns (thread <-> row, NC values in registers) to global
+// memory as contiguous NC-float row segments.  The rows are transposed through a 2 KB
+// shared-memory buffer so that a store instruction covers whole segments:
+//   VEC path  (16 B aligned rows): 16 B chunks, XOR-swizzled so that both the row-wise writes and
+//             the segment-wise reads are bank-conflict free; st.global.v4, 512 B per instruction.
+//   scalar path (ragged widths): same idea with 4 B elements.
 template <int NC>
-__device__ __forceinline__ void store_chunk(float *stg, const float *vals, int lane, float *__restrict__ gbase,
-                                            size_t row_pitch, int rows_valid, int cols_valid) {
-  constexpr int S = NC + 1;
-  constexpr int RPI = 32 / NC;  // rows per store instruction
+__device__ __forceinline__ void store_rows(uint32_t buf, const float *v, int lane, float *__restrict__ g,
+                                           size_t pitch, int rows_valid, int cols_valid, bool vec) {
+  static_assert(NC == 32 || NC == 16 || NC == 8, "segment width");
+  constexpr int CH = NC / 4;          // 16 B chunks per row
+  constexpr int RPI = 32 / CH;        // rows per vector store instruction
+  constexpr int SH = (NC == 32) ? 0 : (NC == 16) ? 1 : 2;  // log2(rows per 128 B of the buffer)
+  if (vec) {
 #pragma unroll
-  for (int i = 0; i < NC; ++i) stg[lane * S + i] = vals[i];
-  __syncwarp();
-  const int rsub = lane / NC, c = lane - rsub * NC;
-  if (c < cols_valid) {
-#pragma unroll 8
-    for (int rr = 0; rr < 32; rr += RPI) {
-      const int r = rr + rsub;
-      if (r < rows_valid) st_stream(gbase + (size_t)r * row_pitch + c, stg[r * S + c]);
+    for (int c = 0; c < CH; ++c)
+      sts128(buf + lane * (NC * 4) + (((c ^ ((lane >> SH) & (CH - 1)))) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2],
+             v[4 * c + 3]);
+    __syncwarp();
+    const int rsub = lane / CH, c = lane % CH;
+    float *gp = g + (size_t)rsub * pitch + 4 * c;
+    const bool cok = 4 * c < cols_valid;
+#pragma unroll
+    for (int i = 0; i < 32 / RPI; ++i) {
+      const int row = i * RPI + rsub;
+      const float4 val = lds128(buf + row * (NC * 4) + (((c ^ ((row >> SH) & (CH - 1)))) << 4));
+      if (cok && row < rows_valid) stg128(gp, val);
+      gp += (size_t)RPI * pitch;
     }
+    __syncwarp();
+  } else {
+#pragma unroll
+    for (int i = 0; i < NC; ++i) sts32(buf + ((lane * NC + (i ^ ((lane ^ (lane >> 3)) & (NC - 1)))) << 2), v[i]);
+    __syncwarp();
+    constexpr int RPS = 32 / NC;  // rows per scalar store instruction
+    const int rsub = lane / NC, c = lane % NC;
+    float *gp = g + (size_t)rsub * pitch + c;
+    const bool cok = c < cols_valid;
+#pragma unroll 8
+    for (int i = 0; i < 32 / RPS; ++i) {
+      const int row = i * RPS + rsub;
+      const float val = lds32(buf + ((row * NC + (c ^ ((row ^ (row >> 3)) & (NC - 1)))) << 2));
+      if (cok && row < rows_valid) st_stream(gp, val);
+      gp += (size_t)RPS * pitch;
+    }
+    __syncwarp();
   }
-  __syncwarp();
 }
 
 template <int NPASS>
@@ -190,10 +257,13 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 const Params P) {
   using C = Cfg<NPASS>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024 B alignment (SWIZZLE_128B atoms) by offsetting inside the shared window
+  const uint32_t raw_u32 = smem_u32(smem_raw);
+  const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
+  uint8_t *smem = smem_raw + (base_u32 - raw_u32);
   uint8_t *stage_base = smem;
-  float *stg_all = reinterpret_cast<float *>(smem + C::kStages * C::kStageBytes);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(stg_all + kEpiWarps * kStageFloats);
+  const uint32_t stg_u32 = base_u32 + C::kStages * C::kStageBytes;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + C::kStages * C::kStageBytes + kEpiWarps * kStgBytesPerWarp);
   uint64_t *full = bars;                       // [kStages]
   uint64_t *empty = bars + C::kStages;         // [kStages]
   uint64_t *tfull = bars + 2 * C::kStages;     // [2]
@@ -202,7 +272,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == kProducerWarp && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
@@ -219,7 +289,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       prefetch_tmap(&tmB_lo);
     }
   }
-  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -228,7 +298,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
   const long long tiles_per_item = (long long)P.m_tiles * P.nt_x * P.nt_y;
   const int nt = P.nt_x * P.nt_y;
 
-  if (warp == 0) {
+  if (warp == kProducerWarp) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0;
@@ -252,7 +322,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       int stage = 0;
@@ -266,7 +336,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         for (int kb = 0; kb < P.k_blocks; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(stage_base + stage * C::kStageBytes);
+          const uint32_t sa = base_u32 + stage * C::kStageBytes;
           const uint64_t a_hi = make_sw128_desc(sa);
           const uint64_t b_hi = make_sw128_desc(sa + C::kOps * A_BYTES);
           const uint64_t a_lo = make_sw128_desc(sa + A_BYTES);
@@ -289,20 +359,21 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       }
     }
   } else {
-    // ===================== epilogue (4 warps, thread <-> query pixel) =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    float *stg = stg_all + (warp - 2) * kStageFloats;
+    // ===================== epilogue: 8 warps =====================
+    // warp e: TMEM lane quarter q = e & 3 (32 query pixels, thread <-> pixel) and row half
+    // hf = e >> 2 (spatial rows 0-3 / 4-7 of the 8x32 patch).  Pooling up to level 2 is in
+    // registers; the two halves meet once per tile for the single level-3 row.
+    const int q = warp & 3, hf = warp >> 2;
+    const uint32_t buf = stg_u32 + warp * kStgBytesPerWarp;
+    const uint32_t buf_peer = stg_u32 + (warp | 4) * kStgBytesPerWarp;  // hf=1 warp of this quarter
+    const int bar_full = 1 + q, bar_free = 5 + q;                       // named barriers of the pair
     int acc = 0;
     uint32_t acc_phase = 0;
     const int h = P.h, w = P.w, N = P.N, L = P.L;
-    const size_t pitch0 = (size_t)h * w;
-    const size_t pitch1 = (size_t)(h >> 1) * (w >> 1);
-    const size_t pitch2 = (size_t)(h >> 2) * (w >> 2);
-    const size_t pitch3 = (size_t)(h >> 3) * (w >> 3);
-    float *const lv0 = P.lv.p[0];
-    float *const lv1 = P.lv.p[1];
-    float *const lv2 = P.lv.p[2];
-    float *const lv3 = P.lv.p[3];
+    const int h1 = h >> 1, w1 = w >> 1, h2 = h >> 2, w2 = w >> 2, h3 = h >> 3, w3 = w >> 3;
+    const size_t pitch0 = (size_t)h * w, pitch1 = (size_t)h1 * w1, pitch2 = (size_t)h2 * w2, pitch3 = (size_t)h3 * w3;
+    const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;
+    bool peer_pending = false;  // hf=1: our staging buffer still holds the level-2 row for the peer
     for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
       const int b = (int)(t / tiles_per_item);
       const int rem = (int)(t - (long long)b * tiles_per_item);
@@ -310,18 +381,28 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const int ny = n / P.nt_x, nx = n - ny * P.nt_x;
       const int prow0 = m * TM + q * 32;                 // first query pixel of this warp
       const int rows_valid = min(32, N - prow0);         // may be <= 0
-      const size_t grow0 = (size_t)b * N + prow0;        // global row of the volume
+      const size_t grow0 = (size_t)b * N + prow0;        // first row of the volume for this warp
+      const int x0 = nx * PW;
+      float *const g0 = P.lv.p[0] + grow0 * pitch0 + x0;
+      float *const g1 = P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
+      float *const g2 = P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
+      float *const g3 = P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN);
-      float l1prev[16], l2prev[8];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN + hf * (TN / 2));
+      if (L > 3 && hf == 1 && peer_pending) {
+        // the peer must have read last tile's level-2 row before this buffer is reused
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_free) : "memory");
+        peer_pending = false;
+      }
+      float l1prev[16], l2[8];
 #pragma unroll
-      for (int j = 0; j < PH / 2; ++j) {
+      for (int j = 0; j < 2; ++j) {
         float v0[32], v1[32];
-        tmem_ld32(taddr + j * 64, v0);
-        tmem_ld32(taddr + j * 64 + 32, v1);
+        tmem_ld32(taddr + (2 * j) * PW, v0);
+        tmem_ld32(taddr + (2 * j + 1) * PW, v1);
         tmem_ld_wait();
-        if (j == PH / 2 - 1) {
+        if (j == 1) {
           // all TMEM reads of this tile are done: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -332,11 +413,9 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           v0[i] *= P.scale;
           v1[i] *= P.scale;
         }
-        const int y0 = ny * PH + 2 * j, x0 = nx * PW;
-        if (y0 < h)
-          store_chunk<32>(stg, v0, lane, lv0 + grow0 * pitch0 + (size_t)y0 * w + x0, pitch0, rows_valid, w - x0);
-        if (y0 + 1 < h)
-          store_chunk<32>(stg, v1, lane, lv0 + grow0 * pitch0 + (size_t)(y0 + 1) * w + x0, pitch0, rows_valid, w - x0);
+        const int y0 = ny * PH + hf * 4 + 2 * j;
+        if (y0 < h) store_rows<32>(buf, v0, lane, g0 + (size_t)y0 * w, pitch0, rows_valid, w - x0, vec0);
+        if (y0 + 1 < h) store_rows<32>(buf, v1, lane, g0 + (size_t)(y0 + 1) * w, pitch0, rows_valid, w - x0, vec0);
         if (L > 1) {
           float l1[16];
 #pragma unroll
@@ -346,15 +425,13 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             s += v1[2 * i + 1];
             l1[i] = s * 0.25f;
           }
-          const int h1 = h >> 1, w1 = w >> 1, y1 = ny * (PH / 2) + j, x1 = nx * (PW / 2);
-          if (y1 < h1)
-            store_chunk<16>(stg, l1, lane, lv1 + grow0 * pitch1 + (size_t)y1 * w1 + x1, pitch1, rows_valid, w1 - x1);
+          const int y1 = ny * (PH / 2) + hf * 2 + j;
+          if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
           if (L > 2) {
-            if ((j & 1) == 0) {
+            if (j == 0) {
 #pragma unroll
               for (int i = 0; i < 16; ++i) l1prev[i] = l1[i];
             } else {
-              float l2[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 float s = l1prev[2 * i] + l1prev[2 * i + 1];
@@ -362,27 +439,42 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 s += l1[2 * i + 1];
                 l2[i] = s * 0.25f;
               }
-              const int h2 = h >> 2, w2 = w >> 2, y2 = ny * (PH / 4) + (j >> 1), x2 = nx * (PW / 4);
-              if (y2 < h2)
-                store_chunk<8>(stg, l2, lane, lv2 + grow0 * pitch2 + (size_t)y2 * w2 + x2, pitch2, rows_valid, w2 - x2);
-              if (L > 3) {
-                if (j == 1) {
+              const int y2 = ny * (PH / 4) + hf;
+              if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
+            }
+          }
+        }
+      }
+      if (L > 3) {
+        if (hf == 1) {
+          // publish this half's level-2 row (8 floats per query pixel) through our staging buffer
+          sts128(buf + lane * 32, l2[0], l2[1], l2[2], l2[3]);
+          sts128(buf + lane * 32 + 16, l2[4], l2[5], l2[6], l2[7]);
+          __threadfence_block();
+          asm volatile("bar.arrive %0, 64;" ::"r"(bar_full) : "memory");
+          peer_pending = true;
+        } else {
+          asm volatile("bar.sync %0, 64;" ::"r"(bar_full) : "memory");
+          const float4 pa = lds128(buf_peer + lane * 32), pb = lds128(buf_peer + lane * 32 + 16);
+          asm volatile("bar.arrive %0, 64;" ::"r"(bar_free) : "memory");
+          const float lo[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
+          float l3[4];
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) l2prev[i] = l2[i];
-                } else {
-                  float l3[4];
+          for (int i = 0; i < 4; ++i) {
+            float s = l2[2 * i] + l2[2 * i + 1];
+            s += lo[2 * i];
+            s += lo[2 * i + 1];
+            l3[i] = s * 0.25f;
+          }
+          const int cv3 = w3 - (x0 >> 3);
+          if (ny < h3 && lane < rows_valid) {
+            float *d = g3 + (size_t)ny * w3;
+            if (vec3 && cv3 >= 4) {
+              stg128(d, make_float4(l3[0], l3[1], l3[2], l3[3]));
+            } else {
 #pragma unroll
-                  for (int i = 0; i < 4; ++i) {
-                    float s = l2prev[2 * i] + l2prev[2 * i + 1];
-                    s += l2[2 * i];
-                    s += l2[2 * i + 1];
-                    l3[i] = s * 0.25f;
-                  }
-                  const int h3 = h >> 3, w3 = w >> 3, y3 = ny, x3 = nx * (PW / 8);
-                  if (y3 < h3)
-                    store_chunk<4>(stg, l3, lane, lv3 + grow0 * pitch3 + (size_t)y3 * w3 + x3, pitch3, rows_valid, w3 - x3);
-                }
-              }
+              for (int i = 0; i < 4; ++i)
+                if (i < cv3) st_stream(d + i, l3[i]);
             }
           }
         }
@@ -390,12 +482,13 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (L > 3 && hf == 1 && peer_pending) asm volatile("bar.sync %0, 64;" ::"r"(bar_free) : "memory");
   }
 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 // ------------------------------------------------------------------ prep: NCHW fp32 -> NHWC bf16 hi/lo
@@ -547,6 +640,12 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   P.total_tiles = (long long)B * P.m_tiles * P.nt_x * P.nt_y;
   P.scale = scale;
   P.lv = lv;
+  P.vec_mask = 0;
+  for (int l = 0; l < 4 && l < L; ++l) {
+    const int wl = w >> l;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(lv.p[l]);
+    if (wl % 4 == 0 && (a & 15) == 0) P.vec_mask |= 1 << l;
+  }
   for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
 
   int rc = x3 ? tc::launch<3>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1>(tmAh, tmAl, tmBh, tmBl, P, st);

@@ -7,7 +7,11 @@ normwise, never element-wise relative):
   fp32 build          relmax <= 3e-6   (fp32 FMA vs the reference's SGEMM / double oracle)
   bf16x3 build        relmax <= 1e-4, normwise <= 3e-5   (the "<=1e-4" fp32-class bound)
   bf16 build          normwise <= 6e-3 (single-pass bf16 operands, 8-bit mantissa)
-  lookup (same pyramid) relmax <= 5e-6 (pixel-space sampling vs grid_sample's round trip)
+  lookup (same pyramid) relmax <= 2e-5: fp32 coordinate rounding.  The reference (and the oracle)
+                      form each tap's coordinate as fl(x + k) and grid_sample round-trips it through
+                      [-1,1], which moves it by up to ~2^-23 * |coord| (1.5e-5 px at |coord| = 128);
+                      the kernel uses one exact fraction for the whole window.  The result is
+                      continuous in the coordinate, so the effect is that shift times the local slope.
 """
 import os
 
@@ -25,6 +29,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 BUILD_TOL = {"fp32": dict(rel=3e-6, norm=2e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
 PRECISIONS = ["fp32", "bf16x3", "bf16"]
+LOOKUP_TOL = 2e-5
 
 
 @pytest.fixture(scope="module")
@@ -88,10 +93,10 @@ def test_golden_lookup_on_reference_pyramid(rr, golden_dir, name):
         out = lookup_raw(levels, t(z[f"coords_{kind}"]), r)
         ref = z[f"out_{kind}"]
         assert tuple(out.shape) == ref.shape and out.dtype == torch.float32 and out.is_contiguous()
-        assert relmax(n(out), ref) <= 5e-6, (name, kind)
-        # and bit-for-layout against the oracle in the same (pixel-space) arithmetic
+        assert relmax(n(out), ref) <= LOOKUP_TOL, (name, kind)
+        # and against the oracle in the same (pixel-space) arithmetic
         orc = O.corr_lookup([z[f"level{l}"] for l in range(L)], z[f"coords_{kind}"], r, roundtrip=False)
-        assert relmax(n(out), orc) <= 1e-6, (name, kind)
+        assert relmax(n(out), orc) <= LOOKUP_TOL, (name, kind)
 
 
 @pytest.mark.parametrize("name", GOLDEN)
@@ -105,7 +110,7 @@ def test_golden_end_to_end_and_backward(rr, golden_dir, name):
     total = None
     for kind in _kinds(z):
         out = blk(t(z[f"coords_{kind}"]))
-        assert relmax(n(out), z[f"out_{kind}"]) <= 8e-6, (name, kind)
+        assert relmax(n(out), z[f"out_{kind}"]) <= LOOKUP_TOL, (name, kind)
         g = t(cotangent(name, kind, z[f"out_{kind}"].shape))
         total = (out * g).sum() if total is None else total + (out * g).sum()
     total.backward()
@@ -154,7 +159,7 @@ def test_lookup_vs_oracle(rr, shape, kind):
     want = O.corr_lookup(levels, coords, r)
     got = n(lookup_raw([t(lv) for lv in levels], t(coords), r))
     assert got.shape == want.shape
-    assert relmax(got, want) <= 1e-6, (shape, kind)
+    assert relmax(got, want) <= LOOKUP_TOL, (shape, kind, relmax(got, want))
     if kind == "huge":
         assert np.isfinite(got).all()
 
@@ -317,3 +322,40 @@ def test_error_conventions(rr):
     with pytest.raises(RuntimeError, match="radius"):
         rr.CorrBlock(torch.zeros(1, 32, 16, 16, device=DEV), torch.zeros(1, 32, 16, 16, device=DEV), radius=9, precision="fp32")(
             torch.zeros(1, 2, 16, 16, device=DEV))
+
+
+# ----------------------------------------------------------------------------- the reference's own binary
+def _ref_ext():
+    from oracle import build_ref
+    try:
+        return build_ref.load_module()
+    except Exception:  # built for another torch ABI, etc.
+        return None
+
+
+@pytest.mark.parametrize("shape", ALT_SHAPES[:3])
+def test_alt_vs_reference_binary(rr, shape):
+    """rc_alt_corr_fwd/bwd against the reference's UNMODIFIED alt_cuda_corr extension
+    (oracle/_ref/, compiled from the reference's sources by oracle/build_ref.py).  C must be a
+    multiple of 32 for the reference kernel; H1/W1 multiples of the reference's 4x8 block avoid
+    its out-of-bounds coordinate read in the backward (correlation_kernel.cu:178-179)."""
+    ext = _ref_ext()
+    if ext is None:
+        pytest.skip("oracle/_ref/alt_cuda_corr_ref.so not present")
+    B, N, H1, W1, H2, W2, C, r = shape
+    H1, W1 = (H1 + 3) // 4 * 4, (W1 + 7) // 8 * 8
+    g = torch.Generator(device="cpu").manual_seed(seed_of(shape))
+    f1 = torch.randn(B, H1, W1, C, generator=g).to(DEV)
+    f2 = torch.randn(B, H2, W2, C, generator=g).to(DEV)
+    coords = (torch.rand(B, N, H1, W1, 2, generator=g) * torch.tensor([W2 + 6.0, H2 + 6.0]) - 3.0).to(DEV)
+    (want,) = ext.forward(f1, f2, coords, r)
+    (got,) = rr.alt_cuda_corr.forward(f1, f2, coords, r)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape
+    assert relmax(n(got), n(want)) <= 5e-6
+    cg = torch.randn(want.shape, generator=g).to(DEV)
+    w1, w2, wc = ext.backward(f1, f2, coords, cg, r)
+    g1, g2, gc = rr.alt_cuda_corr.backward(f1, f2, coords, cg, r)
+    torch.cuda.synchronize()
+    assert relmax(n(g1), n(w1)) <= 1e-5 and relmax(n(g2), n(w2)) <= 1e-5
+    assert not bool(wc.any()) and not bool(gc.any())
