@@ -82,6 +82,31 @@ int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, 
                           void *workspace, size_t workspace_bytes, void *stream);
 
 /*
+ * rc_corr_build_pyramid without a caller workspace and without any allocation.
+ * No counterpart in the reference (its build is torch.matmul; torch allocates as it likes).
+ * It exists for hosts that may not allocate device memory while running: a real-time inference
+ * loop (the ROS node's worker thread) that cannot take cudaMalloc's unbounded latency and its
+ * device-wide synchronisation, or a process whose whole device memory already belongs to
+ * another pool, where cudaMalloc would fail.  The scratch is a fixed array inside the library
+ * image: each GPU that loads libraftcorr.so holds RC_STATIC_SCRATCH_BYTES until exit.
+ *   - only the tensor-core precisions (RC_PREC_BF16X3, RC_PREC_BF16); RC_PREC_FP32 needs no
+ *     scratch and is served by rc_corr_build_pyramid;
+ *   - a problem whose rc_corr_build_workspace_bytes(...) exceeds RC_STATIC_SCRATCH_BYTES is
+ *     rejected with RC_ERR_WORKSPACE and nothing is launched (32 MiB covers two 440x1024 pairs in
+ *     BF16X3, four in BF16);
+ *   - the first call on a device looks up the array's device address; issue that first call
+ *     before beginning any stream capture on that device;
+ *   - every call on a device uses the same array and finds the previous call's contents in it.
+ *     Nothing must be cleared: each call rewrites all it reads.  Calls that overlap on the GPU
+ *     race on the array; order them (same stream, or an event between streams).
+ * Inputs, outputs, return codes: exactly as rc_corr_build_pyramid.
+ */
+#define RC_STATIC_SCRATCH_BYTES (32u << 20)
+int rc_corr_build_pyramid_noalloc(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
+                                  float *const *level_ptrs, int num_levels, int precision, float scale,
+                                  void *stream);
+
+/*
  * CorrBlock.__call__: the (2r+1)^2 bilinear window of every level around coords / 2^l.
  * Replaces: core/corr.py:29-50 and, through it, core/utils/utils.py:57-71
  * (bilinear_sampler -> F.grid_sample bilinear, zeros padding, align_corners=True).

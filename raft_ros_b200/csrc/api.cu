@@ -95,6 +95,27 @@ int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, 
   }
 }
 
+// Allocation-free build: same contract as rc_corr_build_pyramid, scratch inside the library image
+// (see the block comment in build_tc.cu and include/raftcorr.h).  Calls no allocating routine.
+int rc_corr_build_pyramid_noalloc(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
+                                  float *const *level_ptrs, int num_levels, int precision, float scale,
+                                  void *stream) {
+  if (int rc = check_geometry("rc_corr_build_pyramid_noalloc", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && level_ptrs, "rc_corr_build_pyramid_noalloc: null pointer");
+  RC_CHECK_ARG(D > 0, "rc_corr_build_pyramid_noalloc: D must be positive");
+  RC_CHECK_ARG(precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16,
+               "rc_corr_build_pyramid_noalloc: only RC_PREC_BF16X3 / RC_PREC_BF16 use scratch; "
+               "RC_PREC_FP32 goes through rc_corr_build_pyramid");
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_build_pyramid_noalloc: level %d pointer is null", l);
+    lv.p[l] = level_ptrs[l];
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  return launch_build_tc_noalloc(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale,
+                                 static_cast<cudaStream_t>(stream));
+}
+
 int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
                        int h, int w, int num_levels, int radius, void *stream) {
   if (int rc = check_geometry("rc_corr_lookup_fwd", B, h, w, num_levels)) return rc;

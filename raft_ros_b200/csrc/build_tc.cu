@@ -654,4 +654,71 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   return RC_OK;
 }
 
+// =====================================================================================
+// Allocation-free variant of the tensor-core build (no counterpart in the reference).
+//
+// Some hosts of this library must not allocate device memory while they run: a real-time
+// inference loop such as the ROS node's worker thread cannot afford cudaMalloc's unbounded
+// latency and implicit device-wide synchronisation, and a process whose device memory has been
+// handed over in full to another pool (a framework's caching allocator, a pre-partitioned
+// embedded budget) would simply see cudaMalloc fail.  For them the scratch that
+// rc_corr_build_pyramid normally receives from the caller lives in the fixed array below, which
+// is part of the library image: every GPU that loads libraftcorr.so holds these
+// RC_STATIC_SCRATCH_BYTES until the process exits, whether or not this entry point is used.
+//
+// Rules of use (also in include/raftcorr.h):
+//  * sizes whose scratch need exceeds RC_STATIC_SCRATCH_BYTES are rejected, nothing is launched;
+//  * the first call on each device resolves the device address of the array (one
+//    cudaGetSymbolAddress with that device current); make that first call before any stream
+//    capture is begun on that device;
+//  * all calls on one device share the one array and it keeps whatever the previous call left.
+//    Nothing in it has to start at zero: the layout prepass rewrites every byte the main kernel
+//    reads (channel padding included) before it is read.  Two calls that overlap on the GPU
+//    (different streams, no dependency) race on it: keep them ordered.
+// =====================================================================================
+static __device__ __align__(256) unsigned char g_static_scratch[RC_STATIC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_scratch_mu;
+void *g_scratch_addr[64] = {};  // per device ordinal; filled lazily, never freed
+}  // namespace
+
+// In host code `g_static_scratch` is only a handle for the symbol, not a device address: the
+// address a kernel can use has to be asked for, per device.
+static int static_scratch_ptr(void **out) {
+  int dev = -1;
+  RC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("rc_corr_build_pyramid_noalloc: device ordinal %d not supported", dev);
+    return RC_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_scratch_mu);
+  if (g_scratch_addr[dev] == nullptr) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+    if (p == nullptr) {
+      set_error("rc_corr_build_pyramid_noalloc: static scratch has no device address");
+      return RC_ERR_CUDA;
+    }
+    g_scratch_addr[dev] = p;
+  }
+  *out = g_scratch_addr[dev];
+  return RC_OK;
+}
+
+int launch_build_tc_noalloc(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv,
+                            int L, int precision, float scale, cudaStream_t st) {
+  const size_t need = build_tc_workspace_bytes(B, D, h, w, precision);
+  if (need == 0 || need > (size_t)RC_STATIC_SCRATCH_BYTES) {
+    set_error("rc_corr_build_pyramid_noalloc: this problem needs %zu bytes of scratch but the built-in scratch "
+              "holds %zu; use rc_corr_build_pyramid with a caller-provided workspace",
+              need, (size_t)RC_STATIC_SCRATCH_BYTES);
+    return RC_ERR_WORKSPACE;
+  }
+  void *ws = nullptr;
+  if (int rc = static_scratch_ptr(&ws)) return rc;
+  return launch_build_tc(f1, f2, B, D, h, w, lv, L, precision, scale, ws, (size_t)RC_STATIC_SCRATCH_BYTES, st);
+}
+
 }  // namespace rc

@@ -1,0 +1,114 @@
+"""rc_corr_build_pyramid_noalloc: the build for hosts that must not allocate device memory
+while running (a real-time inference loop such as the ROS node's worker thread, where
+cudaMalloc's latency and device-wide synchronisation are not acceptable, or a process whose
+device memory is already owned in full by another pool, where cudaMalloc would fail).
+
+Its scratch is a fixed 32 MiB array inside libraftcorr.so instead of a caller workspace.  The
+test drives the entry point through the C ABI (ctypes, raw device pointers) and checks it against
+the ordinary entry point, rc_corr_build_pyramid, on two calls in a row: the second call uses a
+different shape and precision, so anything left in the shared scratch by the first call would show
+up if it were ever read.  The file name keeps it last in pytest's collection order.
+"""
+import ctypes
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+PREC = {"bf16x3": 1, "bf16": 2}
+TOL = {"bf16x3": 1e-4, "bf16": 3e-2}  # same bounds as tests/test_gpu_parity.py::BUILD_TOL (relmax)
+RC_ERR_INVALID, RC_ERR_WORKSPACE = 1, 4
+STATIC_BYTES = 32 << 20
+
+
+@pytest.fixture(scope="module")
+def L():
+    from raft_ros_b200 import _lib
+    _lib.build()
+    assert torch.cuda.is_available()
+    return _lib.lib()
+
+
+def _levels(B, h, w, nl):
+    return [torch.empty(B * h * w, 1, h >> l, w >> l, device=DEV) for l in range(nl)]
+
+
+def _ptrs(ts):
+    from raft_ros_b200 import _lib
+    return _lib.ptr_array([t.data_ptr() for t in ts])
+
+
+def _build_with_workspace(L, f1, f2, nl, prec):
+    B, D, h, w = f1.shape
+    out = _levels(B, h, w, nl)
+    nbytes = int(L.rc_corr_build_workspace_bytes(B, D, h, w, PREC[prec]))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    rc = L.rc_corr_build_pyramid(f1.data_ptr(), f2.data_ptr(), B, D, h, w, _ptrs(out), nl, PREC[prec], 0.0,
+                                 ws.data_ptr(), nbytes, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L.rc_last_error()
+    torch.cuda.synchronize()
+    return out
+
+
+def _build_noalloc(L, f1, f2, nl, prec):
+    B, D, h, w = f1.shape
+    out = _levels(B, h, w, nl)
+    for t in out:
+        t.fill_(float("nan"))  # every element must be overwritten
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    rc = L.rc_corr_build_pyramid_noalloc(f1.data_ptr(), f2.data_ptr(), B, D, h, w, _ptrs(out), nl, PREC[prec], 0.0,
+                                         torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L.rc_last_error()
+    torch.cuda.synchronize()
+    # device memory in use, sampled around the call alone (all tensors above already exist)
+    return out, free0 - torch.cuda.mem_get_info()[0]
+
+
+def _relmax(a, b):
+    return float((a - b).abs().max() / b.abs().max())
+
+
+def test_noalloc_matches_workspace_entry_point_twice_in_a_row(L):
+    g = torch.Generator(device="cpu").manual_seed(2024)
+    calls = [
+        ((1, 256, 55, 128), 4, "bf16x3"),   # the 440x1024 geometry: 14.4 MB of the 32 MiB
+        ((2, 96, 23, 39), 3, "bf16"),       # smaller, ragged, other precision, right after
+    ]
+    first = True
+    for shape, nl, prec in calls:
+        f1 = torch.randn(*shape, generator=g).to(DEV)
+        f2 = torch.randn(*shape, generator=g).to(DEV)
+        want = _build_with_workspace(L, f1, f2, nl, prec)
+        if first:
+            # the first call on a device also resolves the scratch address (module data may be
+            # made resident then); memory is accounted from the calls after it
+            _build_noalloc(L, f1, f2, nl, prec)
+            first = False
+        got, grew = _build_noalloc(L, f1, f2, nl, prec)
+        assert grew == 0, f"device memory in use grew by {grew} bytes across the call"
+        for l in range(nl):
+            assert torch.isfinite(got[l]).all(), (shape, l)
+            assert _relmax(got[l], want[l]) <= TOL[prec], (shape, prec, l)
+            # same kernels, same inputs: in fact bit-identical
+            assert torch.equal(got[l], want[l]), (shape, prec, l)
+        del want, got, f1, f2
+    torch.cuda.synchronize()
+
+
+def test_noalloc_rejects_what_does_not_fit(L):
+    B, D, h, w, nl = 8, 256, 55, 128, 4
+    need = int(L.rc_corr_build_workspace_bytes(B, D, h, w, PREC["bf16x3"]))
+    assert need > STATIC_BYTES
+    f = torch.zeros(1, device=DEV)  # never dereferenced: the size check comes first
+    out = (ctypes.c_void_p * nl)(*[f.data_ptr()] * nl)
+    rc = L.rc_corr_build_pyramid_noalloc(f.data_ptr(), f.data_ptr(), B, D, h, w, out, nl, PREC["bf16x3"], 0.0, None)
+    assert rc == RC_ERR_WORKSPACE
+    msg = L.rc_last_error().decode()
+    assert str(need) in msg and str(STATIC_BYTES) in msg
+    # fp32 has no scratch at all and is sent to the ordinary entry point
+    rc = L.rc_corr_build_pyramid_noalloc(f.data_ptr(), f.data_ptr(), 1, 32, 16, 16, out, nl, 0, 0.0, None)
+    assert rc == RC_ERR_INVALID and b"RC_PREC_FP32" in L.rc_last_error()
+    torch.cuda.synchronize()
