@@ -24,6 +24,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -103,6 +104,65 @@ __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *tm, ui
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// ---- cta_group::2 (CTA pair) variants.  In a cluster launch the 32-bit shared address carries the
+// CTA rank in bit 24; clearing it addresses the same offset in the even (leader) CTA of the pair.
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
+}
+__device__ __forceinline__ void tma2_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_4d(void *dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2,
+                                             int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t *slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// one thread of the leader CTA issues the pair's 256 x 256 x 16 MMA
+__device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once all earlier MMAs are done) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma2_commit_both(uint64_t *bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap *tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
 }
@@ -156,6 +216,8 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
 }
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=256
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+// the CTA pair's instruction: M=256 (128 rows in each CTA), N=256 (128 B rows held by each CTA)
+constexpr uint32_t kIdesc2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)((2 * TM) >> 4) << 24);
 
 // ---- small shared / global access helpers (explicit state spaces: no generic addressing)
 __device__ __forceinline__ void sts128(uint32_t a, float x, float y, float z, float w) {
@@ -192,11 +254,12 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
       : "memory");
 }
 
-template <int NPASS>
+template <int NPASS, int NCTA>
 struct Cfg {
   static constexpr int kOps = (NPASS == 3) ? 2 : 1;          // hi (+ lo)
-  static constexpr int kStageBytes = kOps * (A_BYTES + B_BYTES);
-  static constexpr int kStages = (NPASS == 3) ? 2 : 4;
+  static constexpr int kBBytes = B_BYTES / NCTA;             // a CTA of a pair stages half of the patch
+  static constexpr int kStageBytes = kOps * (A_BYTES + kBBytes);
+  static constexpr int kStages = 192 * 1024 / kStageBytes;   // 4 / 2 (single CTA), 6 / 3 (pair)
   static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kEpiWarps * kStgBytesPerWarp +
                                     256 /*barriers*/;
 };
@@ -250,12 +313,19 @@ __device__ __forceinline__ void store_rows(uint32_t buf, const float *v, int lan
   }
 }
 
-template <int NPASS>
+template <int NPASS, int NCTA>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                 const Params P) {
-  using C = Cfg<NPASS>;
+  using C = Cfg<NPASS, NCTA>;
+  // NCTA == 2: the kernel runs as clusters of two CTAs on one TPC.  The pair computes a 256 x 256
+  // tile with tcgen05.mma.cta_group::2: each CTA stages its own 128 query pixels (A) and HALF of
+  // the patch (B, 4 of the 8 rows), which halves the B-operand shared-memory traffic per SM;
+  // each CTA's TMEM still receives its 128 rows x all 256 columns, so the epilogue is unchanged.
+  const uint32_t rank = (NCTA == 2) ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const unsigned unit0 = blockIdx.x / NCTA, unit_step = gridDim.x / NCTA;
   extern __shared__ uint8_t smem_raw[];
   // 1024 B alignment (SWIZZLE_128B atoms) by offsetting inside the shared window
   const uint32_t raw_u32 = smem_u32(smem_raw);
@@ -274,12 +344,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
 
   if (warp == kProducerWarp && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], NCTA);  // pair: the leader's barrier also takes the peer's arrival and bytes
       mbar_init(&empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], kEpiWarps);
+      mbar_init(&tempty[a], kEpiWarps * NCTA);
     }
     fence_barrier_init();
     prefetch_tmap(&tmA_hi);
@@ -289,9 +359,13 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       prefetch_tmap(&tmB_lo);
     }
   }
-  if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
+  if (warp == kMmaWarp) {
+    if (NCTA == 2) tmem_alloc2(tmem_slot, kTmemCols);
+    else tmem_alloc(tmem_slot, kTmemCols);
+  }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();  // both CTAs' barriers are initialised before any remote use
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -303,33 +377,47 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      for (long long t = unit0; t < P.total_tiles; t += unit_step) {
         const int b = (int)(t / tiles_per_item);
         const int rem = (int)(t - (long long)b * tiles_per_item);
-        const int m = rem / nt, n = rem - m * nt;
+        const int mu = rem / nt, n = rem - mu * nt;
+        const int m = mu * NCTA + (int)rank;
         const int ny = n / P.nt_x, nx = n - ny * P.nt_x;
+        const int by = ny * PH + (int)rank * (PH / NCTA);  // this CTA's rows of the patch
         for (int kb = 0; kb < P.k_blocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t *sp = stage_base + stage * C::kStageBytes;
-          mbar_expect_tx(&full[stage], C::kStageBytes);
-          tma_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
-          tma_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, ny * PH, b);
-          if (NPASS == 3) {
-            tma_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
-            tma_load_4d(sp + C::kOps * A_BYTES + B_BYTES, &tmB_lo, &full[stage], kb * TK, nx * PW, ny * PH, b);
+          if (NCTA == 1) {
+            mbar_expect_tx(&full[stage], C::kStageBytes);
+            tma_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
+            tma_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, by, b);
+            if (NPASS == 3) {
+              tma_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
+              tma_load_4d(sp + C::kOps * A_BYTES + C::kBBytes, &tmB_lo, &full[stage], kb * TK, nx * PW, by, b);
+            }
+          } else {
+            // both CTAs' bytes are counted on the LEADER's barrier
+            if (leader) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+            tma2_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
+            tma2_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, by, b);
+            if (NPASS == 3) {
+              tma2_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
+              tma2_load_4d(sp + C::kOps * A_BYTES + C::kBBytes, &tmB_lo, &full[stage], kb * TK, nx * PW, by, b);
+            }
+            if (!leader) mbar_arrive_leader(&full[stage]);
           }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == kMmaWarp) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (leader CTA only in pair mode) =====================
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      for (long long t = unit0; t < P.total_tiles; t += unit_step) {
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
@@ -340,20 +428,33 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           const uint64_t a_hi = make_sw128_desc(sa);
           const uint64_t b_hi = make_sw128_desc(sa + C::kOps * A_BYTES);
           const uint64_t a_lo = make_sw128_desc(sa + A_BYTES);
-          const uint64_t b_lo = make_sw128_desc(sa + C::kOps * A_BYTES + B_BYTES);
+          const uint64_t b_lo = make_sw128_desc(sa + C::kOps * A_BYTES + C::kBBytes);
 #pragma unroll
           for (int k = 0; k < TK / UK; ++k) {
             const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);  // 32 B per K step inside the 128 B row
-            umma_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdesc, (kb | k) != 0 ? 1u : 0u);
-            if (NPASS == 3) {
-              umma_bf16(d_tmem, a_hi + koff, b_lo + koff, kIdesc, 1u);
-              umma_bf16(d_tmem, a_lo + koff, b_hi + koff, kIdesc, 1u);
+            const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
+            if (NCTA == 1) {
+              umma_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdesc, accum);
+              if (NPASS == 3) {
+                umma_bf16(d_tmem, a_hi + koff, b_lo + koff, kIdesc, 1u);
+                umma_bf16(d_tmem, a_lo + koff, b_hi + koff, kIdesc, 1u);
+              }
+            } else {
+              umma2_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdesc2, accum);
+              if (NPASS == 3) {
+                umma2_bf16(d_tmem, a_hi + koff, b_lo + koff, kIdesc2, 1u);
+                umma2_bf16(d_tmem, a_lo + koff, b_hi + koff, kIdesc2, 1u);
+              }
             }
           }
-          umma_commit(&empty[stage]);  // smem slot reusable once these MMAs have read it
+          // smem slot reusable (in both CTAs) once these MMAs have read it
+          if (NCTA == 1) umma_commit(&empty[stage]);
+          else umma2_commit_both(&empty[stage]);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs)
+        if (NCTA == 1) umma_commit(&tfull[acc]);
+        else umma2_commit_both(&tfull[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -374,10 +475,11 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     const size_t pitch0 = (size_t)h * w, pitch1 = (size_t)h1 * w1, pitch2 = (size_t)h2 * w2, pitch3 = (size_t)h3 * w3;
     const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;
     bool peer_pending = false;  // hf=1: our staging buffer still holds the level-2 row for the peer
-    for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+    for (long long t = unit0; t < P.total_tiles; t += unit_step) {
       const int b = (int)(t / tiles_per_item);
       const int rem = (int)(t - (long long)b * tiles_per_item);
-      const int m = rem / nt, n = rem - m * nt;
+      const int mu = rem / nt, n = rem - mu * nt;
+      const int m = mu * NCTA + (int)rank;
       const int ny = n / P.nt_x, nx = n - ny * P.nt_x;
       const int prow0 = m * TM + q * 32;                 // first query pixel of this warp
       const int rows_valid = min(32, N - prow0);         // may be <= 0
@@ -406,7 +508,10 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           // all TMEM reads of this tile are done: hand the accumulator back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[acc]);
+          if (lane == 0) {
+            if (NCTA == 1) mbar_arrive(&tempty[acc]);
+            else mbar_arrive_leader(&tempty[acc]);  // the pair's MMA thread lives in the leader CTA
+          }
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
@@ -487,8 +592,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();  // the peer may still be reading our smem / signalling our barriers
   tc_fence_after();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == kMmaWarp) {
+    if (NCTA == 2) tmem_dealloc2(tmem_base, kTmemCols);
+    else tmem_dealloc(tmem_base, kTmemCols);
+  }
 }
 
 // ------------------------------------------------------------------ prep: NCHW fp32 -> NHWC bf16 hi/lo
@@ -564,17 +673,39 @@ static int sm_count() {
   return n;
 }
 
-template <int NPASS>
+template <int NPASS, int NCTA>
 static int launch(const CUtensorMap &ah, const CUtensorMap &al, const CUtensorMap &bh, const CUtensorMap &bl,
                   const Params &P, cudaStream_t st) {
-  using C = Cfg<NPASS>;
+  using C = Cfg<NPASS, NCTA>;
   static_assert(C::kSmemBytes <= 227 * 1024, "shared memory budget");
-  RC_CUDA(cudaFuncSetAttribute(build_tc_kernel<NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-  const long long sms = sm_count();
-  const unsigned grid = (unsigned)(P.total_tiles < sms ? P.total_tiles : sms);
-  build_tc_kernel<NPASS><<<grid, kThreads, C::kSmemBytes, st>>>(ah, al, bh, bl, P);
+  auto kern = build_tc_kernel<NPASS, NCTA>;
+  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  const long long units = sm_count() / NCTA;  // one CTA (or CTA pair) per SM (per TPC)
+  const unsigned grid = (unsigned)((P.total_tiles < units ? P.total_tiles : units) * NCTA);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = NCTA;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  RC_CUDA(cudaLaunchKernelEx(&cfg, kern, ah, al, bh, bl, P));
   RC_CUDA(cudaGetLastError());
   return RC_OK;
+}
+
+// CTA pairs (cta_group::2) unless RAFT_CORR_TC_CTAS=1 asks for the single-CTA kernel
+static int ctas_per_tile() {
+  static const int n = [] {
+    const char *e = getenv("RAFT_CORR_TC_CTAS");
+    return (e && e[0] == '1') ? 1 : 2;
+  }();
+  return n;
 }
 
 }  // namespace tc
@@ -602,6 +733,7 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   }
   const int N = h * w, Dp = round_up64(D);
   const bool x3 = precision == RC_PREC_BF16X3;
+  const int ncta = tc::ctas_per_tile();
   const size_t per_map = ((size_t)B * N * Dp * 2 + 255) / 256 * 256;
   uint8_t *base = static_cast<uint8_t *>(ws);
   __nv_bfloat16 *a_hi = reinterpret_cast<__nv_bfloat16 *>(base);
@@ -626,7 +758,7 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   {
     const cuuint64_t dims[4] = {(cuuint64_t)Dp, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
     const cuuint64_t strides[3] = {(cuuint64_t)Dp * 2, (cuuint64_t)w * Dp * 2, (cuuint64_t)N * Dp * 2};
-    const cuuint32_t box[4] = {TK, PW, PH, 1};
+    const cuuint32_t box[4] = {TK, PW, (cuuint32_t)(PH / ncta), 1};  // a CTA of a pair loads half the patch
     if (int rc = make_map(&tmBh, b_hi, 4, dims, strides, box)) return rc;
     if (int rc = make_map(&tmBl, b_lo, 4, dims, strides, box)) return rc;
   }
@@ -634,7 +766,7 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   Params P{};
   P.B = B; P.N = N; P.h = h; P.w = w; P.L = L;
   P.k_blocks = Dp / TK;
-  P.m_tiles = (N + TM - 1) / TM;
+  P.m_tiles = (N + TM * ncta - 1) / (TM * ncta);  // tiles (or tile pairs) along the query pixels
   P.nt_x = (w + PW - 1) / PW;
   P.nt_y = (h + PH - 1) / PH;
   P.total_tiles = (long long)B * P.m_tiles * P.nt_x * P.nt_y;
@@ -648,7 +780,11 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
   }
   for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
 
-  int rc = x3 ? tc::launch<3>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1>(tmAh, tmAl, tmBh, tmBl, P, st);
+  int rc;
+  if (ncta == 2)
+    rc = x3 ? tc::launch<3, 2>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2>(tmAh, tmAl, tmBh, tmBl, P, st);
+  else
+    rc = x3 ? tc::launch<3, 1>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1>(tmAh, tmAl, tmBh, tmBl, P, st);
   if (rc) return rc;
   if (L > 4) return launch_pool_tail(lv, B, h, w, 4, L, st);
   return RC_OK;

@@ -75,14 +75,14 @@ __device__ __forceinline__ auto pick_level(const P &t, int lvl) {
   return r;
 }
 
-// floor() of a coordinate as an int that is safe for any float (NaN/Inf/huge -> far outside)
+// floor() of a coordinate as an int that is safe for any float (NaN/Inf/huge -> far outside the
+// grid with a zero fraction); branch-free
 __device__ __forceinline__ int safe_floor_int(float v, float *frac) {
-  float f = floorf(v);
-  *frac = v - f;
-  // clamp before the cast: everything beyond +-2^24 is outside any feature grid anyway
-  if (!(f > -16777216.0f)) { *frac = 0.0f; return -16777216; }
-  if (!(f < 16777216.0f)) { *frac = 0.0f; return 16777216; }
-  return (int)f;
+  const float f = floorf(v);
+  const bool sane = fabsf(v) < 16777216.0f;  // false for NaN / Inf / huge
+  *frac = sane ? v - f : 0.0f;
+  // fmaxf/fminf drop a NaN operand; everything beyond +-2^24 is outside any feature grid anyway
+  return __float2int_rz(fminf(fmaxf(f, -16777216.0f), 16777216.0f));
 }
 
 __device__ __forceinline__ float ld_stream(const float *p) {

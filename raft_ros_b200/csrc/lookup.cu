@@ -50,6 +50,28 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
   const float *__restrict__ vol = pick_level(lv, lvl);
   float *patch = patch_all + warp * (kUnroll * NPATCH);
 
+  // per-lane constants of the patch element(s) and tap(s) this lane owns, hoisted out of the
+  // pixel loop: the kernel is issue-bound on integer address math otherwise
+  int e_py[NE], e_px[NE], e_rel[NE];
+#pragma unroll
+  for (int k = 0; k < NE; ++k) {
+    const int e = lane + 32 * k;
+    e_py[k] = e / PN;
+    e_px[k] = e - e_py[k] * PN;
+    e_rel[k] = e_py[k] * wl + e_px[k];
+  }
+  int t_src[NT], t_dst[NT];
+#pragma unroll
+  for (int k = 0; k < NT; ++k) {
+    const int t = lane + 32 * k;
+    const int i = t / RD, j = t - i * RD;  // i: x offset, j: y offset
+    t_src[k] = j * PN + i;
+    t_dst[k] = t * TS;
+  }
+  const size_t row_elems = (size_t)hl * wl;
+  const float *__restrict__ cxp = coords + ((size_t)b * 2 + 0) * N;
+  const float *__restrict__ cyp = coords + ((size_t)b * 2 + 1) * N;
+
 #pragma unroll 1
   for (int g = 0; g < kPixPerWarp; g += kUnroll) {
     float v[kUnroll][NE];
@@ -61,28 +83,32 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
       const bool pvalid = p < N;
       float cx = 0.f, cy = 0.f;
       if (pvalid) {
-        cx = __ldg(coords + ((size_t)b * 2 + 0) * N + p) * inv;
-        cy = __ldg(coords + ((size_t)b * 2 + 1) * N + p) * inv;
+        cx = __ldg(cxp + p) * inv;
+        cy = __ldg(cyp + p) * inv;
       }
       const int x0 = safe_floor_int(cx, &fx[u]) - R;
       const int y0 = safe_floor_int(cy, &fy[u]) - R;
-      const float *row = vol + ((size_t)b * N + (pvalid ? p : 0)) * ((size_t)hl * wl);
+      const float *row = vol + ((size_t)b * N + (pvalid ? p : 0)) * row_elems + (y0 * wl + x0);
+      // whole (2r+2)^2 patch inside the level: no per-element bounds tests (warp-uniform branch)
+      const bool interior = pvalid && y0 >= 0 && x0 >= 0 && y0 + PN <= hl && x0 + PN <= wl;
+      if (interior) {
 #pragma unroll
-      for (int k = 0; k < NE; ++k) {
-        const int e = lane + 32 * k;
-        const int py = e / PN, px = e - py * PN;
-        const int gy = y0 + py, gx = x0 + px;
-        const bool ok = pvalid && (e < NPATCH) && gy >= 0 && gy < hl && gx >= 0 && gx < wl;
-        v[u][k] = ok ? ld_stream(row + (size_t)gy * wl + gx) : 0.0f;
+        for (int k = 0; k < NE; ++k)
+          v[u][k] = ((NPATCH % 32 == 0) || lane + 32 * k < NPATCH) ? ld_stream(row + e_rel[k]) : 0.0f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < NE; ++k) {
+          const bool ok = pvalid && (lane + 32 * k < NPATCH) && (unsigned)(y0 + e_py[k]) < (unsigned)hl &&
+                          (unsigned)(x0 + e_px[k]) < (unsigned)wl;
+          v[u][k] = ok ? ld_stream(row + e_rel[k]) : 0.0f;
+        }
       }
     }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u)
 #pragma unroll
-      for (int k = 0; k < NE; ++k) {
-        const int e = lane + 32 * k;
-        if (e < NPATCH) patch[u * NPATCH + e] = v[u][k];
-      }
+      for (int k = 0; k < NE; ++k)
+        if ((NPATCH % 32 == 0) || lane + 32 * k < NPATCH) patch[u * NPATCH + lane + 32 * k] = v[u][k];
     __syncwarp();
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
@@ -93,15 +119,13 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
       const float *pp = patch + u * NPATCH;
 #pragma unroll
       for (int k = 0; k < NT; ++k) {
-        const int t = lane + 32 * k;
-        if (t < NTAP) {
-          const int i = t / RD, j = t - i * RD;  // i: x offset, j: y offset
-          const float *q = pp + j * PN + i;
+        if ((NTAP % 32 == 0) || lane + 32 * k < NTAP) {
+          const float *q = pp + t_src[k];
           float s = q[0] * w00;
           s = fmaf(q[1], w01, s);
           s = fmaf(q[PN], w10, s);
           s = fmaf(q[PN + 1], w11, s);
-          tile[t * TS + pix] = s;
+          tile[t_dst[k] + pix] = s;
         }
       }
     }
@@ -112,9 +136,15 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
   const int CH = L * NTAP;
   const int p = p0 + lane;
   if (p < N) {
-    float *o = out + ((size_t)b * CH + (size_t)lvl * NTAP) * N + p;
-#pragma unroll 4
-    for (int t = warp; t < NTAP; t += kLookupWarps) st_stream(o + (size_t)t * N, tile[t * TS + lane]);
+    float *o = out + ((size_t)b * CH + (size_t)lvl * NTAP + warp) * N + p;
+    const float *src = tile + warp * TS + lane;
+    const size_t ostep = (size_t)kLookupWarps * N;
+#pragma unroll 7
+    for (int t = warp; t < NTAP; t += kLookupWarps) {
+      st_stream(o, *src);
+      o += ostep;
+      src += kLookupWarps * TS;
+    }
   }
 }
 
