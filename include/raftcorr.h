@@ -129,18 +129,22 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
 int rc_corr_lookup_bwd(const float *grad_out, const float *coords, float *const *grad_level_ptrs,
                        int B, int h, int w, int num_levels, int radius, void *stream);
 
-/* Bytes of scratch rc_corr_build_bwd needs. */
-size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w);
+/* Bytes of scratch rc_corr_build_bwd needs for this problem and precision. */
+size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w, int precision);
 
 /*
  * Gradient of the build: folds the grad pyramid back to level 0 (avg_pool2d backward,
  * core/corr.py:26), applies 1/sqrt(D) (:60) and the two contractions of matmul's backward
  * (:58):  dfmap1[d,p] = sum_q dC[p,q] fmap2[d,q],  dfmap2[d,q] = sum_p dC[p,q] fmap1[d,p].
  *   dfmap1, dfmap2 : (B, D, h, w) fp32, fully overwritten
+ *   precision      : RC_PREC_FP32 = fp32 FMA on CUDA cores; RC_PREC_BF16X3 / RC_PREC_BF16 = tcgen05
+ *                    with bf16 hi/lo split operands (three MMAs, fp32 accumulate: gradients are
+ *                    always fp32-class, also when the forward was single-pass bf16)
+ *   workspace      : >= rc_corr_build_bwd_workspace_bytes(...), 256 B aligned
  */
 int rc_corr_build_bwd(const float *const *grad_level_ptrs, const float *fmap1, const float *fmap2,
                       float *dfmap1, float *dfmap2, int B, int D, int h, int w, int num_levels,
-                      float scale, void *workspace, size_t workspace_bytes, void *stream);
+                      int precision, float scale, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
  * alt_cuda_corr.forward: windowed dot products computed on the fly (no volume).

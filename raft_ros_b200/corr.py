@@ -123,17 +123,19 @@ def lookup_bwd_raw(grad_out: torch.Tensor, coords: torch.Tensor, grad_levels: Se
         _lib.check(rc, "rc_corr_lookup_bwd")
 
 
-def build_bwd_raw(grad_levels: Sequence[torch.Tensor], fmap1: torch.Tensor, fmap2: torch.Tensor, scale: float = 0.0):
+def build_bwd_raw(grad_levels: Sequence[torch.Tensor], fmap1: torch.Tensor, fmap2: torch.Tensor, scale: float = 0.0,
+                  precision: Optional[str] = None):
     """rc_corr_build_bwd: grad pyramid -> (dfmap1, dfmap2), both (B,D,h,w)."""
     f1, f2 = _f32c(fmap1), _f32c(fmap2)
     B, D, h, w = f1.shape
+    prec = _precision_code(precision)
     L = _lib.lib()
     with torch.cuda.device(f1.device):
         df1, df2 = torch.empty_like(f1), torch.empty_like(f2)
-        ws_bytes = int(L.rc_corr_build_bwd_workspace_bytes(B, D, h, w))
+        ws_bytes = int(L.rc_corr_build_bwd_workspace_bytes(B, D, h, w, prec))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=f1.device)
         rc = L.rc_corr_build_bwd(_lib.ptr_array([t.data_ptr() for t in grad_levels]), f1.data_ptr(), f2.data_ptr(),
-                                 df1.data_ptr(), df2.data_ptr(), B, D, h, w, len(grad_levels), float(scale),
+                                 df1.data_ptr(), df2.data_ptr(), B, D, h, w, len(grad_levels), prec, float(scale),
                                  ws.data_ptr(), ws_bytes, _stream())
         _lib.check(rc, "rc_corr_build_bwd")
         ws.record_stream(torch.cuda.current_stream())
@@ -141,28 +143,68 @@ def build_bwd_raw(grad_levels: Sequence[torch.Tensor], fmap1: torch.Tensor, fmap
 
 
 # --------------------------------------------------------------------------- autograd
+class _GradState:
+    """Per-CorrBlock bookkeeping of one backward pass.
+
+    The reference lets autograd add up the K per-iteration gradients of the pyramid: every
+    grid_sample backward allocates a zeros_like(level) and the engine sums them (K zero-fills and
+    K-1 adds over a volume-sized tensor).  Here all K lookups of a CorrBlock accumulate straight
+    into ONE gradient pyramid (rc_corr_lookup_bwd is `+=` and deterministic), and the build's
+    backward consumes it once.  The autograd edge between the lookups and the build is a
+    one-element `token` tensor, so the engine still orders build.backward after every lookup.
+    """
+
+    def __init__(self):
+        self.levels = None        # detached pyramid, read by the lookups
+        self.grad_levels = None   # allocated lazily by the first lookup backward of a pass
+
+
+def _alloc_like_levels(levels):
+    sizes = [lv.numel() for lv in levels]
+    offs, total = [], 0
+    for s_ in sizes:
+        offs.append(total)
+        total += (s_ + 63) // 64 * 64
+    flat = torch.zeros(total, dtype=torch.float32, device=levels[0].device)
+    return [flat[o:o + n].view(lv.shape) for o, n, lv in zip(offs, sizes, levels)]
+
+
 class _BuildPyramidFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, fmap1, fmap2, num_levels, precision):
-        ctx.save_for_backward(fmap1, fmap2)
-        levels = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
-        return tuple(levels)
+    """outputs: (token, level_0, ..., level_{L-1}).  Gradients may arrive through the levels
+    (generic autograd use of `corr_pyramid`) and/or through `state.grad_levels` (the lookups)."""
 
     @staticmethod
-    def backward(ctx, *grad_levels):
+    def forward(ctx, fmap1, fmap2, num_levels, precision, state):
+        ctx.save_for_backward(fmap1, fmap2)
+        ctx.state = state
+        ctx.precision = precision
+        levels = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
+        state.levels = [lv.detach() for lv in levels]
+        token = torch.zeros(1, dtype=torch.float32, device=fmap1.device)
+        return (token,) + tuple(levels)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_token, *grad_levels):
         fmap1, fmap2 = ctx.saved_tensors
-        B, D, h, w = fmap1.shape
-        shapes = level_shapes(h, w, len(grad_levels))
-        gl = []
-        for g, (hl, wl) in zip(grad_levels, shapes):
+        state = ctx.state
+        gl = state.grad_levels
+        state.grad_levels = None  # a later backward pass (retain_graph) starts from zero again
+        for l, g in enumerate(grad_levels):
             if g is None:
-                g = torch.zeros((B * h * w, 1, hl, wl), dtype=torch.float32, device=fmap1.device)
-            gl.append(_f32c(g))
-        df1, df2 = build_bwd_raw(gl, fmap1, fmap2)
-        return df1.to(fmap1.dtype), df2.to(fmap2.dtype), None, None
+                continue
+            if gl is None:
+                gl = _alloc_like_levels(state.levels)
+            gl[l].add_(g.view(gl[l].shape))
+        if gl is None:
+            return torch.zeros_like(fmap1), torch.zeros_like(fmap2), None, None, None
+        df1, df2 = build_bwd_raw(gl, fmap1, fmap2, precision=ctx.precision)
+        return df1.to(fmap1.dtype), df2.to(fmap2.dtype), None, None, None
 
 
 class _LookupFn(torch.autograd.Function):
+    """Generic path: the pyramid levels themselves are the differentiable inputs."""
+
     @staticmethod
     def forward(ctx, coords, radius, *levels):
         ctx.radius = radius
@@ -171,12 +213,34 @@ class _LookupFn(torch.autograd.Function):
         return lookup_raw(levels, coords, radius)
 
     @staticmethod
+    @torch.autograd.function.once_differentiable
     def backward(ctx, grad_out):
         (coords,) = ctx.saved_tensors
         grads = [torch.zeros(s, dtype=torch.float32, device=grad_out.device) for s in ctx.level_shapes]
         lookup_bwd_raw(grad_out, coords, grads, ctx.radius)
         # coords carry no gradient (they are detached at core/raft.py:123)
         return (None, None) + tuple(grads)
+
+
+class _LookupTokenFn(torch.autograd.Function):
+    """CorrBlock's own path: accumulate into the block's single gradient pyramid."""
+
+    @staticmethod
+    def forward(ctx, coords, token, state, radius):
+        ctx.radius = radius
+        ctx.state = state
+        ctx.save_for_backward(coords)
+        return lookup_raw(state.levels, coords, radius)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_out):
+        (coords,) = ctx.saved_tensors
+        state = ctx.state
+        if state.grad_levels is None:
+            state.grad_levels = _alloc_like_levels(state.levels)
+        lookup_bwd_raw(grad_out, coords, state.grad_levels, ctx.radius)
+        return None, torch.zeros(1, dtype=torch.float32, device=grad_out.device), None, None
 
 
 # --------------------------------------------------------------------------- public classes
@@ -193,14 +257,18 @@ class CorrBlock:
         self.num_levels = num_levels
         self.radius = radius
         self.precision = precision
+        self._state = None
+        self._token = None
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
-            self.corr_pyramid = list(_BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision))
+            self._state = _GradState()
+            out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state)
+            self._token, self.corr_pyramid = out[0], list(out[1:])
         else:
             self.corr_pyramid = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
 
     def __call__(self, coords):
-        if torch.is_grad_enabled() and any(lv.requires_grad for lv in self.corr_pyramid):
-            return _LookupFn.apply(coords, self.radius, *self.corr_pyramid)
+        if self._token is not None and torch.is_grad_enabled():
+            return _LookupTokenFn.apply(coords, self._token, self._state, self.radius)
         return lookup_raw(self.corr_pyramid, coords, self.radius)
 
     @staticmethod
@@ -208,7 +276,7 @@ class CorrBlock:
         """(B,D,h,w) x2 -> (B,h,w,1,h,w): fmap1^T fmap2 / sqrt(D) (reference core/corr.py:52-60)."""
         B, _, h, w = fmap1.shape
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
-            (vol,) = _BuildPyramidFn.apply(fmap1, fmap2, 1, precision)
+            _, vol = _BuildPyramidFn.apply(fmap1, fmap2, 1, precision, _GradState())
         else:
             (vol,) = build_pyramid_raw(fmap1, fmap2, 1, precision)
         return vol.view(B, h, w, 1, h, w)

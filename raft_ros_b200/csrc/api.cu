@@ -142,14 +142,15 @@ int rc_corr_lookup_bwd(const float *grad_out, const float *coords, float *const 
   return launch_lookup_bwd(grad_out, coords, lv, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
-size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w) {
+size_t rc_corr_build_bwd_workspace_bytes(int B, int D, int h, int w, int precision) {
   if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return 0;
-  return build_bwd_workspace_bytes(B, D, h, w);
+  if (precision == RC_PREC_FP32) return build_bwd_workspace_bytes(B, D, h, w);
+  return build_bwd_tc_workspace_bytes(B, D, h, w);
 }
 
 int rc_corr_build_bwd(const float *const *grad_level_ptrs, const float *fmap1, const float *fmap2,
                       float *dfmap1, float *dfmap2, int B, int D, int h, int w, int num_levels,
-                      float scale, void *workspace, size_t workspace_bytes, void *stream) {
+                      int precision, float scale, void *workspace, size_t workspace_bytes, void *stream) {
   if (int rc = check_geometry("rc_corr_build_bwd", B, h, w, num_levels)) return rc;
   RC_CHECK_ARG(grad_level_ptrs && fmap1 && fmap2 && dfmap1 && dfmap2, "rc_corr_build_bwd: null pointer");
   RC_CHECK_ARG(D > 0, "rc_corr_build_bwd: D must be positive");
@@ -159,6 +160,11 @@ int rc_corr_build_bwd(const float *const *grad_level_ptrs, const float *fmap1, c
     lv.p[l] = grad_level_ptrs[l];
   }
   if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  RC_CHECK_ARG(precision == RC_PREC_FP32 || precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16,
+               "rc_corr_build_bwd: unknown precision %d", precision);
+  if (precision != RC_PREC_FP32)
+    return launch_build_bwd_tc(lv, fmap1, fmap2, dfmap1, dfmap2, B, D, h, w, num_levels, scale, workspace,
+                               workspace_bytes, static_cast<cudaStream_t>(stream));
   return launch_build_bwd(lv, fmap1, fmap2, dfmap1, dfmap2, B, D, h, w, num_levels, scale, workspace,
                           workspace_bytes, static_cast<cudaStream_t>(stream));
 }

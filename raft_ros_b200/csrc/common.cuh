@@ -50,6 +50,10 @@ size_t build_bwd_workspace_bytes(int B, int D, int h, int w);
 int launch_build_bwd(const ConstLevelPtrs &glv, const float *f1, const float *f2, float *df1,
                      float *df2, int B, int D, int h, int w, int L, float scale, void *ws,
                      size_t ws_bytes, cudaStream_t st);
+size_t build_bwd_tc_workspace_bytes(int B, int D, int h, int w);
+int launch_build_bwd_tc(const ConstLevelPtrs &glv, const float *f1, const float *f2, float *df1,
+                        float *df2, int B, int D, int h, int w, int L, float scale, void *ws,
+                        size_t ws_bytes, cudaStream_t st);
 int launch_alt_fwd(const float *f1, const float *f2, const float *coords, float *corr, int B,
                    int N, int H1, int W1, int H2, int W2, int C, int r, cudaStream_t st);
 int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const float *cg,

@@ -187,16 +187,68 @@ def test_lookup_bwd_vs_oracle_and_determinism(rr, shape):
     assert relmax(n(grads[0]), 2 * want[0]) <= 2e-6
 
 
-def test_build_bwd_vs_oracle(rr):
+@pytest.mark.parametrize("precision,tol", [("fp32", 5e-6), ("bf16x3", 5e-5)])
+@pytest.mark.parametrize("dims", [(2, 48, 18, 21, 4), (1, 256, 23, 39, 3), (1, 96, 33, 67, 4)])
+def test_build_bwd_vs_oracle(rr, dims, precision, tol):
     from raft_ros_b200.corr import build_bwd_raw
-    B, D, h, w, L = 2, 48, 18, 21, 4
+    B, D, h, w, L = dims
     rng = np.random.default_rng(5)
     f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
     f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
     gl = [rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32) for hl, wl in O.level_shapes(h, w, L)]
     w1, w2 = O.corr_build_bwd(gl, f1, f2)
-    d1, d2 = build_bwd_raw([t(g) for g in gl], t(f1), t(f2))
-    assert relmax(n(d1), w1) <= 5e-6 and relmax(n(d2), w2) <= 5e-6
+    d1, d2 = build_bwd_raw([t(g) for g in gl], t(f1), t(f2), precision=precision)
+    assert relmax(n(d1), w1) <= tol and relmax(n(d2), w2) <= tol, (relmax(n(d1), w1), relmax(n(d2), w2))
+
+
+def test_autograd_paths(rr):
+    """(a) CorrBlock's own lookups accumulate into one gradient pyramid; (b) user code may also
+    differentiate through `corr_pyramid` tensors directly; (c) a second backward pass over a
+    retained graph starts from zero again; all against torch autograd of the same math."""
+    from oracle import torch_port as TP
+    B, D, h, w, r = 2, 64, 20, 24, 4
+    g = torch.Generator(device="cpu").manual_seed(7)
+    f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    f2 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    coords = [rr.coords_grid(B, h, w, DEV) + 2.0 * torch.randn(B, 2, h, w, generator=g).to(DEV) for _ in range(3)]
+    cot = [torch.randn(B, 324, h, w, generator=g).to(DEV) for _ in range(3)]
+
+    def loss_of(build, look, a, b):
+        pyr = build(a, b)
+        tot = (pyr[1] ** 2).sum() * 1e-3 + pyr[3].sum()     # direct use of the pyramid tensors
+        for c, ct in zip(coords, cot):
+            tot = tot + (look(pyr, c) * ct).sum()
+        return tot
+
+    a, b = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
+    blk = {}
+
+    def our_build(x, y):
+        blk["b"] = rr.CorrBlock(x, y, radius=r, precision="fp32")
+        return blk["b"].corr_pyramid
+
+    ours = loss_of(our_build, lambda pyr, c: blk["b"](c), a, b)
+    ours.backward(retain_graph=True)
+    ga1, gb1 = a.grad.clone(), b.grad.clone()
+    a.grad = None
+    b.grad = None
+    ours.backward()
+    assert torch.equal(a.grad, ga1) and torch.equal(b.grad, gb1)  # deterministic, re-entrant
+    ra, rb = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
+    ref = loss_of(lambda x, y: TP.build_pyramid(x, y, 4), lambda pyr, c: TP.lookup(pyr, c, r), ra, rb)
+    ref.backward()
+    assert abs(float(ours) - float(ref)) <= 1e-4 * abs(float(ref))
+    assert relmax(n(ga1), n(ra.grad)) <= 2e-5 and relmax(n(gb1), n(rb.grad)) <= 2e-5
+    # CorrBlock.corr
+    a2, b2 = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
+    v = rr.CorrBlock.corr(a2, b2, precision="bf16x3")
+    assert v.shape == (B, h, w, 1, h, w)
+    wgt = torch.randn(v.shape, generator=g).to(DEV)
+    (v * wgt).sum().backward()
+    a3, b3 = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
+    vr = (torch.matmul(a3.view(B, D, h * w).transpose(1, 2), b3.view(B, D, h * w)) / 8.0).view(B, h, w, 1, h, w)
+    (vr * wgt).sum().backward()
+    assert relmax(n(a2.grad), n(a3.grad)) <= 5e-5 and relmax(n(b2.grad), n(b3.grad)) <= 5e-5
 
 
 # ----------------------------------------------------------------------------- alt (on the fly)

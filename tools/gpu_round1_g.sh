@@ -1,0 +1,7 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+python -c "import __graft_entry__ as g; g.build()" > gpurun_out/build.log 2>&1; echo "build rc=$?"
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_gpu.log
+timeout 600 python tools/bench_configs.py train > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"
+cat gpurun_out/configs.jsonl; tail -3 gpurun_out/configs.err
