@@ -180,52 +180,98 @@ __global__ void split_rows_kernel(const float *__restrict__ src, __nv_bfloat16 *
   }
 }
 
-// gradient pyramid -> dC (p-major) and dC^T (q-major), both as bf16 hi/lo with pitch `pitch`
+// gradient pyramid -> dC (p-major) and dC^T (q-major), both as bf16 hi/lo with pitch `pitch`.
+// One CTA = a 64 x 64 tile of dC; a thread owns 4 consecutive columns (one 16 B read of level 0,
+// 8 B bf16x4 writes), the transpose goes through shared memory.
+struct __align__(8) bf16x4 {
+  __nv_bfloat16 v[4];
+};
+
+__device__ __forceinline__ void split4(const float (&g)[4], bf16x4 &hi, bf16x4 &lo) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    hi.v[j] = __float2bfloat16_rn(g[j]);
+    lo.v[j] = __float2bfloat16_rn(g[j] - __bfloat162float(hi.v[j]));
+  }
+}
+
 __global__ void __launch_bounds__(256)
 fold_split_kernel(ConstLevelPtrs glv, __nv_bfloat16 *__restrict__ c_hi, __nv_bfloat16 *__restrict__ c_lo,
                   __nv_bfloat16 *__restrict__ t_hi, __nv_bfloat16 *__restrict__ t_lo, int h, int w, int L, int pitch,
-                  float scale) {
-  __shared__ float tile[32][33];
+                  float scale, int vec_in) {
+  __shared__ float tile[64][65];
   const int N = h * w;
   const int b = blockIdx.z;
-  const int p0 = blockIdx.y * 32, q0 = blockIdx.x * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int p0 = blockIdx.y * 64, q0 = blockIdx.x * 64;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const size_t item = (size_t)b * N;
+  const int q = q0 + tx * 4;
+  // per-column geometry of this thread's 4 columns is the same for every row it handles
+  int yy[4], xx[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    yy[j] = (q + j) / w;
+    xx[j] = (q + j) - yy[j] * w;
+  }
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int p = p0 + ty + 8 * i, q = q0 + tx;
-    float g = 0.0f;
+    const int p = p0 + ty + 16 * i;
+    float g[4] = {0.f, 0.f, 0.f, 0.f};
     if (p < N && q < N) {
       const size_t rp = item + p;
-      int y = q / w, x = q - y * w;
-      g = __ldg(glv.p[0] + rp * N + q);
+      const float *g0 = glv.p[0] + rp * N + q;
+      if (vec_in && q + 3 < N) {
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(g0));
+        g[0] = v.x; g[1] = v.y; g[2] = v.z; g[3] = v.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (q + j < N) g[j] = __ldg(g0 + j);
+      }
       float wgt = 1.0f;
       for (int l = 1; l < L; ++l) {
         const int hl = h >> l, wl = w >> l;
-        y >>= 1;
-        x >>= 1;
         wgt *= 0.25f;
-        if (y >= hl || x >= wl) break;
-        g = fmaf(wgt, __ldg(pick_level(glv, l) + rp * ((size_t)hl * wl) + (size_t)y * wl + x), g);
+        const float *gl = pick_level(glv, l) + rp * ((size_t)hl * wl);
+        int last = -1;
+        float lastv = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int y = yy[j] >> l, x = xx[j] >> l;
+          if (q + j < N && y < hl && x < wl) {
+            const int idx = y * wl + x;
+            if (idx != last) {
+              last = idx;
+              lastv = __ldg(gl + idx);
+            }
+            g[j] = fmaf(wgt, lastv, g[j]);
+          }
+        }
       }
-      g *= scale;
-      const __nv_bfloat16 gh = __float2bfloat16_rn(g);
-      const size_t o = (item + p) * (size_t)pitch + q;
-      c_hi[o] = gh;
-      c_lo[o] = __float2bfloat16_rn(g - __bfloat162float(gh));
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] *= scale;
+      bf16x4 hi, lo;
+      split4(g, hi, lo);
+      const size_t o = (item + p) * (size_t)pitch + q;  // 8 B aligned: pitch and q0 are multiples of 64
+      *reinterpret_cast<bf16x4 *>(c_hi + o) = hi;
+      *reinterpret_cast<bf16x4 *>(c_lo + o) = lo;
     }
-    tile[ty + 8 * i][tx] = g;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tile[ty + 16 * i][tx * 4 + j] = g[j];
   }
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int q = q0 + ty + 8 * i, p = p0 + tx;
-    if (p < N && q < N) {
-      const float g = tile[tx][ty + 8 * i];
-      const __nv_bfloat16 gh = __float2bfloat16_rn(g);
-      const size_t o = (item + q) * (size_t)pitch + p;
-      t_hi[o] = gh;
-      t_lo[o] = __float2bfloat16_rn(g - __bfloat162float(gh));
+    const int qq = q0 + ty + 16 * i, pp = p0 + tx * 4;
+    if (qq < N && pp < N) {
+      float g[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] = tile[tx * 4 + j][ty + 16 * i];
+      bf16x4 hi, lo;
+      split4(g, hi, lo);
+      const size_t o = (item + qq) * (size_t)pitch + pp;
+      *reinterpret_cast<bf16x4 *>(t_hi + o) = hi;
+      *reinterpret_cast<bf16x4 *>(t_lo + o) = lo;
     }
   }
 }
@@ -337,8 +383,9 @@ int launch_build_bwd_tc(const ConstLevelPtrs &glv, const float *f1, const float 
   auto *f2_hi = reinterpret_cast<__nv_bfloat16 *>(base + 4 * big + 2 * small);
   auto *f2_lo = reinterpret_cast<__nv_bfloat16 *>(base + 4 * big + 3 * small);
   {
-    dim3 grid((unsigned)((N + 31) / 32), (unsigned)((N + 31) / 32), (unsigned)B);
-    fold_split_kernel<<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, L, pitch, scale);
+    dim3 grid((unsigned)((N + 63) / 64), (unsigned)((N + 63) / 64), (unsigned)B);
+    const int vec_in = (N % 4 == 0 && (reinterpret_cast<uintptr_t>(glv.p[0]) & 15) == 0) ? 1 : 0;
+    fold_split_kernel<<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, L, pitch, scale, vec_in);
     RC_CUDA(cudaGetLastError());
     const long long rows = (long long)B * D;
     const int blocks = 148 * 8;
