@@ -159,6 +159,31 @@ int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords,
                     int B, int N, int H1, int W1, int H2, int W2, int C, int radius, void *stream);
 
 /*
+ * AlternateCorrBlock on tensor cores: every pyramid level of the on-the-fly correlation in ONE
+ * launch, output already in CorrBlock's layout and scaled.
+ * Replaces: the per-level loop of AlternateCorrBlock.__call__ (core/corr.py:74-91: 8 NHWC
+ * permute-copies, num_levels x alt_cuda_corr.forward, stack, reshape, divide).
+ *
+ * rc_alt_prep_fmap converts one feature map once (AlternateCorrBlock.__init__ time):
+ *   fmap (B, C, H, W) fp32 NCHW  ->  hi, lo : (B, H, W, Cp) bf16, Cp = C rounded up to 64,
+ *   x ~= hi + lo (lo may be NULL when only RC_PREC_BF16 will be used).
+ * rc_alt_corr_pyramid_fwd then takes fmap1 (hi, lo), HOST arrays of num_levels DEVICE pointers to
+ * the prepared fmap2 levels (level l = the (H>>l, W>>l) average-pooled fmap2, core/corr.py:68-72)
+ * and
+ *   coords : (B, 2, H, W) fp32 [x, y] at level-0 scale (divided by 2^l inside, core/corr.py:85)
+ *   out    : (B, num_levels*(2r+1)^2, H, W) fp32, fully overwritten, channel order as
+ *            rc_corr_lookup_fwd; multiplied by scale (0 -> 1/sqrt(C), core/corr.py:91)
+ *   plan   : device scratch of rc_alt_corr_pyramid_plan_bytes(...) bytes, 16 B aligned
+ * radius must be 4 and num_levels <= 4 (raft-things geometry); other shapes use rc_alt_corr_fwd.
+ */
+int rc_alt_prep_fmap(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, void *stream);
+size_t rc_alt_corr_pyramid_plan_bytes(int B, int H, int W, int num_levels);
+int rc_alt_corr_pyramid_fwd(const void *fmap1_hi, const void *fmap1_lo, const void *const *fmap2_hi,
+                            const void *const *fmap2_lo, const float *coords, float *out, int B, int H, int W,
+                            int C, int num_levels, int radius, int precision, float scale, void *plan,
+                            size_t plan_bytes, void *stream);
+
+/*
  * alt_cuda_corr.backward.
  * Replaces: alt_cuda_corr/correlation.cpp:36-48 -> correlation_kernel.cu:288-324 -> :122-256.
  *   corr_grad  : (B, N, (2r+1)^2, H1, W1)

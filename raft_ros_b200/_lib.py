@@ -84,6 +84,10 @@ SIGNATURES = {
     "rc_corr_build_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rc_corr_build_bwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_alt_prep_fmap": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "rc_alt_corr_pyramid_plan_bytes": (_sz, [_i, _i, _i, _i]),
+    "rc_alt_corr_pyramid_fwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i,
+                                     _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_bilinear_sampler_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_bilinear_sampler_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

@@ -286,12 +286,15 @@ class AlternateCorrBlock:
     """On-the-fly windowed correlation, no materialised volume (reference core/corr.py:63-91).
 
     `pyramid` keeps the reference's attribute: num_levels+1 pairs of average-pooled feature
-    maps.  Unlike the reference, the NHWC copies the kernel needs are made once here instead
-    of on every call (core/corr.py:82-83), and each level is one launch of the sm_100a kernel
-    behind `alt_cuda_corr.forward`.  Forward only, as in the reference.
+    maps.  With precision "bf16x3" (default, fp32-class) or "bf16" and the raft-things geometry
+    (radius 4, <= 4 levels, fmap1 and fmap2 of one shape) every call is ONE tensor-core launch
+    for all levels (rc_alt_corr_pyramid_fwd): the feature maps are converted once here, not
+    re-permuted on every call as in core/corr.py:82-83.  precision="fp32", other radii or shapes
+    use the per-level CUDA-core kernel behind `alt_cuda_corr.forward`.  Forward only, as in the
+    reference.
     """
 
-    def __init__(self, fmap1, fmap2, num_levels=4, radius=4):
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None):
         from torch.nn import functional as F
 
         self.num_levels = num_levels
@@ -303,10 +306,36 @@ class AlternateCorrBlock:
             fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
             fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
             self.pyramid.append((fmap1, fmap2))
-        self._f1_nhwc = _f32c(self.pyramid[0][0].permute(0, 2, 3, 1))
-        self._f2_nhwc = [_f32c(self.pyramid[i][1].permute(0, 2, 3, 1)) for i in range(self.num_levels)]
+        self._prec = _precision_code(precision)
+        f1, f2 = self.pyramid[0]
+        self._tc = (self._prec != _lib.RC_PREC_FP32 and radius == 4 and 1 <= num_levels <= 4
+                    and f1.shape == f2.shape and f1.dim() == 4)
+        if self._tc:
+            level_shapes(f1.shape[2], f1.shape[3], num_levels)  # raises if a level would be empty
+            want_lo = self._prec == _lib.RC_PREC_BF16X3
+            self._f1_tc = self._prep(f1, want_lo)
+            self._f2_tc = [self._prep(self.pyramid[i][1], want_lo) for i in range(num_levels)]
+        else:
+            self._f1_nhwc = _f32c(f1.permute(0, 2, 3, 1))
+            self._f2_nhwc = [_f32c(self.pyramid[i][1].permute(0, 2, 3, 1)) for i in range(self.num_levels)]
+
+    @staticmethod
+    def _prep(fmap, want_lo):
+        """(B,C,H,W) fp32 -> K-major bf16 hi (+ lo residual) for the TMA-fed tensor-core kernel."""
+        f = _f32c(fmap)
+        B, C, H, W = f.shape
+        Cp = (C + 63) // 64 * 64
+        with torch.cuda.device(f.device):
+            hi = torch.empty((B, H, W, Cp), dtype=torch.bfloat16, device=f.device)
+            lo = torch.empty_like(hi) if want_lo else None
+            rc = _lib.lib().rc_alt_prep_fmap(f.data_ptr(), hi.data_ptr(), lo.data_ptr() if want_lo else None,
+                                             B, C, H, W, _stream())
+            _lib.check(rc, "rc_alt_prep_fmap")
+        return hi, lo
 
     def __call__(self, coords):
+        if self._tc:
+            return self._call_tc(coords)
         from . import alt_cuda_corr
 
         coords = coords.permute(0, 2, 3, 1)
@@ -320,3 +349,26 @@ class AlternateCorrBlock:
         corr = torch.stack(corr_list, dim=1).reshape(B, -1, H, W)
         # the reference divides by torch.sqrt(torch.tensor(dim).float()): an fp32 square root
         return corr / float(torch.sqrt(torch.tensor(float(dim))))
+
+    def _call_tc(self, coords):
+        _require_cuda(coords, "coords")
+        c = _f32c(coords)
+        B, C, H, W = self.pyramid[0][0].shape
+        if tuple(c.shape) != (B, 2, H, W):
+            raise RuntimeError(f"coords must be {(B, 2, H, W)}, got {tuple(c.shape)}")
+        L = _lib.lib()
+        nl, rd = self.num_levels, 2 * self.radius + 1
+        x3 = self._prec == _lib.RC_PREC_BF16X3
+        with torch.cuda.device(c.device):
+            out = torch.empty((B, nl * rd * rd, H, W), dtype=torch.float32, device=c.device)
+            nbytes = int(L.rc_alt_corr_pyramid_plan_bytes(B, H, W, nl))
+            plan = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
+            f2_hi = _lib.ptr_array([t[0].data_ptr() for t in self._f2_tc])
+            f2_lo = _lib.ptr_array([t[1].data_ptr() if x3 else None for t in self._f2_tc])
+            # scale: the reference divides by an fp32 sqrt(dim) (core/corr.py:91)
+            scale = 1.0 / float(torch.sqrt(torch.tensor(float(C))))
+            rc = L.rc_alt_corr_pyramid_fwd(self._f1_tc[0].data_ptr(), self._f1_tc[1].data_ptr() if x3 else None,
+                                           f2_hi, f2_lo, c.data_ptr(), out.data_ptr(), B, H, W, C, nl, self.radius,
+                                           self._prec, scale, plan.data_ptr(), nbytes, _stream())
+            _lib.check(rc, "rc_alt_corr_pyramid_fwd")
+        return out

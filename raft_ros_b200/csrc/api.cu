@@ -188,6 +188,38 @@ int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords,
                         static_cast<cudaStream_t>(stream));
 }
 
+int rc_alt_prep_fmap(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, void *stream) {
+  RC_CHECK_ARG(fmap && hi, "rc_alt_prep_fmap: null pointer");
+  RC_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "rc_alt_prep_fmap: all sizes must be positive");
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(hi) & 15) == 0 && (reinterpret_cast<uintptr_t>(lo) & 15) == 0,
+               "rc_alt_prep_fmap: outputs must be 16-byte aligned");
+  return launch_alt_prep(fmap, hi, lo, B, C, H * W, static_cast<cudaStream_t>(stream));
+}
+
+size_t rc_alt_corr_pyramid_plan_bytes(int B, int H, int W, int num_levels) {
+  if (B <= 0 || H <= 0 || W <= 0 || num_levels <= 0) return 0;
+  return alt_tc_plan_bytes(B, H, W, num_levels);
+}
+
+int rc_alt_corr_pyramid_fwd(const void *fmap1_hi, const void *fmap1_lo, const void *const *fmap2_hi,
+                            const void *const *fmap2_lo, const float *coords, float *out, int B, int H, int W,
+                            int C, int num_levels, int radius, int precision, float scale, void *plan,
+                            size_t plan_bytes, void *stream) {
+  if (int rc = check_geometry("rc_alt_corr_pyramid_fwd", B, H, W, num_levels)) return rc;
+  RC_CHECK_ARG(fmap1_hi && fmap2_hi && coords && out, "rc_alt_corr_pyramid_fwd: null pointer");
+  RC_CHECK_ARG(precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16,
+               "rc_alt_corr_pyramid_fwd: precision must be RC_PREC_BF16X3 or RC_PREC_BF16");
+  RC_CHECK_ARG(precision == RC_PREC_BF16 || (fmap1_lo && fmap2_lo), "rc_alt_corr_pyramid_fwd: BF16X3 needs the lo parts");
+  RC_CHECK_ARG(C > 0, "rc_alt_corr_pyramid_fwd: C must be positive");
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(fmap2_hi[l] != nullptr, "rc_alt_corr_pyramid_fwd: level %d pointer is null", l);
+    RC_CHECK_ARG(precision == RC_PREC_BF16 || fmap2_lo[l] != nullptr, "rc_alt_corr_pyramid_fwd: level %d lo pointer is null", l);
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)C);
+  return launch_alt_tc(fmap1_hi, fmap1_lo, fmap2_hi, fmap2_lo, coords, out, B, H, W, (C + 63) / 64 * 64, num_levels,
+                       radius, precision, scale, plan, plan_bytes, static_cast<cudaStream_t>(stream));
+}
+
 int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
                     const float *corr_grad, float *fmap1_grad, float *fmap2_grad, int B, int N,
                     int H1, int W1, int H2, int W2, int C, int radius, void *stream) {

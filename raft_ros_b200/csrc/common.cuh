@@ -60,6 +60,11 @@ int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const 
                    float *g1, float *g2, int B, int N, int H1, int W1, int H2, int W2, int C,
                    int r, cudaStream_t st);
 
+int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW, cudaStream_t st);
+size_t alt_tc_plan_bytes(int B, int H1, int W1, int L);
+int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,
+                  const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius,
+                  int precision, float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st);
 int launch_pool_tail(const LevelPtrs &lv, int B, int h, int w, int first, int L, cudaStream_t st);
 int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
                         int H, int W, int Ho, int Wo, cudaStream_t st);

@@ -276,17 +276,33 @@ def test_alt_fwd_bwd_vs_oracle(rr, shape):
     assert tuple(gc.shape) == coords.shape and not bool(gc.any())
 
 
-def test_alternate_block_equals_corrblock(rr):
-    """AlternateCorrBlock(coords) == CorrBlock(coords) (reference README.md:109-114)."""
-    B, D, h, w = 2, 64, 24, 32
-    g = torch.Generator(device="cpu").manual_seed(1234)
-    f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
-    f2 = torch.randn(B, D, h, w, generator=g).to(DEV)
-    coords = rr.coords_grid(B, h, w, DEV) + 3.0 * torch.randn(B, 2, h, w, generator=g).to(DEV)
-    a = rr.CorrBlock(f1, f2, radius=4, precision="fp32")(coords)
-    b = rr.AlternateCorrBlock(f1, f2, radius=4)(coords)
-    assert a.shape == b.shape == (B, 324, h, w)
-    assert relmax(n(b), n(a)) <= 5e-6
+ALT_TOL = {"fp32": dict(rel=5e-6, norm=3e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16"])
+@pytest.mark.parametrize("geom", [(2, 64, 24, 32, 4), (1, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 256, 55, 128, 4)])
+@pytest.mark.parametrize("kind", ["sigma4", "sigma32", "grid", "oob", "huge"])
+def test_alternate_block_equals_corrblock(rr, geom, kind, precision):
+    """AlternateCorrBlock(coords) == CorrBlock(coords) (reference README.md:109-114), for the
+    per-level CUDA-core kernel (fp32) and the one-launch tensor-core kernel (bf16x3 / bf16),
+    coherent and incoherent flow, ragged tiles, windows off the map."""
+    B, D, h, w, L = geom
+    if kind in ("grid", "oob", "huge") and geom != (1, 256, 27, 40, 4):
+        pytest.skip("edge-case coordinates are exercised on one geometry")
+    rng = np.random.default_rng(seed_of(geom, kind))
+    f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    coords = t(make_coords(kind, B, h, w, rng))
+    a = rr.CorrBlock(f1, f2, num_levels=L, radius=4, precision="fp32")(coords)
+    blk = rr.AlternateCorrBlock(f1, f2, num_levels=L, radius=4, precision=precision)
+    assert len(blk.pyramid) == L + 1 and blk.pyramid[1][1].shape == (B, D, h // 2, w // 2)
+    b = blk(coords)
+    assert a.shape == b.shape == (B, L * 81, h, w) and b.dtype == torch.float32 and b.is_contiguous()
+    assert torch.isfinite(b).all()
+    tol = ALT_TOL[precision]
+    assert relmax(n(b), n(a)) <= tol["rel"], (geom, kind, precision, relmax(n(b), n(a)))
+    assert normwise(n(b), n(a)) <= tol["norm"], (geom, kind, precision, normwise(n(b), n(a)))
+    assert torch.equal(blk(coords), b)  # deterministic
 
 
 # ----------------------------------------------------------------------------- bilinear_sampler
