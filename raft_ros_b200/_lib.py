@@ -14,7 +14,7 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libraftcorr.so")
+LIB_PATH = os.environ.get("RAFTCORR_LIB") or os.path.join(_HERE, "libraftcorr.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "raftcorr.h")
 
 RC_OK = 0

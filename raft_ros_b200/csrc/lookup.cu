@@ -18,11 +18,17 @@
 
 namespace rc {
 
-constexpr int kLookupThreads = 128;
+#ifndef RC_LOOKUP_THREADS
+#define RC_LOOKUP_THREADS 128
+#endif
+#ifndef RC_LOOKUP_UNROLL
+#define RC_LOOKUP_UNROLL 4
+#endif
+constexpr int kLookupThreads = RC_LOOKUP_THREADS;
 constexpr int kLookupWarps = kLookupThreads / 32;
 constexpr int kTilePix = 32;
 constexpr int kPixPerWarp = kTilePix / kLookupWarps;  // 8
-constexpr int kUnroll = 4;                            // pixels in flight per warp
+constexpr int kUnroll = RC_LOOKUP_UNROLL < kPixPerWarp ? RC_LOOKUP_UNROLL : kPixPerWarp;  // pixels in flight per warp
 
 template <int R>
 __global__ void __launch_bounds__(kLookupThreads)
