@@ -427,3 +427,55 @@ def test_alt_vs_reference_binary(rr, shape):
     torch.cuda.synchronize()
     assert relmax(n(g1), n(w1)) <= 1e-5 and relmax(n(g2), n(w2)) <= 1e-5
     assert not bool(wc.any()) and not bool(gc.any())
+
+
+# ----------------------------------------------------------------------------- guard bands
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("geom", [(1, 96, 23, 39, 4), (2, 64, 17, 20, 4), (1, 256, 9, 130, 2)])
+def test_no_writes_outside_outputs(rr, geom, precision):
+    """compute-sanitizer is closed on this GPU pool, so out-of-bounds WRITES are checked with
+    guard bands: every output lives between two sentinel regions that must stay untouched, and
+    every output element must be overwritten (outputs are pre-filled with NaN)."""
+    from raft_ros_b200 import _lib
+    L_ = _lib.lib()
+    B, D, h, w, nl = geom
+    N, G = h * w, 4096
+    rng = np.random.default_rng(seed_of(geom))
+    f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    sizes = [B * N * (h >> l) * (w >> l) for l in range(nl)]
+    padded = [(s + 63) // 64 * 64 for s in sizes]
+    SENT = 1234.5
+    buf = torch.full((G * (nl + 1) + sum(padded),), SENT, device=DEV)
+    levels, off = [], G
+    for s, pz in zip(sizes, padded):
+        lv = buf[off:off + s]
+        lv.fill_(float("nan"))
+        levels.append(lv)
+        off += pz + G
+    prec = {"fp32": 0, "bf16x3": 1, "bf16": 2}[precision]
+    nbytes = int(L_.rc_corr_build_workspace_bytes(B, D, h, w, prec))
+    ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=DEV)
+    rc = L_.rc_corr_build_pyramid(f1.data_ptr(), f2.data_ptr(), B, D, h, w, _lib.ptr_array([x.data_ptr() for x in levels]),
+                                  nl, prec, 0.0, ws.data_ptr() if nbytes else None, nbytes, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L_.rc_last_error()
+    torch.cuda.synchronize()
+    for lv in levels:
+        assert torch.isfinite(lv).all(), "an output element was not written"
+    mask = torch.ones_like(buf, dtype=torch.bool)
+    off = G
+    for s, pz in zip(sizes, padded):
+        mask[off:off + s] = False
+        off += pz + G
+    assert bool((buf[mask] == SENT).all()), "write outside the pyramid levels"
+    # lookup output and on-the-fly output, same scheme
+    rd2 = 81
+    obuf = torch.full((2 * G + B * nl * rd2 * N,), SENT, device=DEV)
+    out = obuf[G:G + B * nl * rd2 * N]
+    out.fill_(float("nan"))
+    coords = t(make_coords("sigma4", B, h, w, rng))
+    rc = L_.rc_corr_lookup_fwd(_lib.ptr_array([x.data_ptr() for x in levels]), coords.data_ptr(), out.data_ptr(), B, h, w, nl, 4,
+                               torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L_.rc_last_error()
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all() and bool((obuf[:G] == SENT).all()) and bool((obuf[G + out.numel():] == SENT).all())
