@@ -47,20 +47,37 @@ def _stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo ... -shared -> libraftcorr.so"""
+    """nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo ... -shared -> libraftcorr.so
+
+    Safe to call from several processes at once (one rank per GPU under torchrun): the compile
+    runs under an exclusive file lock, into a temporary file that is renamed into place."""
     if not force and not _stale():
         return LIB_PATH
-    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    if not os.path.exists(nvcc):
-        nvcc = "nvcc"
-    # the image exports CC/CXX=/opt/gcc/...; nvcc picks its host compiler with -ccbin
-    ccbin = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    cmd = [nvcc, "-ccbin", ccbin] + NVCC_FLAGS + ["-shared", "-o", LIB_PATH] + sources()
-    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout)
-    if verbose:
-        print(res.stdout)
+    import fcntl
+
+    lock_path = os.path.join(_HERE, ".build.lock")
+    with open(lock_path, "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():  # another process built it while we waited
+                return LIB_PATH
+            nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+            if not os.path.exists(nvcc):
+                nvcc = "nvcc"
+            # the image exports CC/CXX=/opt/gcc/...; nvcc picks its host compiler with -ccbin
+            ccbin = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+            tmp = LIB_PATH + f".tmp{os.getpid()}"
+            cmd = [nvcc, "-ccbin", ccbin] + NVCC_FLAGS + ["-shared", "-o", tmp] + sources()
+            res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if res.returncode != 0:
+                if os.path.exists(tmp):
+                    os.remove(tmp)
+                raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout)
+            os.replace(tmp, LIB_PATH)
+            if verbose:
+                print(res.stdout)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
 
 
