@@ -74,29 +74,33 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
     t_src[k] = j * PN + i;
     t_dst[k] = t * TS;
   }
-  const size_t row_elems = (size_t)hl * wl;
-  const float *__restrict__ cxp = coords + ((size_t)b * 2 + 0) * N;
-  const float *__restrict__ cyp = coords + ((size_t)b * 2 + 1) * N;
+  const int row_elems = hl * wl;
+
+  // Per-pixel scalars (window origin, fractions, interior flag) are computed ONCE, by lane u for
+  // pixel u of this warp, from one coalesced coordinate load, and broadcast with shuffles; doing
+  // them redundantly in all 32 lanes was a quarter of the kernel's (issue-bound) instructions.
+  const int pw0 = p0 + warp * kPixPerWarp;
+  int my_x0 = 0, my_y0 = -(1 << 28), my_in = 0;  // invalid pixel: every element out of range -> zeros
+  float my_fx = 0.f, my_fy = 0.f;
+  if (lane < kPixPerWarp && pw0 + lane < N) {
+    const float cx = __ldg(coords + ((size_t)b * 2 + 0) * N + pw0 + lane) * inv;
+    const float cy = __ldg(coords + ((size_t)b * 2 + 1) * N + pw0 + lane) * inv;
+    my_x0 = safe_floor_int(cx, &my_fx) - R;
+    my_y0 = safe_floor_int(cy, &my_fy) - R;
+    my_in = (my_y0 >= 0 && my_x0 >= 0 && my_y0 + PN <= hl && my_x0 + PN <= wl) ? 1 : 0;
+  }
+  const float *__restrict__ base = vol + ((size_t)b * N + pw0) * (size_t)row_elems;  // pixel u: + u * row_elems
 
 #pragma unroll 1
   for (int g = 0; g < kPixPerWarp; g += kUnroll) {
     float v[kUnroll][NE];
-    float fx[kUnroll], fy[kUnroll];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
-      const int pix = warp * kPixPerWarp + g + u;
-      const int p = p0 + pix;
-      const bool pvalid = p < N;
-      float cx = 0.f, cy = 0.f;
-      if (pvalid) {
-        cx = __ldg(cxp + p) * inv;
-        cy = __ldg(cyp + p) * inv;
-      }
-      const int x0 = safe_floor_int(cx, &fx[u]) - R;
-      const int y0 = safe_floor_int(cy, &fy[u]) - R;
-      const float *row = vol + ((size_t)b * N + (pvalid ? p : 0)) * row_elems + (y0 * wl + x0);
+      const int x0 = __shfl_sync(0xffffffffu, my_x0, g + u);
+      const int y0 = __shfl_sync(0xffffffffu, my_y0, g + u);
+      const int interior = __shfl_sync(0xffffffffu, my_in, g + u);
+      const float *row = base + (g + u) * row_elems + (y0 * wl + x0);
       // whole (2r+2)^2 patch inside the level: no per-element bounds tests (warp-uniform branch)
-      const bool interior = pvalid && y0 >= 0 && x0 >= 0 && y0 + PN <= hl && x0 + PN <= wl;
       if (interior) {
 #pragma unroll
         for (int k = 0; k < NE; ++k)
@@ -104,7 +108,7 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
       } else {
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
-          const bool ok = pvalid && (lane + 32 * k < NPATCH) && (unsigned)(y0 + e_py[k]) < (unsigned)hl &&
+          const bool ok = (lane + 32 * k < NPATCH) && (unsigned)(y0 + e_py[k]) < (unsigned)hl &&
                           (unsigned)(x0 + e_px[k]) < (unsigned)wl;
           v[u][k] = ok ? ld_stream(row + e_rel[k]) : 0.0f;
         }
@@ -119,7 +123,7 @@ lookup_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const int pix = warp * kPixPerWarp + g + u;
-      const float dx = fx[u], dy = fy[u];
+      const float dx = __shfl_sync(0xffffffffu, my_fx, g + u), dy = __shfl_sync(0xffffffffu, my_fy, g + u);
       const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
       const float w10 = dy * (1.0f - dx), w11 = dy * dx;
       const float *pp = patch + u * NPATCH;
