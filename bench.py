@@ -62,6 +62,19 @@ def algorithmic_bytes(B, N, D, h, w, L, r, K):
     return build, lookup, build + K * lookup
 
 
+def measured_traffic(kernel, args):
+    """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed ncu capture
+    (profiles/traffic.json); only valid for the configuration it was captured on."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    default = (args.batch, args.height, args.width, args.dim, args.levels, args.radius, args.precision)
+    if default != (8, 440, 1024, 256, 4, 4, "bf16x3") or not os.path.exists(p):
+        return None
+    try:
+        return float(json.load(open(p))[kernel])
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -347,7 +360,7 @@ def run_ours(args):
     dom = "build" if build_ms >= look_ms * K else "lookup"
     roofline = {"bound": "hbm", "kernel": "build_tc_kernel (prep + fused volume/pyramid)" if dom == "build" else "lookup_fwd_kernel",
                 "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kern[dom]["gbs"] / peak,
-                "traffic": None, "peak_source": peak_src,
+                "traffic": measured_traffic(dom, args), "peak_source": peak_src,
                 "whole_step": {"alg_bytes": b_total, "gbs": b_total / (ms_step * 1e-3) / 1e9,
                                "frac": b_total / (ms_step * 1e-3) / 1e9 / peak}}
     line = {
