@@ -118,6 +118,16 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
                        int h, int w, int num_levels, int radius, void *stream);
 
 /*
+ * rc_corr_lookup_fwd on the TILED volume layout (RC_LAYOUT_TILED): level l of row p is stored as
+ * 4x4-float tiles, [ceil4(h>>l)/4][ceil4(w>>l)/4][4][4], zero padded.  Same coords / out contract;
+ * radius 4 only; levels 16-byte aligned.  No counterpart in the reference: it is the
+ * lookup-friendly internal layout of CorrBlock (a 10x10 window covers a few contiguous 64 B tiles
+ * instead of ten row segments that straddle DRAM fill granules).
+ */
+int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
+                             int h, int w, int num_levels, int radius, void *stream);
+
+/*
  * Gradient of the lookup w.r.t. the pyramid (coords carry no gradient: they are detached at
  * core/raft.py:123).  Replaces what autograd does through core/corr.py:45 /
  * F.grid_sample's backward, but deterministically: row p of every level is only ever

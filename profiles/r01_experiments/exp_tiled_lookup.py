@@ -1,6 +1,6 @@
 """Experiment: lookup on a 4x4-tiled copy of the pyramid vs the row layout (time + parity)."""
 import os, sys, torch
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import raft_ros_b200 as rr
 from raft_ros_b200 import _lib
 from raft_ros_b200.corr import build_pyramid_raw, lookup_raw

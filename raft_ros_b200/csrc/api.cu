@@ -129,6 +129,19 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
   return launch_lookup_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
+int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
+                             int h, int w, int num_levels, int radius, void *stream) {
+  if (int rc = check_geometry("rc_corr_lookup_tiled_fwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(level_ptrs && coords && out, "rc_corr_lookup_tiled_fwd: null pointer");
+  ConstLevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_lookup_tiled_fwd: level %d pointer is null", l);
+    RC_CHECK_ARG((reinterpret_cast<uintptr_t>(level_ptrs[l]) & 15) == 0, "rc_corr_lookup_tiled_fwd: level %d must be 16-byte aligned", l);
+    lv.p[l] = level_ptrs[l];
+  }
+  return launch_lookup_tiled_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
+}
+
 int rc_corr_lookup_bwd(const float *grad_out, const float *coords, float *const *grad_level_ptrs,
                        int B, int h, int w, int num_levels, int radius, void *stream) {
   if (int rc = check_geometry("rc_corr_lookup_bwd", B, h, w, num_levels)) return rc;

@@ -44,6 +44,8 @@ int launch_build_tc_noalloc(const float *f1, const float *f2, int B, int D, int 
                             const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st);
 int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
                       int w, int L, int r, cudaStream_t st);
+int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
+                            int w, int L, int r, cudaStream_t st);
 int launch_lookup_bwd(const float *gout, const float *coords, const LevelPtrs &glv, int B, int h,
                       int w, int L, int r, cudaStream_t st);
 size_t build_bwd_workspace_bytes(int B, int D, int h, int w);

@@ -479,3 +479,41 @@ def test_no_writes_outside_outputs(rr, geom, precision):
     assert rc == 0, L_.rc_last_error()
     torch.cuda.synchronize()
     assert torch.isfinite(out).all() and bool((obuf[:G] == SENT).all()) and bool((obuf[G + out.numel():] == SENT).all())
+
+
+# ----------------------------------------------------------------------------- tiled volume layout
+def _tile_levels(levels):
+    """(P,1,hl,wl) rows -> [P][ceil4(hl)/4][ceil4(wl)/4][4][4] zero-padded tiles (test-side conversion)."""
+    out = []
+    for lv in levels:
+        P, _, hl, wl = lv.shape
+        hp, wp = (hl + 3) // 4 * 4, (wl + 3) // 4 * 4
+        x = torch.nn.functional.pad(lv.view(P, hl, wl), (0, wp - wl, 0, hp - hl))
+        out.append(x.view(P, hp // 4, 4, wp // 4, 4).permute(0, 1, 3, 2, 4).contiguous())
+    return out
+
+
+@pytest.mark.parametrize("kind", ["grid", "sigma4", "sigma32", "oob", "border", "huge"])
+@pytest.mark.parametrize("geom", [(2, 27, 40, 4), (1, 23, 39, 3), (1, 55, 128, 4), (3, 16, 16, 4)])
+def test_lookup_on_tiled_layout(rr, geom, kind):
+    """rc_corr_lookup_tiled_fwd (4x4-tiled volume rows, cp.async-fed persistent kernel) gives the
+    row-layout lookup's result on every geometry, including widths / heights that need padding."""
+    from raft_ros_b200 import _lib
+    from raft_ros_b200.corr import lookup_raw
+    B, h, w, L = geom
+    rng = np.random.default_rng(seed_of(geom, kind))
+    levels = [t(rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32)) for hl, wl in O.level_shapes(h, w, L)]
+    coords = t(make_coords(kind, B, h, w, rng))
+    want = lookup_raw(levels, coords, 4)
+    tiles = _tile_levels(levels)
+    out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
+    lib = _lib.lib()
+    rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),
+                                      B, h, w, L, 4, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.rc_last_error()
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    assert relmax(n(out), n(want)) <= 2e-6, (geom, kind, relmax(n(out), n(want)))
+    rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),
+                                      B, h, w, L, 3, torch.cuda.current_stream().cuda_stream)
+    assert rc == 3 and b"radius" in lib.rc_last_error()
