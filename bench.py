@@ -47,6 +47,9 @@ def parse():
                     choices=["fp32", "bf16x3", "bf16"])
     ap.add_argument("--l2-fetch", type=int, default=int(os.environ.get("RAFT_CORR_L2_FETCH", "0")),
                     help="set cudaLimitMaxL2FetchGranularity (32/64/128); 0 = leave the driver default")
+    ap.add_argument("--layout", default=os.environ.get("RAFT_CORR_LAYOUT", "tiled"), choices=["tiled", "rows"],
+                    help="HBM layout of the pyramid: 'tiled' is what CorrBlock keeps for inference, "
+                         "'rows' the reference's (B*h*w,1,h_l,w_l) arrays")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
@@ -62,7 +65,7 @@ def algorithmic_bytes(B, N, D, h, w, L, r, K):
     return build, lookup, build + K * lookup
 
 
-def measured_traffic(kernel, args):
+def measured_traffic(kernel, args, layout="rows"):
     """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed ncu capture
     (profiles/traffic.json); only valid for the configuration it was captured on."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -70,7 +73,8 @@ def measured_traffic(kernel, args):
     if default != (8, 440, 1024, 256, 4, 4, "bf16x3") or not os.path.exists(p):
         return None
     try:
-        return float(json.load(open(p))[kernel])
+        d = json.load(open(p))
+        return float(d[layout][kernel]) if layout in d else (float(d[kernel]) if layout == "rows" else None)
     except Exception:
         return None
 
@@ -226,7 +230,12 @@ def run_ours(args):
 
     import raft_ros_b200 as rr
     from raft_ros_b200 import _lib
-    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw
+    from raft_ros_b200.corr import build_pyramid_raw, build_pyramid_tiled_raw, lookup_raw, lookup_tiled_raw
+
+    tiled = args.layout == "tiled" and args.precision != "fp32" and args.radius == 4 and args.levels <= 4
+    os.environ["RAFT_CORR_LAYOUT"] = "tiled" if tiled else "rows"  # the e2e arm's CorrBlock follows
+    build_fn = build_pyramid_tiled_raw if tiled else build_pyramid_raw
+    look_fn = lookup_tiled_raw if tiled else lookup_raw
 
     _lib.build()
     _lib.lib()  # fail loudly if the CUDA library is missing
@@ -272,12 +281,12 @@ def run_ours(args):
         if timed:
             e0, e1, e2 = ev(), ev(), ev()
             e0.record()
-        levels = build_pyramid_raw(f1, f2, L, args.precision)
+        levels = build_fn(f1, f2, L, args.precision)
         if timed:
             e1.record()
         out = None
         for k in range(K):
-            out = lookup_raw(levels, coords[k], r)
+            out = look_fn(levels, coords[k], r)
         if timed:
             e2.record()
             build_ev.append((e0, e1))
@@ -358,9 +367,10 @@ def run_ours(args):
                    "share_of_step": look_ms * K / ms_step},
     }
     dom = "build" if build_ms >= look_ms * K else "lookup"
-    roofline = {"bound": "hbm", "kernel": "build_tc_kernel (prep + fused volume/pyramid)" if dom == "build" else "lookup_fwd_kernel",
+    roofline = {"bound": "hbm", "kernel": "build_tc_kernel (prep + fused volume/pyramid)" if dom == "build"
+                else ("lookup_tiled_fwd_kernel" if tiled else "lookup_fwd_kernel"),
                 "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kern[dom]["gbs"] / peak,
-                "traffic": measured_traffic(dom, args), "peak_source": peak_src,
+                "traffic": measured_traffic(dom, args, "tiled" if tiled else "rows"), "peak_source": peak_src,
                 "whole_step": {"alg_bytes": b_total, "gbs": b_total / (ms_step * 1e-3) / 1e9,
                                "frac": b_total / (ms_step * 1e-3) / 1e9 / peak}}
     line = {
@@ -369,7 +379,7 @@ def run_ours(args):
         "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup"}[args.precision],
         "data": "synthetic", "config": workload_config(args, "gpu"), "precision": args.precision,
         "roofline": roofline, "kernels": kern, "clocks": clocks, "gpu_launches": int(args.steps * (2 + K)),
-        "l2_fetch_granularity": l2_fetch,
+        "l2_fetch_granularity": l2_fetch, "layout": "tiled" if tiled else "rows",
     }
     if e2e is not None:
         line["e2e"] = e2e

@@ -89,6 +89,78 @@ def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
     return levels
 
 
+def tiled_plane_elems(hl: int, wl: int) -> int:
+    """floats per row p of a level in the tiled layout (include/raftcorr.h: rc_corr_tiled_plane_elems)."""
+    return ((hl + 1) & ~1) * ((wl + 7) & ~7)
+
+
+def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
+                            precision: Optional[str] = None, scale: float = 0.0) -> List[torch.Tensor]:
+    """rc_corr_build_pyramid_tiled: (B,D,h,w) x2 -> list of (B*h*w, plane_l) fp32 in the TILED layout."""
+    _require_cuda(fmap1, "fmap1")
+    _require_cuda(fmap2, "fmap2")
+    if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
+        raise RuntimeError(f"fmap1/fmap2 must both be (B,D,h,w); got {tuple(fmap1.shape)} and {tuple(fmap2.shape)}")
+    if fmap1.device != fmap2.device:
+        raise RuntimeError("fmap1 and fmap2 must be on the same device")
+    f1, f2 = _f32c(fmap1), _f32c(fmap2)
+    B, D, h, w = f1.shape
+    shapes = level_shapes(h, w, num_levels)
+    prec = _precision_code(precision)
+    L = _lib.lib()
+    with torch.cuda.device(f1.device):
+        planes = [tiled_plane_elems(hl, wl) for hl, wl in shapes]
+        sizes = [B * h * w * pl for pl in planes]  # multiples of 16 floats: every level stays 64 B aligned
+        flat = torch.empty(sum(sizes), dtype=torch.float32, device=f1.device)
+        levels, o = [], 0
+        for s_, pl in zip(sizes, planes):
+            levels.append(flat[o:o + s_].view(B * h * w, pl))
+            o += s_
+        ws_bytes = int(L.rc_corr_build_workspace_bytes(B, D, h, w, prec))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=f1.device)
+        rc = L.rc_corr_build_pyramid_tiled(f1.data_ptr(), f2.data_ptr(), B, D, h, w,
+                                           _lib.ptr_array([lv.data_ptr() for lv in levels]), num_levels, prec,
+                                           float(scale), ws.data_ptr(), ws_bytes, _stream())
+        _lib.check(rc, "rc_corr_build_pyramid_tiled")
+        ws.record_stream(torch.cuda.current_stream())
+    return levels
+
+
+def relayout_raw(src: torch.Tensor, rows: int, hl: int, wl: int, to_tiled: bool) -> torch.Tensor:
+    """rc_corr_relayout_level: one level, row layout (rows, 1, hl, wl) <-> tiled layout (rows, plane)."""
+    _require_cuda(src, "level")
+    s = src if (src.dtype == torch.float32 and src.is_contiguous()) else _f32c(src)
+    with torch.cuda.device(s.device):
+        if to_tiled:
+            dst = torch.empty((rows, tiled_plane_elems(hl, wl)), dtype=torch.float32, device=s.device)
+        else:
+            dst = torch.empty((rows, 1, hl, wl), dtype=torch.float32, device=s.device)
+        rc = _lib.lib().rc_corr_relayout_level(s.data_ptr(), dst.data_ptr(), rows, hl, wl, 1 if to_tiled else 0, _stream())
+        _lib.check(rc, "rc_corr_relayout_level")
+    return dst
+
+
+def lookup_tiled_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radius: int) -> torch.Tensor:
+    """rc_corr_lookup_tiled_fwd: lookup_raw on levels kept in the tiled layout."""
+    _require_cuda(coords, "coords")
+    if coords.dim() != 4 or coords.shape[1] != 2:
+        raise RuntimeError(f"coords must be (B,2,h,w); got {tuple(coords.shape)}")
+    c = _f32c(coords)
+    B, _, h, w = c.shape
+    nl = len(levels)
+    shapes = level_shapes(h, w, nl)
+    for l, (t, (hl, wl)) in enumerate(zip(levels, shapes)):
+        if t.numel() != B * h * w * tiled_plane_elems(hl, wl) or t.dtype != torch.float32 or not t.is_contiguous():
+            raise RuntimeError(f"tiled level {l} does not match a {B}x{h}x{w} problem")
+    rd = 2 * radius + 1
+    with torch.cuda.device(c.device):
+        out = torch.empty((B, nl * rd * rd, h, w), dtype=torch.float32, device=c.device)
+        rc = _lib.lib().rc_corr_lookup_tiled_fwd(_lib.ptr_array([t.data_ptr() for t in levels]), c.data_ptr(),
+                                                 out.data_ptr(), B, h, w, nl, radius, _stream())
+        _lib.check(rc, "rc_corr_lookup_tiled_fwd")
+    return out
+
+
 def lookup_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radius: int) -> torch.Tensor:
     """rc_corr_lookup_fwd: (B,2,h,w) coords -> (B, L*(2r+1)^2, h, w) fp32, one launch."""
     _require_cuda(coords, "coords")
@@ -251,6 +323,12 @@ class CorrBlock:
     the reference; it is produced by ONE kernel launch (contraction, 1/sqrt(D) scale and every
     pooling level fused, each level written once).  `precision` is an extension: see
     DEFAULT_PRECISION.
+
+    Inference (no gradient wanted, radius 4, <= 4 levels, a tensor-core precision) keeps the
+    pyramid in the TILED layout (include/raftcorr.h) that the lookup kernel reads with 35 % less
+    DRAM traffic; `corr_pyramid` then converts to the reference's row layout on first access (a
+    copy: writing into it does not change what the lookups read -- assign `corr_pyramid` to
+    replace the pyramid).  RAFT_CORR_LAYOUT=rows keeps the row layout throughout.
     """
 
     def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None):
@@ -259,17 +337,39 @@ class CorrBlock:
         self.precision = precision
         self._state = None
         self._token = None
+        self._tiled = None      # tiled levels (inference fast path) or None
+        self._rows = None       # row-layout levels (reference attribute), lazily made from _tiled
+        self._geom = None
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
             self._state = _GradState()
             out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state)
-            self._token, self.corr_pyramid = out[0], list(out[1:])
+            self._token, self._rows = out[0], list(out[1:])
+        elif (radius == 4 and 1 <= num_levels <= 4 and _precision_code(precision) != _lib.RC_PREC_FP32
+              and os.environ.get("RAFT_CORR_LAYOUT", "tiled") != "rows"):
+            self._tiled = build_pyramid_tiled_raw(fmap1, fmap2, num_levels, precision)
+            self._geom = (fmap1.shape[0], fmap1.shape[2], fmap1.shape[3])
         else:
-            self.corr_pyramid = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
+            self._rows = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
+
+    @property
+    def corr_pyramid(self):
+        if self._rows is None:
+            B, h, w = self._geom
+            self._rows = [relayout_raw(t, B * h * w, hl, wl, to_tiled=False)
+                          for t, (hl, wl) in zip(self._tiled, level_shapes(h, w, self.num_levels))]
+        return self._rows
+
+    @corr_pyramid.setter
+    def corr_pyramid(self, levels):
+        self._rows = list(levels)
+        self._tiled = None  # the lookups follow the assigned pyramid
 
     def __call__(self, coords):
         if self._token is not None and torch.is_grad_enabled():
             return _LookupTokenFn.apply(coords, self._token, self._state, self.radius)
-        return lookup_raw(self.corr_pyramid, coords, self.radius)
+        if self._tiled is not None:
+            return lookup_tiled_raw(self._tiled, coords, self.radius)
+        return lookup_raw(self._rows, coords, self.radius)
 
     @staticmethod
     def corr(fmap1, fmap2, precision=None):

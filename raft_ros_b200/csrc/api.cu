@@ -129,6 +129,42 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
   return launch_lookup_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
+int rc_corr_tiled_plane_elems(int h, int w, int level, size_t *elems) {
+  RC_CHECK_ARG(elems, "rc_corr_tiled_plane_elems: null output");
+  int hl = 0, wl = 0;
+  if (int rc = rc_level_dims(h, w, level, &hl, &wl)) return rc;
+  *elems = (size_t)((hl + 1) & ~1) * (size_t)((wl + 7) & ~7);
+  return RC_OK;
+}
+
+int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
+                                float *const *level_ptrs, int num_levels, int precision, float scale,
+                                void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_geometry("rc_corr_build_pyramid_tiled", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && level_ptrs, "rc_corr_build_pyramid_tiled: null pointer");
+  RC_CHECK_ARG(D > 0, "rc_corr_build_pyramid_tiled: D must be positive");
+  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16) {
+    set_error("rc_corr_build_pyramid_tiled: only the tensor-core precisions write the tiled layout (got %d)",
+              precision);
+    return RC_ERR_UNSUPPORTED;
+  }
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_build_pyramid_tiled: level %d pointer is null", l);
+    lv.p[l] = level_ptrs[l];
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  return launch_build_tc_tiled(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale, workspace,
+                               workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_relayout_level(const float *src, float *dst, long long rows, int hl, int wl, int to_tiled,
+                           void *stream) {
+  RC_CHECK_ARG(src && dst, "rc_corr_relayout_level: null pointer");
+  RC_CHECK_ARG(rows > 0 && hl > 0 && wl > 0, "rc_corr_relayout_level: bad shape");
+  return launch_relayout(src, dst, rows, hl, wl, to_tiled != 0, static_cast<cudaStream_t>(stream));
+}
+
 int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
                              int h, int w, int num_levels, int radius, void *stream) {
   if (int rc = check_geometry("rc_corr_lookup_tiled_fwd", B, h, w, num_levels)) return rc;

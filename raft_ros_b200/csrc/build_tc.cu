@@ -56,6 +56,7 @@ struct Params {
   long long total_tiles;
   float scale;
   int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
+  int plane[4], tws[4];         // TILED output only: floats per row p of level l / per tile-row of it
   LevelPtrs lv;
 };
 
@@ -74,7 +75,12 @@ struct Cfg {
                                     256 /*barriers*/;
 };
 
-template <int NPASS, int NCTA>
+// TILED: every row p of a level is written as [hp/2][wp/8] tiles of 2 rows x 8 floats (hp = ceil2,
+// wp = ceil8 of the level's size, zeros in the padding that a lookup can touch) -- the layout
+// lookup_tiled.cu reads.  It costs the epilogue nothing: a warp's row pair of the 8x32 patch IS
+// four whole tiles, 256 contiguous bytes per query pixel, and every row p starts 64 B aligned
+// whatever h and w are, so the stores are whole 128 B lines for ragged sizes too.
+template <int NPASS, int NCTA, bool TILED>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
@@ -233,7 +239,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     uint32_t acc_phase = 0;
     const int h = P.h, w = P.w, N = P.N, L = P.L;
     const int h1 = h >> 1, w1 = w >> 1, h2 = h >> 2, w2 = w >> 2, h3 = h >> 3, w3 = w >> 3;
-    const size_t pitch0 = (size_t)h * w, pitch1 = (size_t)h1 * w1, pitch2 = (size_t)h2 * w2, pitch3 = (size_t)h3 * w3;
+    const size_t pitch0 = TILED ? (size_t)P.plane[0] : (size_t)h * w, pitch1 = TILED ? (size_t)P.plane[1] : (size_t)h1 * w1,
+                 pitch2 = TILED ? (size_t)P.plane[2] : (size_t)h2 * w2, pitch3 = TILED ? (size_t)P.plane[3] : (size_t)h3 * w3;
     const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;
     bool peer_pending = false;  // hf=1: our staging buffer still holds the level-2 row for the peer
     for (long long t = unit0; t < P.total_tiles; t += unit_step) {
@@ -246,10 +253,13 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const int rows_valid = min(32, N - prow0);         // may be <= 0
       const size_t grow0 = (size_t)b * N + prow0;        // first row of the volume for this warp
       const int x0 = nx * PW;
-      float *const g0 = P.lv.p[0] + grow0 * pitch0 + x0;
-      float *const g1 = P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
-      float *const g2 = P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
-      float *const g3 = P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
+      // row layout: first element of this warp's patch columns in row grow0 of each level;
+      // tiled layout: first tile of them (tile-row 0)
+      float *const g0 = TILED ? P.lv.p[0] + grow0 * pitch0 + nx * 64 : P.lv.p[0] + grow0 * pitch0 + x0;
+      float *const g1 = TILED ? P.lv.p[1] + grow0 * pitch1 + nx * 32 : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
+      float *const g2 = TILED ? P.lv.p[2] + grow0 * pitch2 + nx * 16 : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
+      float *const g3 = TILED ? P.lv.p[3] + (grow0 + lane) * pitch3 + (nx >> 1) * 16 + (nx & 1) * 4
+                              : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN + hf * (TN / 2));
@@ -280,8 +290,28 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           v1[i] *= P.scale;
         }
         const int y0 = ny * PH + hf * 4 + 2 * j;
-        if (y0 < h) store_rows<32>(buf, v0, lane, g0 + (size_t)y0 * w, pitch0, rows_valid, w - x0, vec0);
-        if (y0 + 1 < h) store_rows<32>(buf, v1, lane, g0 + (size_t)(y0 + 1) * w, pitch0, rows_valid, w - x0, vec0);
+        if constexpr (TILED) {
+          // rows y0, y0+1 = one tile-row; columns beyond w (and row h of an odd h) are zero accumulators
+          if (y0 < h) {
+            float *const gt = g0 + (size_t)(y0 >> 1) * P.tws[0];
+            const int tiles = (P.tws[0] >> 4) - nx * 4;  // tiles of this tile-row from the patch's first one on
+#pragma unroll
+            for (int c2 = 0; c2 < 2; ++c2) {
+              float ch[32];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                ch[i] = v0[16 * c2 + i];
+                ch[8 + i] = v1[16 * c2 + i];
+                ch[16 + i] = v0[16 * c2 + 8 + i];
+                ch[24 + i] = v1[16 * c2 + 8 + i];
+              }
+              store_rows<32>(buf, ch, lane, gt + c2 * 32, pitch0, rows_valid, (tiles - 2 * c2) * 16, true);
+            }
+          }
+        } else {
+          if (y0 < h) store_rows<32>(buf, v0, lane, g0 + (size_t)y0 * w, pitch0, rows_valid, w - x0, vec0);
+          if (y0 + 1 < h) store_rows<32>(buf, v1, lane, g0 + (size_t)(y0 + 1) * w, pitch0, rows_valid, w - x0, vec0);
+        }
         if (L > 1) {
           float l1[16];
 #pragma unroll
@@ -292,12 +322,33 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             l1[i] = s * 0.25f;
           }
           const int y1 = ny * (PH / 2) + hf * 2 + j;
-          if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
-          if (L > 2) {
+          if constexpr (TILED) {
+            // pooled cells that hang over the level's edge (odd sizes) are padding: they must read as zero
+            if ((nx + 1) * 16 > w1 || y1 >= h1) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (nx * 16 + i >= w1 || y1 >= h1) l1[i] = 0.0f;
+            }
+            if (j == 1 && y1 - 1 < h1) {
+              float ch[32];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                ch[i] = l1prev[i];
+                ch[8 + i] = l1[i];
+                ch[16 + i] = l1prev[8 + i];
+                ch[24 + i] = l1[8 + i];
+              }
+              store_rows<32>(buf, ch, lane, g1 + (size_t)(y1 >> 1) * P.tws[1], pitch1, rows_valid,
+                             ((P.tws[1] >> 4) - nx * 2) * 16, true);
+            }
+          } else {
+            if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
+          }
+          if (L > 2 || TILED) {
             if (j == 0) {
 #pragma unroll
               for (int i = 0; i < 16; ++i) l1prev[i] = l1[i];
-            } else {
+            } else if (L > 2) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 float s = l1prev[2 * i] + l1prev[2 * i + 1];
@@ -306,7 +357,19 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 l2[i] = s * 0.25f;
               }
               const int y2 = ny * (PH / 4) + hf;
-              if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
+              if constexpr (TILED) {
+                if ((nx + 1) * 8 > w2 || y2 >= h2) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i)
+                    if (nx * 8 + i >= w2 || y2 >= h2) l2[i] = 0.0f;
+                }
+                // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
+                if (2 * ny < h2)
+                  store_rows<8>(buf, l2, lane, g2 + (size_t)ny * P.tws[2] + hf * 8, pitch2, rows_valid,
+                                nx < (P.tws[2] >> 4) ? 8 : 0, true);
+              } else {
+                if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
+              }
             }
           }
         }
@@ -333,7 +396,14 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             l3[i] = s * 0.25f;
           }
           const int cv3 = w3 - (x0 >> 3);
-          if (ny < h3 && lane < rows_valid) {
+          if constexpr (TILED) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (i >= cv3 || ny >= h3) l3[i] = 0.0f;
+            // a quarter of a level-3 tile: row ny & 1, columns 4 (nx & 1) .. +3 (16 B, always aligned)
+            if (ny < ((h3 + 1) & ~1) && (nx >> 1) < (P.tws[3] >> 4) && lane < rows_valid)
+              stg128(g3 + (size_t)(ny >> 1) * P.tws[3] + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
+          } else if (ny < h3 && lane < rows_valid) {
             float *d = g3 + (size_t)ny * w3;
             if (vec3 && cv3 >= 4) {
               stg128(d, make_float4(l3[0], l3[1], l3[2], l3[3]));
@@ -434,12 +504,12 @@ static int sm_count() {
   return n;
 }
 
-template <int NPASS, int NCTA>
+template <int NPASS, int NCTA, bool TILED>
 static int launch(const CUtensorMap &ah, const CUtensorMap &al, const CUtensorMap &bh, const CUtensorMap &bl,
                   const Params &P, cudaStream_t st) {
   using C = Cfg<NPASS, NCTA>;
   static_assert(C::kSmemBytes <= 227 * 1024, "shared memory budget");
-  auto kern = build_tc_kernel<NPASS, NCTA>;
+  auto kern = build_tc_kernel<NPASS, NCTA, TILED>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   const long long units = sm_count() / NCTA;  // one CTA (or CTA pair) per SM (per TPC)
   const unsigned grid = (unsigned)((P.total_tiles < units ? P.total_tiles : units) * NCTA);
@@ -480,8 +550,9 @@ size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision) {
   return aligned * 2 * (precision == RC_PREC_BF16X3 ? 2 : 1);
 }
 
-int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv, int L,
-                    int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st) {
+static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv,
+                                int L, int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st,
+                                bool tiled) {
   using namespace tc;
   const size_t need = build_tc_workspace_bytes(B, D, h, w, precision);
   if (ws == nullptr || ws_bytes < need) {
@@ -540,14 +611,79 @@ int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w
     if (wl % 4 == 0 && (a & 15) == 0) P.vec_mask |= 1 << l;
   }
   for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
+  for (int l = 0; l < 4; ++l) {
+    const int hp = ((h >> l) + 1) & ~1, wp = ((w >> l) + 7) & ~7;
+    P.plane[l] = hp * wp;
+    P.tws[l] = wp * 2;
+  }
 
   int rc;
+  if (tiled) {
+    if (L > 4) {
+      set_error("rc_corr_build_pyramid_tiled: at most 4 levels (got %d)", L);
+      return RC_ERR_UNSUPPORTED;
+    }
+    for (int l = 0; l < L; ++l)
+      if ((reinterpret_cast<uintptr_t>(lv.p[l]) & 63) != 0) {
+        set_error("rc_corr_build_pyramid_tiled: level %d must be 64-byte aligned", l);
+        return RC_ERR_INVALID;
+      }
+    if (ncta == 2)
+      rc = x3 ? tc::launch<3, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st);
+    else
+      rc = x3 ? tc::launch<3, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st);
+    return rc;
+  }
   if (ncta == 2)
-    rc = x3 ? tc::launch<3, 2>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2>(tmAh, tmAl, tmBh, tmBl, P, st);
+    rc = x3 ? tc::launch<3, 2, false>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2, false>(tmAh, tmAl, tmBh, tmBl, P, st);
   else
-    rc = x3 ? tc::launch<3, 1>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1>(tmAh, tmAl, tmBh, tmBl, P, st);
+    rc = x3 ? tc::launch<3, 1, false>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1, false>(tmAh, tmAl, tmBh, tmBl, P, st);
   if (rc) return rc;
   if (L > 4) return launch_pool_tail(lv, B, h, w, 4, L, st);
+  return RC_OK;
+}
+
+int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv, int L,
+                    int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st) {
+  return launch_build_tc_impl(f1, f2, B, D, h, w, lv, L, precision, scale, ws, ws_bytes, st, false);
+}
+
+int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv, int L,
+                          int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st) {
+  return launch_build_tc_impl(f1, f2, B, D, h, w, lv, L, precision, scale, ws, ws_bytes, st, true);
+}
+
+// ------------------------------------------------------------------ tiled <-> row layout of one level
+// `rows` = B*N rows p of a level of hl x wl floats; the tiled plane of a row is [hp/2][wp/8][2][8].
+// The loop walks the TILED array (the padded, larger one): converting to it writes every padding
+// element (zero), converting from it skips them.
+template <bool TO_TILED>
+__global__ void __launch_bounds__(256)
+relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, long long rows, int hl, int wl) {
+  const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tpr = wp >> 3;
+  const long long plane = (long long)hp * wp, total = rows * plane;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long p = i / plane;
+    const int e = (int)(i - p * plane);
+    const int tile = e >> 4, in = e & 15;
+    const int ty = tile / tpr, tx = tile - ty * tpr;
+    const int y = ty * 2 + (in >> 3), x = tx * 8 + (in & 7);
+    const bool inside = y < hl && x < wl;
+    const long long r = p * (long long)hl * wl + (long long)y * wl + x;
+    if (TO_TILED) dst[i] = inside ? __ldg(src + r) : 0.0f;
+    else if (inside) dst[r] = __ldg(src + i);
+  }
+}
+
+int launch_relayout(const float *src, float *dst, long long rows, int hl, int wl, bool to_tiled, cudaStream_t st) {
+  const long long plane = (long long)((hl + 1) & ~1) * ((wl + 7) & ~7);
+  const long long total = rows * plane;
+  if (total <= 0) return RC_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148LL * 32) blocks = 148LL * 32;
+  if (to_tiled) relayout_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src, dst, rows, hl, wl);
+  else relayout_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src, dst, rows, hl, wl);
+  RC_CUDA(cudaGetLastError());
   return RC_OK;
 }
 

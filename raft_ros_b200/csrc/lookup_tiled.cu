@@ -1,12 +1,14 @@
 // Pyramid lookup on the TILED volume layout (r = 4): warp-autonomous, persistent, cp.async-fed.
 //
 // Same result as lookup_fwd_kernel<4> (reference core/corr.py:29-50).  Every row p of a level is
-// stored as 4x4-float tiles (64 B each, tiles of a tile-row contiguous, the plane padded to
-// multiples of 4 with zeros) instead of h_l rows of w_l floats:
-//     level l of row p : [hp/4][wp/4][4][4] floats, hp = ceil4(h>>l), wp = ceil4(w>>l)
-// A 10x10 window then lies in 3-4 x 3-4 tiles, i.e. in a few contiguous 192-256 B runs, instead
-// of ten 40 B segments that each straddle DRAM fill granules: measured DRAM reads per launch drop
-// from 235 MB to 147 MB (batch 8 @ 55x128; 91 MB algorithmic).
+// stored as tiles of 2 rows x 8 floats (64 B each, the tiles of a tile-row contiguous, the plane
+// padded with zeros to an even height and a width that is a multiple of 8) instead of h_l rows
+// of w_l floats:
+//     level l of row p : [hp/2][wp/8][2][8] floats, hp = ceil2(h>>l), wp = ceil8(w>>l)
+// A 10x10 window then lies in 5-6 x 2-3 tiles, i.e. in a few contiguous 128-192 B runs, instead
+// of ten 40 B segments that each straddle DRAM fill granules, and every row p starts 64 B aligned
+// whatever w is.  The 2x8 shape is what the build epilogue produces for free: a warp's row pair
+// is 4 whole tiles = 256 contiguous bytes per query pixel (build_tc.cu).
 //
 // Work item = 8 consecutive query pixels of one level, owned by ONE warp (no block-level sync):
 //   fetch   lane u (< 8) loads pixel u's coordinates and keeps its window origin / fractions;
@@ -47,7 +49,7 @@ __device__ __forceinline__ void cp_async_wait() {
 struct TlCtx {
   int lvl, b, p0, valid;
   int x0, y0;      // window origin
-  int poff, xmask; // copy scalars: element offset of (pixel row, first x-tile); which of the 4 x-tiles to fetch
+  int poff;        // copy scalar: element offset of the pixel's row p inside the 8-pixel block
   float fx, fy;
 };
 
@@ -59,11 +61,11 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   const int N = h * w;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float *ring = smem + warp * (kTlStages * kTlStageFloats);
-  const int lr = lane >> 2, lx = lane & 3;  // copy role: patch row 0..7, x-tile 0..3
+  const int lr = lane >> 2, lx = lane & 3;  // copy role: patch row 0..7, 16 B piece 0..3 of the row
   const int tu = lane >> 2, tc = lane & 3;  // tap role: pixel 0..7, column pair 0..3
 
   auto fetch = [&](int it) {
-    TlCtx c{0, 0, 0, 0, 0, -(1 << 28), 0, 0, 0.f, 0.f};  // invalid pixel: no x-tile wanted -> zero patch
+    TlCtx c{0, 0, 0, 0, 0, -(1 << 28), 0, 0.f, 0.f};  // invalid pixel: every row out of range -> zero patch
     if (it < total_items) {
       const int per_level = B * groups_per_item;  // level-major: same-level work is contiguous
       c.lvl = it / per_level;
@@ -79,13 +81,8 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
         c.x0 = safe_floor_int(cx, &c.fx) - R;
         c.y0 = safe_floor_int(cy, &c.fy) - R;
         const int hl = h >> c.lvl, wl = w >> c.lvl;
-        const int hp = (hl + 3) & ~3, wp = (wl + 3) & ~3, twn = wp >> 2;
-        const int tx0 = c.x0 >> 2;  // arithmetic shift = floor division
-        c.poff = lane * (hp * wp) + tx0 * 16;
-        const int ntx = (c.x0 & 3) == 3 ? 4 : 3;  // the 4th x-tile only matters at offset 3
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (k < ntx && (unsigned)(tx0 + k) < (unsigned)twn) c.xmask |= 1 << k;
+        const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7;
+        c.poff = lane * (hp * wp);
       }
     }
     return c;
@@ -100,18 +97,21 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   auto issue = [&](const TlCtx &c, int stage) {
     if (c.valid) {
       const int hl = h >> c.lvl, wl = w >> c.lvl;
-      const int hp = (hl + 3) & ~3, wp = (wl + 3) & ~3, tws = (wp >> 2) * 16;
+      const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tws = wp * 2;  // floats per tile-row
+      const int wb = (wl + 3) & ~3;
       const float *base = pick_level(lv, c.lvl) + ((size_t)c.b * N + c.p0) * (size_t)(hp * wp);
       const unsigned dst0 = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u;
-      // rows 0..7 of every pixel: lane (lr, lx) copies (row lr, x-tile lx); src-size 0 zero-fills
+      // rows 0..7 of every pixel: lane (lr, lx) copies columns xg+4lx .. +3 of row lr, xg = x0 rounded down
+      // to a multiple of 4 (the 4th piece only matters at offset 3); src-size 0 zero-fills.  The
+      // build zeroes columns wl .. ceil4(wl)-1, so whole pieces are fetched up to that bound.
 #pragma unroll
       for (int u = 0; u < kTlPix; ++u) {
         const int poff = __shfl_sync(0xffffffffu, c.poff, u);
         const int y0 = __shfl_sync(0xffffffffu, c.y0, u);
-        const int xm = __shfl_sync(0xffffffffu, c.xmask, u);
-        const int ya = y0 + lr;
-        const bool ok = ((xm >> lx) & 1) && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? poff + lx * 16 + (ya >> 2) * tws + (ya & 3) * 4 : 0;
+        const int x0 = __shfl_sync(0xffffffffu, c.x0, u);
+        const int ya = y0 + lr, cg = (x0 & ~3) + 4 * lx;
+        const bool ok = (lx < 3 || (x0 & 3) == 3) && (unsigned)cg < (unsigned)wb && (unsigned)ya < (unsigned)hl;
+        const int off = ok ? poff + (ya >> 1) * tws + (cg >> 3) * 16 + (ya & 1) * 8 + (cg & 7) : 0;
         copy16(dst0 + (unsigned)(u * kTlPatch) * 4u + dst_lane, base + off, ok);
       }
       // rows 8..9: one instruction serves 4 pixels (lane rows 2k, 2k+1 -> pixel 4*half + k)
@@ -120,10 +120,10 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
         const int u = half * 4 + (lr >> 1);
         const int poff = __shfl_sync(0xffffffffu, c.poff, u);
         const int y0 = __shfl_sync(0xffffffffu, c.y0, u);
-        const int xm = __shfl_sync(0xffffffffu, c.xmask, u);
-        const int yb = y0 + 8 + (lr & 1);
-        const bool ok = ((xm >> lx) & 1) && (unsigned)yb < (unsigned)hl;
-        const int off = ok ? poff + lx * 16 + (yb >> 2) * tws + (yb & 3) * 4 : 0;
+        const int x0 = __shfl_sync(0xffffffffu, c.x0, u);
+        const int yb = y0 + 8 + (lr & 1), cg = (x0 & ~3) + 4 * lx;
+        const bool ok = (lx < 3 || (x0 & 3) == 3) && (unsigned)cg < (unsigned)wb && (unsigned)yb < (unsigned)hl;
+        const int off = ok ? poff + (yb >> 1) * tws + (cg >> 3) * 16 + (yb & 1) * 8 + (cg & 7) : 0;
         copy16(dst0 + (unsigned)(u * kTlPatch) * 4u + dst_tail, base + off, ok);
       }
     }

@@ -483,20 +483,121 @@ def test_no_writes_outside_outputs(rr, geom, precision):
 
 # ----------------------------------------------------------------------------- tiled volume layout
 def _tile_levels(levels):
-    """(P,1,hl,wl) rows -> [P][ceil4(hl)/4][ceil4(wl)/4][4][4] zero-padded tiles (test-side conversion)."""
+    """(P,1,hl,wl) rows -> [P][ceil2(hl)/2][ceil8(wl)/8][2][8] zero-padded tiles (test-side conversion in torch)."""
     out = []
     for lv in levels:
         P, _, hl, wl = lv.shape
-        hp, wp = (hl + 3) // 4 * 4, (wl + 3) // 4 * 4
+        hp, wp = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8
         x = torch.nn.functional.pad(lv.view(P, hl, wl), (0, wp - wl, 0, hp - hl))
-        out.append(x.view(P, hp // 4, 4, wp // 4, 4).permute(0, 1, 3, 2, 4).contiguous())
+        out.append(x.view(P, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 2, 4).contiguous())
     return out
+
+
+@pytest.mark.parametrize("shape", [(7, 5, 9), (3, 16, 32), (5, 1, 1), (2, 23, 39)])
+def test_relayout_level_round_trip(rr, shape):
+    """rc_corr_relayout_level: rows -> tiled equals the torch conversion (padding zeroed), and back is exact."""
+    from raft_ros_b200.corr import relayout_raw
+    P, hl, wl = shape
+    rng = np.random.default_rng(seed_of(shape))
+    rows = t(rng.standard_normal((P, 1, hl, wl)).astype(np.float32))
+    tiled = relayout_raw(rows, P, hl, wl, to_tiled=True)
+    assert torch.equal(tiled.view(-1), _tile_levels([rows])[0].view(-1))
+    assert torch.equal(relayout_raw(tiled, P, hl, wl, to_tiled=False), rows)
+
+
+TILED_GEOMS = [(1, 64, 8, 32, 4), (2, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 256, 47, 156, 4), (1, 128, 17, 20, 4),
+               (2, 256, 16, 18, 2), (1, 64, 9, 65, 1), (1, 256, 55, 128, 4)]
+
+
+@pytest.mark.parametrize("prec", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("geom", TILED_GEOMS)
+def test_tiled_build_equals_row_build(rr, geom, prec):
+    """rc_corr_build_pyramid_tiled writes, tile by tile, exactly the numbers rc_corr_build_pyramid writes
+    row by row (same accumulators, same pooling order), zeros in the padding a lookup can reach, and the
+    tiled lookup on it equals the row lookup -- with every buffer pre-filled with NaN, so anything the
+    kernels read but never wrote would show."""
+    from raft_ros_b200 import _lib
+    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw, relayout_raw, tiled_plane_elems, _PRECISIONS
+    B, D, h, w, L = geom
+    rng = np.random.default_rng(seed_of(geom, prec))
+    f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    rows = build_pyramid_raw(f1, f2, L, prec)
+    lib = _lib.lib()
+    shapes = O.level_shapes(h, w, L)
+    N = h * w
+    tiled = [torch.full((B * N, tiled_plane_elems(hl, wl)), float("nan"), device=DEV) for hl, wl in shapes]
+    code = _PRECISIONS[prec]
+    ws_bytes = int(lib.rc_corr_build_workspace_bytes(B, D, h, w, code))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    rc = lib.rc_corr_build_pyramid_tiled(f1.data_ptr(), f2.data_ptr(), B, D, h, w,
+                                         _lib.ptr_array([x.data_ptr() for x in tiled]), L, code, 0.0, ws.data_ptr(),
+                                         ws_bytes, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.rc_last_error()
+    torch.cuda.synchronize()
+    for l, (hl, wl) in enumerate(shapes):
+        back = relayout_raw(tiled[l], B * N, hl, wl, to_tiled=False)
+        assert torch.equal(back, rows[l]), (geom, prec, l)
+        hp, wp = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8
+        grid = tiled[l].view(B * N, hp // 2, wp // 8, 2, 8).permute(0, 1, 3, 2, 4).reshape(B * N, hp, wp)
+        wb = (wl + 3) // 4 * 4
+        assert bool((grid[:, :hl, wl:wb] == 0).all()), (geom, prec, l, "padding columns a lookup fetches must be zero")
+    for kind in ("sigma4", "border", "oob"):
+        coords = t(make_coords(kind, B, h, w, rng))
+        out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
+        rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiled]), coords.data_ptr(),
+                                          out.data_ptr(), B, h, w, L, 4, torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, lib.rc_last_error()
+        want = lookup_raw(rows, coords, 4)
+        assert torch.isfinite(out).all(), (geom, prec, kind)
+        assert relmax(n(out), n(want)) <= 2e-6, (geom, prec, kind, relmax(n(out), n(want)))
+
+
+def test_tiled_build_rejects(rr):
+    from raft_ros_b200 import _lib
+    lib = _lib.lib()
+    f = torch.zeros((1, 64, 32, 32), device=DEV)
+    lv = [torch.zeros(1 << 22, device=DEV) for _ in range(5)]
+    ws = torch.empty(1 << 22, dtype=torch.uint8, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.rc_corr_build_pyramid_tiled(f.data_ptr(), f.data_ptr(), 1, 64, 32, 32, _lib.ptr_array([x.data_ptr() for x in lv[:4]]),
+                                         4, 0, 0.0, ws.data_ptr(), ws.numel(), st)
+    assert rc == 3 and b"tensor-core" in lib.rc_last_error()
+    rc = lib.rc_corr_build_pyramid_tiled(f.data_ptr(), f.data_ptr(), 1, 64, 32, 32, _lib.ptr_array([x.data_ptr() for x in lv]),
+                                         5, 1, 0.0, ws.data_ptr(), ws.numel(), st)
+    assert rc == 3 and b"4 levels" in lib.rc_last_error()
+    rc = lib.rc_corr_build_pyramid_tiled(f.data_ptr(), f.data_ptr(), 1, 64, 32, 32,
+                                         _lib.ptr_array([lv[0].data_ptr() + 16] + [x.data_ptr() for x in lv[1:4]]),
+                                         4, 1, 0.0, ws.data_ptr(), ws.numel(), st)
+    assert rc == 1 and b"aligned" in lib.rc_last_error()
+
+
+def test_corrblock_layouts_agree(rr, monkeypatch):
+    """CorrBlock's inference path (tiled) and RAFT_CORR_LAYOUT=rows give the same lookups and the same
+    `corr_pyramid`; assigning `corr_pyramid` redirects the lookups, as with the reference's attribute."""
+    from raft_ros_b200.corr import CorrBlock
+    rng = np.random.default_rng(77)
+    B, D, h, w = 2, 256, 27, 41
+    f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    coords = t(make_coords("sigma4", B, h, w, rng))
+    blk = CorrBlock(f1, f2)
+    assert blk._tiled is not None
+    monkeypatch.setenv("RAFT_CORR_LAYOUT", "rows")
+    ref = CorrBlock(f1, f2)
+    assert ref._tiled is None
+    a, b = blk(coords), ref(coords)
+    assert relmax(n(a), n(b)) <= 2e-6
+    for x, y in zip(blk.corr_pyramid, ref.corr_pyramid):
+        assert x.shape == y.shape and torch.equal(x, y)
+    blk.corr_pyramid = [torch.zeros_like(x) for x in blk.corr_pyramid]
+    assert float(blk(coords).abs().max()) == 0.0
 
 
 @pytest.mark.parametrize("kind", ["grid", "sigma4", "sigma32", "oob", "border", "huge"])
 @pytest.mark.parametrize("geom", [(2, 27, 40, 4), (1, 23, 39, 3), (1, 55, 128, 4), (3, 16, 16, 4)])
 def test_lookup_on_tiled_layout(rr, geom, kind):
-    """rc_corr_lookup_tiled_fwd (4x4-tiled volume rows, cp.async-fed persistent kernel) gives the
+    """rc_corr_lookup_tiled_fwd (2x8-tiled volume rows, cp.async-fed persistent kernel) gives the
     row-layout lookup's result on every geometry, including widths / heights that need padding."""
     from raft_ros_b200 import _lib
     from raft_ros_b200.corr import lookup_raw
