@@ -212,13 +212,21 @@ int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float
     return RC_ERR_UNSUPPORTED;
   }
   const size_t smem = sizeof(float) * (size_t)(kTlWarps * kTlStages * kTlStageFloats);
-  RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int dev = 0, sms = 0, ctas_per_sm = 0;
+  // resident CTAs per device: asked once per device (this runs every RAFT iteration)
+  static int resident[64] = {};
+  int dev = 0;
   RC_CUDA(cudaGetDevice(&dev));
-  RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel, kTlThreads, smem));
-  if (ctas_per_sm < 1) ctas_per_sm = 1;
-  long long grid = (long long)sms * ctas_per_sm;
+  int cached = (dev >= 0 && dev < 64) ? __atomic_load_n(&resident[dev], __ATOMIC_ACQUIRE) : 0;
+  if (cached == 0) {
+    int sms = 0, ctas_per_sm = 0;
+    RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel, kTlThreads, smem));
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    cached = sms * ctas_per_sm;
+    if (dev >= 0 && dev < 64) __atomic_store_n(&resident[dev], cached, __ATOMIC_RELEASE);
+  }
+  long long grid = cached;
   const long long need = (total + kTlWarps - 1) / kTlWarps;
   if (grid > need) grid = need;
   lookup_tiled_fwd_kernel<<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);

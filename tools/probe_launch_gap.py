@@ -1,0 +1,43 @@
+"""How much of a lookup's in-loop time is host launch overhead?  Times N back-to-back lookups on the
+GPU (events) and the host-side cost of issuing them (wall clock, no sync inside)."""
+import time
+import torch
+import raft_ros_b200 as rr
+from raft_ros_b200 import _lib
+from raft_ros_b200.corr import build_pyramid_tiled_raw, lookup_tiled_raw, build_pyramid_raw, lookup_raw
+
+dev = torch.device("cuda:0")
+B, D, h, w = 8, 256, 55, 128
+g = torch.Generator().manual_seed(0)
+f1 = torch.randn(B, D, h, w, generator=g).to(dev)
+f2 = torch.randn(B, D, h, w, generator=g).to(dev)
+coords = (rr.coords_grid(B, h, w, "cpu") + 2 * torch.randn(B, 2, h, w, generator=g)).to(dev)
+for name, bf, lf in (("tiled", build_pyramid_tiled_raw, lookup_tiled_raw), ("rows", build_pyramid_raw, lookup_raw)):
+    lv = bf(f1, f2, 4, "bf16x3")
+    for _ in range(5):
+        lf(lv, coords, 4)
+    torch.cuda.synchronize()
+    n = 200
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(n):
+        lf(lv, coords, 4)
+    e1.record()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    print(f"{name}: gpu {e0.elapsed_time(e1) / n * 1e3:.1f} us/launch, host issue {(t1 - t0) / n * 1e6:.1f} us/call")
+    # raw C call only, preallocated output
+    out = torch.empty((B, 4 * 81, h, w), device=dev)
+    pa = _lib.ptr_array([t.data_ptr() for t in lv])
+    fn = _lib.lib().rc_corr_lookup_tiled_fwd if name == "tiled" else _lib.lib().rc_corr_lookup_fwd
+    st = torch.cuda.current_stream().cuda_stream
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(n):
+        fn(pa, coords.data_ptr(), out.data_ptr(), B, h, w, 4, 4, st)
+    e1.record()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    print(f"{name}: C ABI only: gpu {e0.elapsed_time(e1) / n * 1e3:.1f} us/launch, host issue {(t1 - t0) / n * 1e6:.1f} us/call")
