@@ -10,11 +10,13 @@
 // whatever w is.  The 2x8 shape is what the build epilogue produces for free: a warp's row pair
 // is 4 whole tiles = 256 contiguous bytes per query pixel (build_tc.cu).
 //
-// Work item = 8 consecutive query pixels of one level, owned by ONE warp (no block-level sync):
-//   fetch   lane u (< 8) loads pixel u's coordinates and keeps its window origin / fractions;
-//   issue   the 8 patches (10 rows x 16 floats) are copied global -> shared with cp.async
-//           (16 B per lane, zero-filled outside the map) into a two-stage ring: the copies of
-//           item i+1 are in flight while item i is consumed;
+// Work item = 8 consecutive query pixels of one level, owned by ONE warp (no block-level sync, no
+// shuffles: lane = pixel x quarter in every phase):
+//   fetch   the 4 lanes of pixel u load its coordinates (one iteration ahead of their use) and
+//           derive the window origin / fractions;
+//   issue   lane (u, k) copies the k-th 16 B piece of the 10 rows of pixel u's patch global ->
+//           shared with cp.async (zero-filled outside the map) into a two-stage ring: the copies
+//           of item i+1 are in flight while item i is consumed;
 //   taps    lane (u, c) owns window columns 2c, 2c+1 (and a share of column 8) of pixel u:
 //           separable bilinear interpolation from registers, 21 taps per lane;
 //   store   straight from registers: the 8 pixels of a warp are contiguous in the output, so every
@@ -28,6 +30,14 @@ namespace rc {
 #endif
 #ifndef RC_TL_PS
 #define RC_TL_PS 20
+#endif
+#ifndef RC_TL_EXP
+#define RC_TL_EXP 0  // profiling experiments only: 1 = no output stores, 2 = no volume reads
+#endif
+#if RC_TL_EXP == 1
+#define RC_TL_ST(p, v) do { const float v_ = (v); if (v_ == 1.2345e30f) st_stream((p), v_); } while (0)
+#else
+#define RC_TL_ST(p, v) st_stream((p), (v))
 #endif
 constexpr int kTlWarps = 4, kTlThreads = kTlWarps * 32, kTlPix = 8, kTlStages = RC_TL_STAGES;
 constexpr int kTlPS = RC_TL_PS;                 // patch row stride (floats): 16 fetched (+ pad), 16 B aligned
@@ -45,11 +55,16 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-// One decoded work item plus the per-pixel scalars, lane u (< 8) holding pixel u's.
+// One work item as seen by lane (u, k), u = lane >> 2 the pixel, k = lane & 3: the item's place in
+// the problem (warp-uniform) and pixel u's window.  The four lanes of a pixel hold the same values
+// (they load the same coordinates), so neither the copies nor the taps need a shuffle.
+struct TlRaw {
+  int lvl, b, p0, valid;
+  float cx, cy;
+};
 struct TlCtx {
   int lvl, b, p0, valid;
-  int x0, y0;      // window origin
-  int poff;        // copy scalar: element offset of the pixel's row p inside the 8-pixel block
+  int x0, y0;  // window origin (y0 far outside for a pixel beyond the image: every row zero-filled)
   float fx, fy;
 };
 
@@ -61,99 +76,101 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   const int N = h * w;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float *ring = smem + warp * (kTlStages * kTlStageFloats);
-  const int lr = lane >> 2, lx = lane & 3;  // copy role: patch row 0..7, 16 B piece 0..3 of the row
-  const int tu = lane >> 2, tc = lane & 3;  // tap role: pixel 0..7, column pair 0..3
+  const int tu = lane >> 2, tc = lane & 3;  // pixel 0..7 of the item; 16 B piece of a patch row / column pair
 
-  auto fetch = [&](int it) {
-    TlCtx c{0, 0, 0, 0, 0, -(1 << 28), 0, 0.f, 0.f};  // invalid pixel: every row out of range -> zero patch
-    if (it < total_items) {
-      const int per_level = B * groups_per_item;  // level-major: same-level work is contiguous
-      c.lvl = it / per_level;
-      const int rem = it - c.lvl * per_level;
-      c.b = rem / groups_per_item;
-      c.p0 = (rem - c.b * groups_per_item) * kTlPix;
-      c.valid = 1;
-      const int p = c.p0 + lane;
-      if (lane < kTlPix && p < N) {
-        const float inv = 1.0f / (float)(1 << c.lvl);
-        const float cx = __ldg(coords + ((size_t)c.b * 2 + 0) * N + p) * inv;
-        const float cy = __ldg(coords + ((size_t)c.b * 2 + 1) * N + p) * inv;
-        c.x0 = safe_floor_int(cx, &c.fx) - R;
-        c.y0 = safe_floor_int(cy, &c.fy) - R;
-        const int hl = h >> c.lvl, wl = w >> c.lvl;
-        const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7;
-        c.poff = lane * (hp * wp);
+  // ---- item decoder: items are numbered level-major (lvl, b, group); a warp visits it0, it0 + stride, ...
+  // The decoder runs ahead of the pipeline and advances by `stride` with carries instead of divisions.
+  const int stride = gridDim.x * kTlWarps;
+  const int it0 = blockIdx.x * kTlWarps + warp;
+  const int per_level = B * groups_per_item;
+  int dl = it0 / per_level, db = (it0 - dl * per_level) / groups_per_item, dg = it0 - dl * per_level - db * groups_per_item;
+  const int s_l = stride / per_level, s_b = (stride - s_l * per_level) / groups_per_item,
+            s_g = stride - s_l * per_level - s_b * groups_per_item;
+  auto next_raw = [&]() {
+    TlRaw r{dl, db, dg * kTlPix, dl < L ? 1 : 0, 0.f, 0.f};
+    if (r.valid) {
+      const int p = r.p0 + tu;
+      if (p < N) {
+        // the 4 lanes of a pixel read the same word: one 32 B sector per plane for the warp
+        r.cx = __ldg(coords + ((size_t)r.b * 2 + 0) * N + p);
+        r.cy = __ldg(coords + ((size_t)r.b * 2 + 1) * N + p);
       }
+    }
+    dg += s_g;
+    if (dg >= groups_per_item) { dg -= groups_per_item; ++db; }
+    db += s_b;
+    if (db >= B) { db -= B; ++dl; }
+    dl += s_l;
+    return r;
+  };
+  auto resolve = [&](const TlRaw &r) {
+    TlCtx c{r.lvl, r.b, r.p0, r.valid, 0, -(1 << 28), 0.f, 0.f};
+    if (r.valid && r.p0 + tu < N) {
+      const float inv = 1.0f / (float)(1 << r.lvl);
+      c.x0 = safe_floor_int(r.cx * inv, &c.fx) - R;
+      c.y0 = safe_floor_int(r.cy * inv, &c.fy) - R;
     }
     return c;
   };
 
   const unsigned ring_u32 = static_cast<unsigned>(__cvta_generic_to_shared(ring));
-  const unsigned dst_lane = (unsigned)(lr * PS + lx * 4) * 4u;           // rows 0..7
-  const unsigned dst_tail = (unsigned)((8 + (lr & 1)) * PS + lx * 4) * 4u;  // rows 8..9
+  const unsigned dst_lane = (unsigned)(tu * kTlPatch + tc * 4) * 4u;
   auto copy16 = [&](unsigned dst, const float *src, bool ok) {
+#if RC_TL_EXP == 2
+    ok = false;
+#endif
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
   };
+  // Copies of one item: lane (u, k) fetches columns xg+4k .. +3 of the 10 window rows of pixel u,
+  // xg = x0 rounded down to a multiple of 4 (the 4th piece only matters at offset 3).  src-size 0
+  // zero-fills: rows outside the level, pieces outside it (the build zeroes columns wl ..
+  // ceil4(wl)-1, so whole pieces are fetched up to that bound), pixels beyond the image.
   auto issue = [&](const TlCtx &c, int stage) {
     if (c.valid) {
       const int hl = h >> c.lvl, wl = w >> c.lvl;
       const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tws = wp * 2;  // floats per tile-row
       const int wb = (wl + 3) & ~3;
-      const float *base = pick_level(lv, c.lvl) + ((size_t)c.b * N + c.p0) * (size_t)(hp * wp);
-      const unsigned dst0 = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u;
-      // rows 0..7 of every pixel: lane (lr, lx) copies columns xg+4lx .. +3 of row lr, xg = x0 rounded down
-      // to a multiple of 4 (the 4th piece only matters at offset 3); src-size 0 zero-fills.  The
-      // build zeroes columns wl .. ceil4(wl)-1, so whole pieces are fetched up to that bound.
+      const int cg = (c.x0 & ~3) + 4 * tc;
+      const bool okx = (tc < 3 || (c.x0 & 3) == 3) && (unsigned)cg < (unsigned)wb;
+      // for a pixel beyond the image `base` points past the level, but y0 is then far outside: no
+      // row is in range and the copy below is handed the level-0 pointer with src-size 0
+      const size_t prow = (size_t)c.b * N + c.p0 + tu;
+      const float *base = pick_level(lv, c.lvl) + prow * (size_t)(hp * wp) + ((cg >> 3) * 16 + (cg & 7));
+      const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
-      for (int u = 0; u < kTlPix; ++u) {
-        const int poff = __shfl_sync(0xffffffffu, c.poff, u);
-        const int y0 = __shfl_sync(0xffffffffu, c.y0, u);
-        const int x0 = __shfl_sync(0xffffffffu, c.x0, u);
-        const int ya = y0 + lr, cg = (x0 & ~3) + 4 * lx;
-        const bool ok = (lx < 3 || (x0 & 3) == 3) && (unsigned)cg < (unsigned)wb && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? poff + (ya >> 1) * tws + (cg >> 3) * 16 + (ya & 1) * 8 + (cg & 7) : 0;
-        copy16(dst0 + (unsigned)(u * kTlPatch) * 4u + dst_lane, base + off, ok);
-      }
-      // rows 8..9: one instruction serves 4 pixels (lane rows 2k, 2k+1 -> pixel 4*half + k)
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int u = half * 4 + (lr >> 1);
-        const int poff = __shfl_sync(0xffffffffu, c.poff, u);
-        const int y0 = __shfl_sync(0xffffffffu, c.y0, u);
-        const int x0 = __shfl_sync(0xffffffffu, c.x0, u);
-        const int yb = y0 + 8 + (lr & 1), cg = (x0 & ~3) + 4 * lx;
-        const bool ok = (lx < 3 || (x0 & 3) == 3) && (unsigned)cg < (unsigned)wb && (unsigned)yb < (unsigned)hl;
-        const int off = ok ? poff + (yb >> 1) * tws + (cg >> 3) * 16 + (yb & 1) * 8 + (cg & 7) : 0;
-        copy16(dst0 + (unsigned)(u * kTlPatch) * 4u + dst_tail, base + off, ok);
+      for (int r = 0; r < 10; ++r) {
+        const int ya = c.y0 + r;
+        const bool ok = okx && (unsigned)ya < (unsigned)hl;
+        const int off = ok ? (ya >> 1) * tws + (ya & 1) * 8 : 0;
+        copy16(dst + (unsigned)(r * PS) * 4u, ok ? base + off : pick_level(lv, 0), ok);
       }
     }
     cp_async_commit();  // always commit (possibly empty) so that the wait counts stay uniform
   };
 
-  const int stride = gridDim.x * kTlWarps;
-  int it = blockIdx.x * kTlWarps + warp;
   // ring of kTlStages patch buffers: while item i is consumed, items i+1 .. i+D are in flight
   constexpr int D = kTlStages - 1;
   TlCtx q_[D + 1];  // q_[0] = item being consumed, q_[d] = item d steps ahead (coordinates resolved)
 #pragma unroll
-  for (int d = 0; d <= D; ++d) q_[d] = fetch(it + d * stride);
+  for (int d = 0; d <= D; ++d) q_[d] = resolve(next_raw());
+  TlRaw raw = next_raw();
 #pragma unroll
   for (int d = 0; d < D; ++d) issue(q_[d], d);
   int stage = 0;
   const int CH = L * NTAP;
 
-  for (; it < total_items; it += stride) {
-    const TlCtx nn = fetch(it + (D + 1) * stride);  // coordinates D+1 items ahead
+  for (int it = it0; it < total_items; it += stride) {
+    const TlCtx nn = resolve(raw);  // item D+1 ahead: its coordinates were loaded an iteration ago
+    raw = next_raw();
     issue(q_[D], (stage + D) % kTlStages);
     cp_async_wait<D>();
     __syncwarp();
     const TlCtx cur = q_[0];
 
-    // ---- taps: lane (tu, tc)
-    const float dx = __shfl_sync(0xffffffffu, cur.fx, tu), dy = __shfl_sync(0xffffffffu, cur.fy, tu);
-    const int off = __shfl_sync(0xffffffffu, cur.x0, tu) & 3;
+    // ---- taps: lane (tu, tc) owns window columns 2tc, 2tc+1 and a share of column 8 of pixel tu
+    const float dx = cur.fx, dy = cur.fy;
     const float ex = 1.0f - dx, ey = 1.0f - dy;
-    const float *pp = ring + stage * kTlStageFloats + tu * kTlPatch + off;
+    const float *pp = ring + stage * kTlStageFloats + tu * kTlPatch + (cur.x0 & 3);
     const int p = cur.p0 + tu;
     float *o = out + ((size_t)cur.b * CH + (size_t)cur.lvl * NTAP) * N + p;
     const bool pv = p < N;
@@ -171,8 +188,8 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
         float *o0 = o + (size_t)(2 * tc * RD) * N;
 #pragma unroll
         for (int j = 0; j < RD; ++j) {
-          st_stream(o0 + (size_t)j * N, fmaf(h0[j + 1], dy, h0[j] * ey));
-          st_stream(o0 + (size_t)(RD + j) * N, fmaf(h1[j + 1], dy, h1[j] * ey));
+          RC_TL_ST(o0 + (size_t)j * N, fmaf(h0[j + 1], dy, h0[j] * ey));
+          RC_TL_ST(o0 + (size_t)(RD + j) * N, fmaf(h1[j + 1], dy, h1[j] * ey));
         }
       }
     }
@@ -185,7 +202,7 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
         if (j < RD && (k < 2 || tc == 0)) {
           const float a = q[j * PS], b = q[j * PS + 1], c2 = q[(j + 1) * PS], d2 = q[(j + 1) * PS + 1];
           const float top = fmaf(b, dx, a * ex), bot = fmaf(d2, dx, c2 * ex);
-          if (pv) st_stream(o + (size_t)(8 * RD + j) * N, fmaf(bot, dy, top * ey));
+          if (pv) RC_TL_ST(o + (size_t)(8 * RD + j) * N, fmaf(bot, dy, top * ey));
         }
       }
     }
