@@ -119,30 +119,33 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
 
 /*
  * The TILED volume layout (no counterpart in the reference; it is what CorrBlock keeps internally
- * when no gradient is wanted).  Level l of row p -- h_l x w_l floats in the row layout -- is
- * stored as tiles of 2 rows x 8 floats:
- *     [hp/2][wp/8][2][8],   hp = h_l rounded up to 2,  wp = w_l rounded up to 8,
- * hp*wp floats per row p (rc_corr_tiled_plane_elems), zeros in every padding element a lookup can
- * reach.  A 10x10 lookup window then covers a few contiguous 64 B tiles instead of ten 40 B row
- * segments that straddle DRAM fill granules (-35 % DRAM reads per lookup), and every row p starts
- * 64 B aligned whatever h and w are, so the build writes whole 128 B lines for ragged sizes too
- * (2.4x faster build at 47x156).
+ * when no gradient is wanted).  Level l of row p = (b, query pixel q) -- h_l x w_l floats in the
+ * row layout -- is cut into tiles of 2 rows x 8 floats (64 B), and the tiles of 8 consecutive
+ * query pixels are interleaved:
+ *     [B][ceil(h*w/8)][hp/2][wp/8][8 pixels][2][8],  hp = h_l rounded up to 2, wp = w_l rounded up to 8,
+ * rc_corr_tiled_level_elems floats per level, zeros in every padding element a lookup can
+ * reach.  A 10x10 lookup window then covers a few 64 B tiles instead of ten 40 B row segments
+ * that straddle DRAM fill granules (-28 % DRAM reads per lookup); neighbouring query pixels look
+ * at neighbouring places, so the 8 copies of a tile that a group of pixels needs are 512
+ * contiguous bytes; and every tile is 64 B aligned whatever h and w are, so the build writes
+ * whole 128 B lines for ragged sizes too (2.3x faster build at 47x156).
  *
  * rc_corr_build_pyramid_tiled : rc_corr_build_pyramid writing that layout.  RC_PREC_BF16X3 /
  *                     RC_PREC_BF16 only, num_levels <= 4, level pointers 64-byte aligned and
- *                     B*h*w*plane_elems(l) floats each.  Same workspace as the row-layout build.
+ *                     rc_corr_tiled_level_elems floats each.  Same workspace as the row-layout build.
  * rc_corr_lookup_tiled_fwd    : rc_corr_lookup_fwd reading it.  Same coords / out contract;
  *                     radius 4 only.
- * rc_corr_relayout_level      : converts one level between the layouts (to_tiled != 0: rows ->
- *                     tiled, padding zeroed; 0: tiled -> rows).  rows = B*h*w.
+ * rc_corr_relayout_level      : converts one level (hl x wl per row, N = h*w query pixels per batch
+ *                     item) between the layouts (to_tiled != 0: rows -> tiled, padding zeroed;
+ *                     0: tiled -> rows).
  */
-int rc_corr_tiled_plane_elems(int h, int w, int level, size_t *elems);
+int rc_corr_tiled_level_elems(int B, int h, int w, int level, size_t *elems);
 int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
                                 float *const *level_ptrs, int num_levels, int precision, float scale,
                                 void *workspace, size_t workspace_bytes, void *stream);
 int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,
                              int h, int w, int num_levels, int radius, void *stream);
-int rc_corr_relayout_level(const float *src, float *dst, long long rows, int hl, int wl, int to_tiled,
+int rc_corr_relayout_level(const float *src, float *dst, int B, int N, int hl, int wl, int to_tiled,
                            void *stream);
 
 /*

@@ -97,9 +97,9 @@ SIGNATURES = {
     "rc_corr_build_pyramid": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
     "rc_corr_build_pyramid_noalloc": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp]),
     "rc_corr_lookup_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
-    "rc_corr_tiled_plane_elems": (_i, [_i, _i, _i, ctypes.POINTER(_sz)]),
+    "rc_corr_tiled_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
     "rc_corr_build_pyramid_tiled": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
-    "rc_corr_relayout_level": (_i, [_vp, _vp, ctypes.c_longlong, _i, _i, _i, _vp]),
+    "rc_corr_relayout_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_tiled_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_bwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), _i, _i, _i, _i, _i, _vp]),
     "rc_corr_build_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),

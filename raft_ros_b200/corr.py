@@ -89,14 +89,15 @@ def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
     return levels
 
 
-def tiled_plane_elems(hl: int, wl: int) -> int:
-    """floats per row p of a level in the tiled layout (include/raftcorr.h: rc_corr_tiled_plane_elems)."""
-    return ((hl + 1) & ~1) * ((wl + 7) & ~7)
+def tiled_level_elems(B: int, N: int, hl: int, wl: int) -> int:
+    """floats of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems):
+    [B][ceil(N/8)][hp/2][wp/8][8][2][8]."""
+    return B * ((N + 7) // 8) * 8 * ((hl + 1) & ~1) * ((wl + 7) & ~7)
 
 
 def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
                             precision: Optional[str] = None, scale: float = 0.0) -> List[torch.Tensor]:
-    """rc_corr_build_pyramid_tiled: (B,D,h,w) x2 -> list of (B*h*w, plane_l) fp32 in the TILED layout."""
+    """rc_corr_build_pyramid_tiled: (B,D,h,w) x2 -> list of flat fp32 levels in the TILED layout."""
     _require_cuda(fmap1, "fmap1")
     _require_cuda(fmap2, "fmap2")
     if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
@@ -109,12 +110,11 @@ def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels
     prec = _precision_code(precision)
     L = _lib.lib()
     with torch.cuda.device(f1.device):
-        planes = [tiled_plane_elems(hl, wl) for hl, wl in shapes]
-        sizes = [B * h * w * pl for pl in planes]  # multiples of 16 floats: every level stays 64 B aligned
+        sizes = [tiled_level_elems(B, h * w, hl, wl) for hl, wl in shapes]  # multiples of 128 floats
         flat = torch.empty(sum(sizes), dtype=torch.float32, device=f1.device)
         levels, o = [], 0
-        for s_, pl in zip(sizes, planes):
-            levels.append(flat[o:o + s_].view(B * h * w, pl))
+        for s_ in sizes:
+            levels.append(flat[o:o + s_])
             o += s_
         ws_bytes = int(L.rc_corr_build_workspace_bytes(B, D, h, w, prec))
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=f1.device)
@@ -126,16 +126,16 @@ def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels
     return levels
 
 
-def relayout_raw(src: torch.Tensor, rows: int, hl: int, wl: int, to_tiled: bool) -> torch.Tensor:
-    """rc_corr_relayout_level: one level, row layout (rows, 1, hl, wl) <-> tiled layout (rows, plane)."""
+def relayout_raw(src: torch.Tensor, B: int, N: int, hl: int, wl: int, to_tiled: bool) -> torch.Tensor:
+    """rc_corr_relayout_level: one level, row layout (B*N, 1, hl, wl) <-> tiled layout (flat)."""
     _require_cuda(src, "level")
     s = src if (src.dtype == torch.float32 and src.is_contiguous()) else _f32c(src)
     with torch.cuda.device(s.device):
         if to_tiled:
-            dst = torch.empty((rows, tiled_plane_elems(hl, wl)), dtype=torch.float32, device=s.device)
+            dst = torch.empty(tiled_level_elems(B, N, hl, wl), dtype=torch.float32, device=s.device)
         else:
-            dst = torch.empty((rows, 1, hl, wl), dtype=torch.float32, device=s.device)
-        rc = _lib.lib().rc_corr_relayout_level(s.data_ptr(), dst.data_ptr(), rows, hl, wl, 1 if to_tiled else 0, _stream())
+            dst = torch.empty((B * N, 1, hl, wl), dtype=torch.float32, device=s.device)
+        rc = _lib.lib().rc_corr_relayout_level(s.data_ptr(), dst.data_ptr(), B, N, hl, wl, 1 if to_tiled else 0, _stream())
         _lib.check(rc, "rc_corr_relayout_level")
     return dst
 
@@ -150,7 +150,7 @@ def lookup_tiled_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radiu
     nl = len(levels)
     shapes = level_shapes(h, w, nl)
     for l, (t, (hl, wl)) in enumerate(zip(levels, shapes)):
-        if t.numel() != B * h * w * tiled_plane_elems(hl, wl) or t.dtype != torch.float32 or not t.is_contiguous():
+        if t.numel() != tiled_level_elems(B, h * w, hl, wl) or t.dtype != torch.float32 or not t.is_contiguous():
             raise RuntimeError(f"tiled level {l} does not match a {B}x{h}x{w} problem")
     rd = 2 * radius + 1
     with torch.cuda.device(c.device):
@@ -355,7 +355,7 @@ class CorrBlock:
     def corr_pyramid(self):
         if self._rows is None:
             B, h, w = self._geom
-            self._rows = [relayout_raw(t, B * h * w, hl, wl, to_tiled=False)
+            self._rows = [relayout_raw(t, B, h * w, hl, wl, to_tiled=False)
                           for t, (hl, wl) in zip(self._tiled, level_shapes(h, w, self.num_levels))]
         return self._rows
 

@@ -129,11 +129,13 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
   return launch_lookup_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
-int rc_corr_tiled_plane_elems(int h, int w, int level, size_t *elems) {
-  RC_CHECK_ARG(elems, "rc_corr_tiled_plane_elems: null output");
+int rc_corr_tiled_level_elems(int B, int h, int w, int level, size_t *elems) {
+  RC_CHECK_ARG(elems, "rc_corr_tiled_level_elems: null output");
+  RC_CHECK_ARG(B > 0, "rc_corr_tiled_level_elems: B must be positive");
   int hl = 0, wl = 0;
   if (int rc = rc_level_dims(h, w, level, &hl, &wl)) return rc;
-  *elems = (size_t)((hl + 1) & ~1) * (size_t)((wl + 7) & ~7);
+  const size_t groups = (size_t)B * (((size_t)h * w + 7) / 8);
+  *elems = groups * 8 * (size_t)((hl + 1) & ~1) * (size_t)((wl + 7) & ~7);
   return RC_OK;
 }
 
@@ -158,11 +160,11 @@ int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, i
                                workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
-int rc_corr_relayout_level(const float *src, float *dst, long long rows, int hl, int wl, int to_tiled,
+int rc_corr_relayout_level(const float *src, float *dst, int B, int N, int hl, int wl, int to_tiled,
                            void *stream) {
   RC_CHECK_ARG(src && dst, "rc_corr_relayout_level: null pointer");
-  RC_CHECK_ARG(rows > 0 && hl > 0 && wl > 0, "rc_corr_relayout_level: bad shape");
-  return launch_relayout(src, dst, rows, hl, wl, to_tiled != 0, static_cast<cudaStream_t>(stream));
+  RC_CHECK_ARG(B > 0 && N > 0 && hl > 0 && wl > 0, "rc_corr_relayout_level: bad shape");
+  return launch_relayout(src, dst, B, N, hl, wl, to_tiled != 0, static_cast<cudaStream_t>(stream));
 }
 
 int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords, float *out, int B,

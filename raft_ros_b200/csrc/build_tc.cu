@@ -56,7 +56,8 @@ struct Params {
   long long total_tiles;
   float scale;
   int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
-  int plane[4], tws[4];         // TILED output only: floats per row p of level l / per tile-row of it
+  int tpr[4], ng;               // TILED output only: tiles per tile-row of level l; groups of 8 query pixels per item
+  long long gstride[4];         //   floats per group of level l (= 8 * hp * wp)
   LevelPtrs lv;
 };
 
@@ -75,11 +76,13 @@ struct Cfg {
                                     256 /*barriers*/;
 };
 
-// TILED: every row p of a level is written as [hp/2][wp/8] tiles of 2 rows x 8 floats (hp = ceil2,
-// wp = ceil8 of the level's size, zeros in the padding that a lookup can touch) -- the layout
+// TILED: every row p of a level is cut into [hp/2][wp/8] tiles of 2 rows x 8 floats (hp = ceil2,
+// wp = ceil8 of the level's size, zeros in the padding that a lookup can touch) and the tiles of 8
+// consecutive query pixels are interleaved, [group][tile][pixel][2][8] -- the layout
 // lookup_tiled.cu reads.  It costs the epilogue nothing: a warp's row pair of the 8x32 patch IS
-// four whole tiles, 256 contiguous bytes per query pixel, and every row p starts 64 B aligned
-// whatever h and w are, so the stores are whole 128 B lines for ragged sizes too.
+// four whole tiles per query pixel, one store instruction writes one tile of 8 pixels = 512
+// contiguous bytes, and every tile is 64 B aligned whatever h and w are, so the stores are whole
+// 128 B lines for ragged sizes too.
 template <int NPASS, int NCTA, bool TILED>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
@@ -239,8 +242,9 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     uint32_t acc_phase = 0;
     const int h = P.h, w = P.w, N = P.N, L = P.L;
     const int h1 = h >> 1, w1 = w >> 1, h2 = h >> 2, w2 = w >> 2, h3 = h >> 3, w3 = w >> 3;
-    const size_t pitch0 = TILED ? (size_t)P.plane[0] : (size_t)h * w, pitch1 = TILED ? (size_t)P.plane[1] : (size_t)h1 * w1,
-                 pitch2 = TILED ? (size_t)P.plane[2] : (size_t)h2 * w2, pitch3 = TILED ? (size_t)P.plane[3] : (size_t)h3 * w3;
+    // row layout: floats per volume row; tiled layout: floats per group of 8 query pixels
+    const size_t pitch0 = TILED ? (size_t)P.gstride[0] : (size_t)h * w, pitch1 = TILED ? (size_t)P.gstride[1] : (size_t)h1 * w1,
+                 pitch2 = TILED ? (size_t)P.gstride[2] : (size_t)h2 * w2, pitch3 = TILED ? (size_t)P.gstride[3] : (size_t)h3 * w3;
     const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;
     bool peer_pending = false;  // hf=1: our staging buffer still holds the level-2 row for the peer
     for (long long t = unit0; t < P.total_tiles; t += unit_step) {
@@ -254,11 +258,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const size_t grow0 = (size_t)b * N + prow0;        // first row of the volume for this warp
       const int x0 = nx * PW;
       // row layout: first element of this warp's patch columns in row grow0 of each level;
-      // tiled layout: first tile of them (tile-row 0)
-      float *const g0 = TILED ? P.lv.p[0] + grow0 * pitch0 + nx * 64 : P.lv.p[0] + grow0 * pitch0 + x0;
-      float *const g1 = TILED ? P.lv.p[1] + grow0 * pitch1 + nx * 32 : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
-      float *const g2 = TILED ? P.lv.p[2] + grow0 * pitch2 + nx * 16 : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
-      float *const g3 = TILED ? P.lv.p[3] + (grow0 + lane) * pitch3 + (nx >> 1) * 16 + (nx & 1) * 4
+      // tiled layout: the patch's first tile (tile-row 0) of the warp's first group of 8 query pixels
+      const size_t grp0 = (size_t)b * P.ng + (prow0 >> 3);
+      float *const g0 = TILED ? P.lv.p[0] + grp0 * pitch0 + nx * 512 : P.lv.p[0] + grow0 * pitch0 + x0;
+      float *const g1 = TILED ? P.lv.p[1] + grp0 * pitch1 + nx * 256 : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
+      float *const g2 = TILED ? P.lv.p[2] + grp0 * pitch2 + nx * 128 : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
+      float *const g3 = TILED ? P.lv.p[3] + (grp0 + (lane >> 3)) * pitch3 + (nx >> 1) * 128 + (lane & 7) * 16 + (nx & 1) * 4
                               : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
@@ -293,8 +298,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         if constexpr (TILED) {
           // rows y0, y0+1 = one tile-row; columns beyond w (and row h of an odd h) are zero accumulators
           if (y0 < h) {
-            float *const gt = g0 + (size_t)(y0 >> 1) * P.tws[0];
-            const int tiles = (P.tws[0] >> 4) - nx * 4;  // tiles of this tile-row from the patch's first one on
+            float *const gt = g0 + (size_t)(y0 >> 1) * (P.tpr[0] * 128);
+            const int tiles = P.tpr[0] - nx * 4;  // tiles of this tile-row from the patch's first one on
 #pragma unroll
             for (int c2 = 0; c2 < 2; ++c2) {
               float ch[32];
@@ -305,7 +310,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = v0[16 * c2 + 8 + i];
                 ch[24 + i] = v1[16 * c2 + 8 + i];
               }
-              store_rows<32>(buf, ch, lane, gt + c2 * 32, pitch0, rows_valid, (tiles - 2 * c2) * 16, true);
+              store_tiles32(buf, ch, lane, gt + c2 * 256, pitch0, rows_valid, tiles - 2 * c2);
             }
           }
         } else {
@@ -338,8 +343,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = l1prev[8 + i];
                 ch[24 + i] = l1[8 + i];
               }
-              store_rows<32>(buf, ch, lane, g1 + (size_t)(y1 >> 1) * P.tws[1], pitch1, rows_valid,
-                             ((P.tws[1] >> 4) - nx * 2) * 16, true);
+              store_tiles32(buf, ch, lane, g1 + (size_t)(y1 >> 1) * (P.tpr[1] * 128), pitch1, rows_valid,
+                            P.tpr[1] - nx * 2);
             }
           } else {
             if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
@@ -365,8 +370,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 }
                 // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
                 if (2 * ny < h2)
-                  store_rows<8>(buf, l2, lane, g2 + (size_t)ny * P.tws[2] + hf * 8, pitch2, rows_valid,
-                                nx < (P.tws[2] >> 4) ? 8 : 0, true);
+                  store_halftile8(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * 128) + hf * 8, pitch2, rows_valid,
+                                  nx < P.tpr[2]);
               } else {
                 if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
               }
@@ -401,8 +406,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             for (int i = 0; i < 4; ++i)
               if (i >= cv3 || ny >= h3) l3[i] = 0.0f;
             // a quarter of a level-3 tile: row ny & 1, columns 4 (nx & 1) .. +3 (16 B, always aligned)
-            if (ny < ((h3 + 1) & ~1) && (nx >> 1) < (P.tws[3] >> 4) && lane < rows_valid)
-              stg128(g3 + (size_t)(ny >> 1) * P.tws[3] + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
+            if (ny < ((h3 + 1) & ~1) && (nx >> 1) < P.tpr[3] && lane < rows_valid)
+              stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * 128) + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
           } else if (ny < h3 && lane < rows_valid) {
             float *d = g3 + (size_t)ny * w3;
             if (vec3 && cv3 >= 4) {
@@ -613,9 +618,11 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
   for (int l = 0; l < 4; ++l) {
     const int hp = ((h >> l) + 1) & ~1, wp = ((w >> l) + 7) & ~7;
-    P.plane[l] = hp * wp;
-    P.tws[l] = wp * 2;
+    P.tpr[l] = wp >> 3;
+    P.gstride[l] = (long long)hp * wp * 8;
   }
+
+  P.ng = (N + 7) >> 3;
 
   int rc;
   if (tiled) {
@@ -654,35 +661,37 @@ int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h,
 }
 
 // ------------------------------------------------------------------ tiled <-> row layout of one level
-// `rows` = B*N rows p of a level of hl x wl floats; the tiled plane of a row is [hp/2][wp/8][2][8].
-// The loop walks the TILED array (the padded, larger one): converting to it writes every padding
-// element (zero), converting from it skips them.
+// Row layout: (B*N, hl, wl).  Tiled layout: [B][ceil(N/8)][hp/2][wp/8][8 pixels][2][8] -- the tiles of
+// 8 consecutive query pixels are interleaved, so that a group's copies of one tile are 512
+// contiguous bytes.  The loop walks the TILED array (the padded, larger one): converting to it
+// writes every padding element (zero), converting from it skips them.
 template <bool TO_TILED>
 __global__ void __launch_bounds__(256)
-relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, long long rows, int hl, int wl) {
+relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, int B, int N, int hl, int wl) {
   const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tpr = wp >> 3;
-  const long long plane = (long long)hp * wp, total = rows * plane;
+  const int ng = (N + 7) >> 3;
+  const long long gstride = (long long)hp * wp * 8, total = (long long)B * ng * gstride;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const long long p = i / plane;
-    const int e = (int)(i - p * plane);
-    const int tile = e >> 4, in = e & 15;
+    const long long grp = i / gstride;
+    const int e = (int)(i - grp * gstride);
+    const int tile = e >> 7, u = (e >> 4) & 7, in = e & 15;
     const int ty = tile / tpr, tx = tile - ty * tpr;
     const int y = ty * 2 + (in >> 3), x = tx * 8 + (in & 7);
-    const bool inside = y < hl && x < wl;
-    const long long r = p * (long long)hl * wl + (long long)y * wl + x;
+    const int b = (int)(grp / ng), p = (int)(grp - (long long)b * ng) * 8 + u;
+    const bool inside = y < hl && x < wl && p < N;
+    const long long r = ((long long)b * N + p) * hl * wl + (long long)y * wl + x;
     if (TO_TILED) dst[i] = inside ? __ldg(src + r) : 0.0f;
     else if (inside) dst[r] = __ldg(src + i);
   }
 }
 
-int launch_relayout(const float *src, float *dst, long long rows, int hl, int wl, bool to_tiled, cudaStream_t st) {
-  const long long plane = (long long)((hl + 1) & ~1) * ((wl + 7) & ~7);
-  const long long total = rows * plane;
+int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, bool to_tiled, cudaStream_t st) {
+  const long long total = (long long)B * ((N + 7) >> 3) * 8 * ((hl + 1) & ~1) * ((wl + 7) & ~7);
   if (total <= 0) return RC_OK;
   long long blocks = (total + 255) / 256;
   if (blocks > 148LL * 32) blocks = 148LL * 32;
-  if (to_tiled) relayout_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src, dst, rows, hl, wl);
-  else relayout_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src, dst, rows, hl, wl);
+  if (to_tiled) relayout_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
+  else relayout_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
 }

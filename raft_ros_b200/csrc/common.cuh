@@ -45,7 +45,7 @@ int launch_build_tc_noalloc(const float *f1, const float *f2, int B, int D, int 
 int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h, int w,
                           const LevelPtrs &lv, int L, int precision, float scale, void *ws,
                           size_t ws_bytes, cudaStream_t st);
-int launch_relayout(const float *src, float *dst, long long rows, int hl, int wl, bool to_tiled,
+int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, bool to_tiled,
                     cudaStream_t st);
 int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
                       int w, int L, int r, cudaStream_t st);

@@ -128,20 +128,20 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   auto issue = [&](const TlCtx &c, int stage) {
     if (c.valid) {
       const int hl = h >> c.lvl, wl = w >> c.lvl;
-      const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tws = wp * 2;  // floats per tile-row
+      const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tpr = wp >> 3;  // tiles per tile-row
       const int wb = (wl + 3) & ~3;
       const int cg = (c.x0 & ~3) + 4 * tc;
       const bool okx = (tc < 3 || (c.x0 & 3) == 3) && (unsigned)cg < (unsigned)wb;
-      // for a pixel beyond the image `base` points past the level, but y0 is then far outside: no
-      // row is in range and the copy below is handed the level-0 pointer with src-size 0
-      const size_t prow = (size_t)c.b * N + c.p0 + tu;
-      const float *base = pick_level(lv, c.lvl) + prow * (size_t)(hp * wp) + ((cg >> 3) * 16 + (cg & 7));
+      // group (b, p0/8) of 8 query pixels: [tile][pixel u][2][8]; this lane: pixel u, tile column cg/8
+      const size_t grp = (size_t)c.b * groups_per_item + (c.p0 >> 3);
+      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * kTlPix) + ((cg >> 3) * 128 + tu * 16 + (cg & 7));
+      const int trs = tpr * 128;  // floats per tile-row of a group
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
       for (int r = 0; r < 10; ++r) {
         const int ya = c.y0 + r;
         const bool ok = okx && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? (ya >> 1) * tws + (ya & 1) * 8 : 0;
+        const int off = ok ? (ya >> 1) * trs + (ya & 1) * 8 : 0;
         copy16(dst + (unsigned)(r * PS) * 4u, ok ? base + off : pick_level(lv, 0), ok);
       }
     }

@@ -252,5 +252,45 @@ __device__ __forceinline__ void store_rows(uint32_t buf, const float *v, int lan
   }
 }
 
+// ---- stores into the TILED layout: [group of 8 query pixels][tile][pixel][2][8] (include/raftcorr.h).
+// The warp's 32 rows (query pixels) are 4 aligned groups; `g` points at (group of row 0, first tile,
+// pixel 0), `gstride` is the distance between groups in floats.
+
+// v = two whole tiles per row (32 floats).  One instruction stores one tile of one group:
+// 8 pixels x 64 B = 512 contiguous bytes.
+__device__ __forceinline__ void store_tiles32(uint32_t buf, const float *v, int lane, float *__restrict__ g,
+                                              size_t gstride, int rows_valid, int tiles_valid) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    sts128(buf + lane * 128 + ((c ^ (lane & 7)) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+  __syncwarp();
+  const int pix = lane >> 2, ch = lane & 3;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int grp = i >> 1, t = i & 1;
+    const int row = grp * 8 + pix;
+    const float4 val = lds128(buf + row * 128 + ((((t << 2) | ch) ^ pix) << 4));
+    if (t < tiles_valid && row < rows_valid) stg128(g + (size_t)grp * gstride + t * 128 + pix * 16 + ch * 4, val);
+  }
+  __syncwarp();
+}
+
+// v = one 8-float tile row per query pixel (a 32 B sector, tile row `half`).  One instruction
+// stores 16 pixels x 32 B.
+__device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, int lane, float *__restrict__ g,
+                                                size_t gstride, int rows_valid, bool tile_valid) {
+  sts128(buf + lane * 32 + ((0 ^ ((lane >> 2) & 1)) << 4), v[0], v[1], v[2], v[3]);
+  sts128(buf + lane * 32 + ((1 ^ ((lane >> 2) & 1)) << 4), v[4], v[5], v[6], v[7]);
+  __syncwarp();
+  const int pixl = lane >> 1, ch = lane & 1;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int row = i * 16 + pixl;
+    const float4 val = lds128(buf + row * 32 + ((ch ^ ((row >> 2) & 1)) << 4));
+    if (tile_valid && row < rows_valid) stg128(g + (size_t)(row >> 3) * gstride + (row & 7) * 16 + ch * 4, val);
+  }
+  __syncwarp();
+}
+
 }  // namespace tc
 }  // namespace rc

@@ -482,27 +482,36 @@ def test_no_writes_outside_outputs(rr, geom, precision):
 
 
 # ----------------------------------------------------------------------------- tiled volume layout
-def _tile_levels(levels):
-    """(P,1,hl,wl) rows -> [P][ceil2(hl)/2][ceil8(wl)/8][2][8] zero-padded tiles (test-side conversion in torch)."""
+def _tile_levels(levels, B):
+    """(B*N,1,hl,wl) rows -> [B][ceil(N/8)][ceil2(hl)/2][ceil8(wl)/8][8][2][8] zero-padded, pixel-interleaved
+    tiles (test-side conversion in torch; layout documented in include/raftcorr.h)."""
     out = []
     for lv in levels:
         P, _, hl, wl = lv.shape
-        hp, wp = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8
-        x = torch.nn.functional.pad(lv.view(P, hl, wl), (0, wp - wl, 0, hp - hl))
-        out.append(x.view(P, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 2, 4).contiguous())
+        N = P // B
+        hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + 7) // 8
+        x = torch.nn.functional.pad(lv.view(B, N, hl, wl), (0, wp - wl, 0, hp - hl, 0, ng * 8 - N))
+        x = x.view(B, ng, 8, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 5, 2, 4, 6)  # b, g, ty, tx, u, r, c
+        out.append(x.contiguous().view(-1))
     return out
 
 
-@pytest.mark.parametrize("shape", [(7, 5, 9), (3, 16, 32), (5, 1, 1), (2, 23, 39)])
+def _untile(flat, B, N, hl, wl):
+    hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + 7) // 8
+    x = flat.view(B, ng, hp // 2, wp // 8, 8, 2, 8).permute(0, 1, 4, 2, 5, 3, 6).reshape(B, ng * 8, hp, wp)
+    return x  # padded planes, query pixel major
+
+
+@pytest.mark.parametrize("shape", [(1, 7, 5, 9), (2, 16, 16, 32), (1, 5, 1, 1), (3, 11, 23, 39)])
 def test_relayout_level_round_trip(rr, shape):
     """rc_corr_relayout_level: rows -> tiled equals the torch conversion (padding zeroed), and back is exact."""
     from raft_ros_b200.corr import relayout_raw
-    P, hl, wl = shape
+    B, N, hl, wl = shape
     rng = np.random.default_rng(seed_of(shape))
-    rows = t(rng.standard_normal((P, 1, hl, wl)).astype(np.float32))
-    tiled = relayout_raw(rows, P, hl, wl, to_tiled=True)
-    assert torch.equal(tiled.view(-1), _tile_levels([rows])[0].view(-1))
-    assert torch.equal(relayout_raw(tiled, P, hl, wl, to_tiled=False), rows)
+    rows = t(rng.standard_normal((B * N, 1, hl, wl)).astype(np.float32))
+    tiled = relayout_raw(rows, B, N, hl, wl, to_tiled=True)
+    assert torch.equal(tiled.view(-1), _tile_levels([rows], B)[0])
+    assert torch.equal(relayout_raw(tiled, B, N, hl, wl, to_tiled=False), rows)
 
 
 TILED_GEOMS = [(1, 64, 8, 32, 4), (2, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 256, 47, 156, 4), (1, 128, 17, 20, 4),
@@ -517,7 +526,7 @@ def test_tiled_build_equals_row_build(rr, geom, prec):
     tiled lookup on it equals the row lookup -- with every buffer pre-filled with NaN, so anything the
     kernels read but never wrote would show."""
     from raft_ros_b200 import _lib
-    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw, relayout_raw, tiled_plane_elems, _PRECISIONS
+    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw, relayout_raw, tiled_level_elems, _PRECISIONS
     B, D, h, w, L = geom
     rng = np.random.default_rng(seed_of(geom, prec))
     f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
@@ -526,7 +535,7 @@ def test_tiled_build_equals_row_build(rr, geom, prec):
     lib = _lib.lib()
     shapes = O.level_shapes(h, w, L)
     N = h * w
-    tiled = [torch.full((B * N, tiled_plane_elems(hl, wl)), float("nan"), device=DEV) for hl, wl in shapes]
+    tiled = [torch.full((tiled_level_elems(B, N, hl, wl),), float("nan"), device=DEV) for hl, wl in shapes]
     code = _PRECISIONS[prec]
     ws_bytes = int(lib.rc_corr_build_workspace_bytes(B, D, h, w, code))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
@@ -536,12 +545,11 @@ def test_tiled_build_equals_row_build(rr, geom, prec):
     assert rc == 0, lib.rc_last_error()
     torch.cuda.synchronize()
     for l, (hl, wl) in enumerate(shapes):
-        back = relayout_raw(tiled[l], B * N, hl, wl, to_tiled=False)
+        back = relayout_raw(tiled[l], B, N, hl, wl, to_tiled=False)
         assert torch.equal(back, rows[l]), (geom, prec, l)
-        hp, wp = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8
-        grid = tiled[l].view(B * N, hp // 2, wp // 8, 2, 8).permute(0, 1, 3, 2, 4).reshape(B * N, hp, wp)
+        grid = _untile(tiled[l], B, N, hl, wl)
         wb = (wl + 3) // 4 * 4
-        assert bool((grid[:, :hl, wl:wb] == 0).all()), (geom, prec, l, "padding columns a lookup fetches must be zero")
+        assert bool((grid[:, :N, :hl, wl:wb] == 0).all()), (geom, prec, l, "padding columns a lookup fetches must be zero")
     for kind in ("sigma4", "border", "oob"):
         coords = t(make_coords(kind, B, h, w, rng))
         out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
@@ -606,7 +614,7 @@ def test_lookup_on_tiled_layout(rr, geom, kind):
     levels = [t(rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32)) for hl, wl in O.level_shapes(h, w, L)]
     coords = t(make_coords(kind, B, h, w, rng))
     want = lookup_raw(levels, coords, 4)
-    tiles = _tile_levels(levels)
+    tiles = _tile_levels(levels, B)
     out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
     lib = _lib.lib()
     rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),

@@ -4,7 +4,7 @@ import time
 import torch
 import raft_ros_b200 as rr
 from raft_ros_b200 import _lib
-from raft_ros_b200.corr import build_pyramid_tiled_raw, lookup_tiled_raw, build_pyramid_raw, lookup_raw
+from raft_ros_b200.corr import lookup_tiled_raw, build_pyramid_raw, lookup_raw, relayout_raw, level_shapes
 
 dev = torch.device("cuda:0")
 B, D, h, w = 8, 256, 55, 128
@@ -12,7 +12,17 @@ g = torch.Generator().manual_seed(0)
 f1 = torch.randn(B, D, h, w, generator=g).to(dev)
 f2 = torch.randn(B, D, h, w, generator=g).to(dev)
 coords = (rr.coords_grid(B, h, w, "cpu") + 2 * torch.randn(B, 2, h, w, generator=g)).to(dev)
-for name, bf, lf in (("tiled", build_pyramid_tiled_raw, lookup_tiled_raw), ("rows", build_pyramid_raw, lookup_raw)):
+sigma = float(__import__("os").environ.get("PROBE_SIGMA", "2"))
+coords = (rr.coords_grid(B, h, w, "cpu") + sigma * torch.randn(B, 2, h, w, generator=g)).to(dev)
+rows = build_pyramid_raw(f1, f2, 4, "bf16x3")
+
+
+def tiled_from_rows(f1_, f2_, L_, prec):
+    return [relayout_raw(x, B, h * w, hl, wl, True) for x, (hl, wl) in zip(rows, level_shapes(h, w, 4))]
+
+
+print("max |tiled - rows| =", float((lookup_tiled_raw(tiled_from_rows(0, 0, 0, 0), coords, 4) - lookup_raw(rows, coords, 4)).abs().max()))
+for name, bf, lf in (("tiled", tiled_from_rows, lookup_tiled_raw), ("rows", build_pyramid_raw, lookup_raw)):
     lv = bf(f1, f2, 4, "bf16x3")
     for _ in range(5):
         lf(lv, coords, 4)
