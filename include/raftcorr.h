@@ -120,13 +120,13 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
 /*
  * The TILED volume layout (no counterpart in the reference; it is what CorrBlock keeps internally
  * when no gradient is wanted).  Level l of row p = (b, query pixel q) -- h_l x w_l floats in the
- * row layout -- is cut into tiles of 2 rows x 8 floats (64 B), and the tiles of 8 consecutive
- * query pixels are interleaved:
- *     [B][ceil(h*w/8)][hp/2][wp/8][8 pixels][2][8],  hp = h_l rounded up to 2, wp = w_l rounded up to 8,
+ * row layout -- is cut into tiles of 2 rows x 8 floats (64 B), and the tiles of G = RC_TILE_GROUP
+ * consecutive query pixels are interleaved:
+ *     [B][ceil(h*w/G)][hp/2][wp/8][G pixels][2][8],  hp = h_l rounded up to 2, wp = w_l rounded up to 8,
  * rc_corr_tiled_level_elems floats per level, zeros in every padding element a lookup can
  * reach.  A 10x10 lookup window then covers a few 64 B tiles instead of ten 40 B row segments
  * that straddle DRAM fill granules (-28 % DRAM reads per lookup); neighbouring query pixels look
- * at neighbouring places, so the 8 copies of a tile that a group of pixels needs are 512
+ * at neighbouring places, so the G copies of a tile that a group of pixels needs are G*64
  * contiguous bytes; and every tile is 64 B aligned whatever h and w are, so the build writes
  * whole 128 B lines for ragged sizes too (2.3x faster build at 47x156).
  *
@@ -139,6 +139,10 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
  *                     item) between the layouts (to_tiled != 0: rows -> tiled, padding zeroed;
  *                     0: tiled -> rows).
  */
+#ifndef RC_TILE_GROUP
+#define RC_TILE_GROUP 32 /* 8, 16 or 32; a build-time constant of the library */
+#endif
+int rc_corr_tile_group(void); /* the RC_TILE_GROUP the library was built with */
 int rc_corr_tiled_level_elems(int B, int h, int w, int level, size_t *elems);
 int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, int D, int h, int w,
                                 float *const *level_ptrs, int num_levels, int precision, float scale,

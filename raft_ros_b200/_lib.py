@@ -97,6 +97,7 @@ SIGNATURES = {
     "rc_corr_build_pyramid": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
     "rc_corr_build_pyramid_noalloc": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp]),
     "rc_corr_lookup_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rc_corr_tile_group": (_i, []),
     "rc_corr_tiled_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
     "rc_corr_build_pyramid_tiled": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
     "rc_corr_relayout_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

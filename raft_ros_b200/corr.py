@@ -91,8 +91,9 @@ def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
 
 def tiled_level_elems(B: int, N: int, hl: int, wl: int) -> int:
     """floats of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems):
-    [B][ceil(N/8)][hp/2][wp/8][8][2][8]."""
-    return B * ((N + 7) // 8) * 8 * ((hl + 1) & ~1) * ((wl + 7) & ~7)
+    [B][ceil(N/G)][hp/2][wp/8][G][2][8], G = rc_corr_tile_group()."""
+    G = int(_lib.lib().rc_corr_tile_group())
+    return B * ((N + G - 1) // G) * G * ((hl + 1) & ~1) * ((wl + 7) & ~7)
 
 
 def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,

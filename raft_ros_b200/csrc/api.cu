@@ -129,13 +129,15 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
   return launch_lookup_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
+int rc_corr_tile_group(void) { return RC_TILE_GROUP; }
+
 int rc_corr_tiled_level_elems(int B, int h, int w, int level, size_t *elems) {
   RC_CHECK_ARG(elems, "rc_corr_tiled_level_elems: null output");
   RC_CHECK_ARG(B > 0, "rc_corr_tiled_level_elems: B must be positive");
   int hl = 0, wl = 0;
   if (int rc = rc_level_dims(h, w, level, &hl, &wl)) return rc;
-  const size_t groups = (size_t)B * (((size_t)h * w + 7) / 8);
-  *elems = groups * 8 * (size_t)((hl + 1) & ~1) * (size_t)((wl + 7) & ~7);
+  const size_t groups = (size_t)B * (((size_t)h * w + RC_TILE_GROUP - 1) / RC_TILE_GROUP);
+  *elems = groups * RC_TILE_GROUP * (size_t)((hl + 1) & ~1) * (size_t)((wl + 7) & ~7);
   return RC_OK;
 }
 

@@ -56,8 +56,8 @@ struct Params {
   long long total_tiles;
   float scale;
   int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
-  int tpr[4], ng;               // TILED output only: tiles per tile-row of level l; groups of 8 query pixels per item
-  long long gstride[4];         //   floats per group of level l (= 8 * hp * wp)
+  int tpr[4], ng;               // TILED output only: tiles per tile-row of level l; groups of query pixels per item
+  long long gstride[4];         //   floats per group of level l (= kTileGroup * hp * wp)
   LevelPtrs lv;
 };
 
@@ -259,11 +259,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const int x0 = nx * PW;
       // row layout: first element of this warp's patch columns in row grow0 of each level;
       // tiled layout: the patch's first tile (tile-row 0) of the warp's first group of 8 query pixels
-      const size_t grp0 = (size_t)b * P.ng + (prow0 >> 3);
-      float *const g0 = TILED ? P.lv.p[0] + grp0 * pitch0 + nx * 512 : P.lv.p[0] + grow0 * pitch0 + x0;
-      float *const g1 = TILED ? P.lv.p[1] + grp0 * pitch1 + nx * 256 : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
-      float *const g2 = TILED ? P.lv.p[2] + grp0 * pitch2 + nx * 128 : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
-      float *const g3 = TILED ? P.lv.p[3] + (grp0 + (lane >> 3)) * pitch3 + (nx >> 1) * 128 + (lane & 7) * 16 + (nx & 1) * 4
+      constexpr int G = kTileGroup, TS = 16 * G;  // query pixels per group, floats per tile of a group
+      const size_t grp0 = (size_t)b * P.ng + prow0 / G;  // prow0 is a multiple of 32, G divides 32
+      float *const g0 = TILED ? P.lv.p[0] + grp0 * pitch0 + nx * (4 * TS) : P.lv.p[0] + grow0 * pitch0 + x0;
+      float *const g1 = TILED ? P.lv.p[1] + grp0 * pitch1 + nx * (2 * TS) : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
+      float *const g2 = TILED ? P.lv.p[2] + grp0 * pitch2 + nx * TS : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
+      float *const g3 = TILED ? P.lv.p[3] + (grp0 + lane / G) * pitch3 + (nx >> 1) * TS + (lane % G) * 16 + (nx & 1) * 4
                               : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
@@ -298,7 +299,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         if constexpr (TILED) {
           // rows y0, y0+1 = one tile-row; columns beyond w (and row h of an odd h) are zero accumulators
           if (y0 < h) {
-            float *const gt = g0 + (size_t)(y0 >> 1) * (P.tpr[0] * 128);
+            float *const gt = g0 + (size_t)(y0 >> 1) * (P.tpr[0] * TS);
             const int tiles = P.tpr[0] - nx * 4;  // tiles of this tile-row from the patch's first one on
 #pragma unroll
             for (int c2 = 0; c2 < 2; ++c2) {
@@ -310,7 +311,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = v0[16 * c2 + 8 + i];
                 ch[24 + i] = v1[16 * c2 + 8 + i];
               }
-              store_tiles32(buf, ch, lane, gt + c2 * 256, pitch0, rows_valid, tiles - 2 * c2);
+              store_tiles32<G>(buf, ch, lane, gt + c2 * (2 * TS), pitch0, rows_valid, tiles - 2 * c2);
             }
           }
         } else {
@@ -343,8 +344,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = l1prev[8 + i];
                 ch[24 + i] = l1[8 + i];
               }
-              store_tiles32(buf, ch, lane, g1 + (size_t)(y1 >> 1) * (P.tpr[1] * 128), pitch1, rows_valid,
-                            P.tpr[1] - nx * 2);
+              store_tiles32<G>(buf, ch, lane, g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS), pitch1, rows_valid,
+                               P.tpr[1] - nx * 2);
             }
           } else {
             if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
@@ -370,8 +371,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 }
                 // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
                 if (2 * ny < h2)
-                  store_halftile8(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * 128) + hf * 8, pitch2, rows_valid,
-                                  nx < P.tpr[2]);
+                  store_halftile8<G>(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * TS) + hf * 8, pitch2, rows_valid,
+                                     nx < P.tpr[2]);
               } else {
                 if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
               }
@@ -407,7 +408,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
               if (i >= cv3 || ny >= h3) l3[i] = 0.0f;
             // a quarter of a level-3 tile: row ny & 1, columns 4 (nx & 1) .. +3 (16 B, always aligned)
             if (ny < ((h3 + 1) & ~1) && (nx >> 1) < P.tpr[3] && lane < rows_valid)
-              stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * 128) + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
+              stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * TS) + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
           } else if (ny < h3 && lane < rows_valid) {
             float *d = g3 + (size_t)ny * w3;
             if (vec3 && cv3 >= 4) {
@@ -619,10 +620,10 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   for (int l = 0; l < 4; ++l) {
     const int hp = ((h >> l) + 1) & ~1, wp = ((w >> l) + 7) & ~7;
     P.tpr[l] = wp >> 3;
-    P.gstride[l] = (long long)hp * wp * 8;
+    P.gstride[l] = (long long)hp * wp * kTileGroup;
   }
 
-  P.ng = (N + 7) >> 3;
+  P.ng = (N + kTileGroup - 1) / kTileGroup;
 
   int rc;
   if (tiled) {
@@ -661,23 +662,24 @@ int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h,
 }
 
 // ------------------------------------------------------------------ tiled <-> row layout of one level
-// Row layout: (B*N, hl, wl).  Tiled layout: [B][ceil(N/8)][hp/2][wp/8][8 pixels][2][8] -- the tiles of
-// 8 consecutive query pixels are interleaved, so that a group's copies of one tile are 512
-// contiguous bytes.  The loop walks the TILED array (the padded, larger one): converting to it
+// Row layout: (B*N, hl, wl).  Tiled layout: [B][ceil(N/G)][hp/2][wp/8][G pixels][2][8] -- the tiles of
+// G = RC_TILE_GROUP consecutive query pixels are interleaved, so that a group's copies of one tile
+// are G*64 contiguous bytes.  The loop walks the TILED array (the padded, larger one): converting to it
 // writes every padding element (zero), converting from it skips them.
 template <bool TO_TILED>
 __global__ void __launch_bounds__(256)
 relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, int B, int N, int hl, int wl) {
   const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tpr = wp >> 3;
-  const int ng = (N + 7) >> 3;
-  const long long gstride = (long long)hp * wp * 8, total = (long long)B * ng * gstride;
+  constexpr int G = kTileGroup;
+  const int ng = (N + G - 1) / G;
+  const long long gstride = (long long)hp * wp * G, total = (long long)B * ng * gstride;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long grp = i / gstride;
     const int e = (int)(i - grp * gstride);
-    const int tile = e >> 7, u = (e >> 4) & 7, in = e & 15;
+    const int tile = e / (16 * G), u = (e >> 4) % G, in = e & 15;
     const int ty = tile / tpr, tx = tile - ty * tpr;
     const int y = ty * 2 + (in >> 3), x = tx * 8 + (in & 7);
-    const int b = (int)(grp / ng), p = (int)(grp - (long long)b * ng) * 8 + u;
+    const int b = (int)(grp / ng), p = (int)(grp - (long long)b * ng) * G + u;
     const bool inside = y < hl && x < wl && p < N;
     const long long r = ((long long)b * N + p) * hl * wl + (long long)y * wl + x;
     if (TO_TILED) dst[i] = inside ? __ldg(src + r) : 0.0f;
@@ -686,7 +688,7 @@ relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, int B, i
 }
 
 int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, bool to_tiled, cudaStream_t st) {
-  const long long total = (long long)B * ((N + 7) >> 3) * 8 * ((hl + 1) & ~1) * ((wl + 7) & ~7);
+  const long long total = (long long)B * ((N + kTileGroup - 1) / kTileGroup) * kTileGroup * ((hl + 1) & ~1) * ((wl + 7) & ~7);
   if (total <= 0) return RC_OK;
   long long blocks = (total + 255) / 256;
   if (blocks > 148LL * 32) blocks = 148LL * 32;

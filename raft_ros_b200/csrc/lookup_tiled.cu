@@ -132,10 +132,13 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
       const int wb = (wl + 3) & ~3;
       const int cg = (c.x0 & ~3) + 4 * tc;
       const bool okx = (tc < 3 || (c.x0 & 3) == 3) && (unsigned)cg < (unsigned)wb;
-      // group (b, p0/8) of 8 query pixels: [tile][pixel u][2][8]; this lane: pixel u, tile column cg/8
-      const size_t grp = (size_t)c.b * groups_per_item + (c.p0 >> 3);
-      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * kTlPix) + ((cg >> 3) * 128 + tu * 16 + (cg & 7));
-      const int trs = tpr * 128;  // floats per tile-row of a group
+      // group of kTileGroup query pixels: [tile][pixel][2][8]; this lane: its pixel, tile column cg/8
+      constexpr int G = kTileGroup;
+      const int ng = (N + G - 1) / G;
+      const size_t grp = (size_t)c.b * ng + c.p0 / G;
+      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * G) +
+                          ((cg >> 3) * (16 * G) + (c.p0 % G + tu) * 16 + (cg & 7));
+      const int trs = tpr * 16 * G;  // floats per tile-row of a group
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
       for (int r = 0; r < 10; ++r) {

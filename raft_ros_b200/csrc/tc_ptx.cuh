@@ -252,12 +252,13 @@ __device__ __forceinline__ void store_rows(uint32_t buf, const float *v, int lan
   }
 }
 
-// ---- stores into the TILED layout: [group of 8 query pixels][tile][pixel][2][8] (include/raftcorr.h).
-// The warp's 32 rows (query pixels) are 4 aligned groups; `g` points at (group of row 0, first tile,
-// pixel 0), `gstride` is the distance between groups in floats.
+// ---- stores into the TILED layout: [group of G query pixels][tile][pixel][2][8] (include/raftcorr.h).
+// The warp's 32 rows (query pixels) are 32/G aligned groups; `g` points at (group of row 0, first
+// tile, pixel 0), `gstride` is the distance between groups in floats.
 
 // v = two whole tiles per row (32 floats).  One instruction stores one tile of one group:
 // 8 pixels x 64 B = 512 contiguous bytes.
+template <int G>
 __device__ __forceinline__ void store_tiles32(uint32_t buf, const float *v, int lane, float *__restrict__ g,
                                               size_t gstride, int rows_valid, int tiles_valid) {
 #pragma unroll
@@ -267,16 +268,18 @@ __device__ __forceinline__ void store_tiles32(uint32_t buf, const float *v, int 
   const int pix = lane >> 2, ch = lane & 3;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const int grp = i >> 1, t = i & 1;
-    const int row = grp * 8 + pix;
+    const int t = i & 1;
+    const int row = (i >> 1) * 8 + pix;
     const float4 val = lds128(buf + row * 128 + ((((t << 2) | ch) ^ pix) << 4));
-    if (t < tiles_valid && row < rows_valid) stg128(g + (size_t)grp * gstride + t * 128 + pix * 16 + ch * 4, val);
+    if (t < tiles_valid && row < rows_valid)
+      stg128(g + (size_t)(row / G) * gstride + t * (16 * G) + (row % G) * 16 + ch * 4, val);
   }
   __syncwarp();
 }
 
 // v = one 8-float tile row per query pixel (a 32 B sector, tile row `half`).  One instruction
 // stores 16 pixels x 32 B.
+template <int G>
 __device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, int lane, float *__restrict__ g,
                                                 size_t gstride, int rows_valid, bool tile_valid) {
   sts128(buf + lane * 32 + ((0 ^ ((lane >> 2) & 1)) << 4), v[0], v[1], v[2], v[3]);
@@ -287,7 +290,7 @@ __device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, in
   for (int i = 0; i < 2; ++i) {
     const int row = i * 16 + pixl;
     const float4 val = lds128(buf + row * 32 + ((ch ^ ((row >> 2) & 1)) << 4));
-    if (tile_valid && row < rows_valid) stg128(g + (size_t)(row >> 3) * gstride + (row & 7) * 16 + ch * 4, val);
+    if (tile_valid && row < rows_valid) stg128(g + (size_t)(row / G) * gstride + (row % G) * 16 + ch * 4, val);
   }
   __syncwarp();
 }

@@ -483,22 +483,26 @@ def test_no_writes_outside_outputs(rr, geom, precision):
 
 # ----------------------------------------------------------------------------- tiled volume layout
 def _tile_levels(levels, B):
-    """(B*N,1,hl,wl) rows -> [B][ceil(N/8)][ceil2(hl)/2][ceil8(wl)/8][8][2][8] zero-padded, pixel-interleaved
+    """(B*N,1,hl,wl) rows -> [B][ceil(N/G)][ceil2(hl)/2][ceil8(wl)/8][G][2][8] zero-padded, pixel-interleaved
     tiles (test-side conversion in torch; layout documented in include/raftcorr.h)."""
+    from raft_ros_b200 import _lib
+    G = int(_lib.lib().rc_corr_tile_group())
     out = []
     for lv in levels:
         P, _, hl, wl = lv.shape
         N = P // B
-        hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + 7) // 8
-        x = torch.nn.functional.pad(lv.view(B, N, hl, wl), (0, wp - wl, 0, hp - hl, 0, ng * 8 - N))
-        x = x.view(B, ng, 8, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 5, 2, 4, 6)  # b, g, ty, tx, u, r, c
+        hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + G - 1) // G
+        x = torch.nn.functional.pad(lv.view(B, N, hl, wl), (0, wp - wl, 0, hp - hl, 0, ng * G - N))
+        x = x.view(B, ng, G, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 5, 2, 4, 6)  # b, g, ty, tx, u, r, c
         out.append(x.contiguous().view(-1))
     return out
 
 
 def _untile(flat, B, N, hl, wl):
-    hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + 7) // 8
-    x = flat.view(B, ng, hp // 2, wp // 8, 8, 2, 8).permute(0, 1, 4, 2, 5, 3, 6).reshape(B, ng * 8, hp, wp)
+    from raft_ros_b200 import _lib
+    G = int(_lib.lib().rc_corr_tile_group())
+    hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + G - 1) // G
+    x = flat.view(B, ng, hp // 2, wp // 8, G, 2, 8).permute(0, 1, 4, 2, 5, 3, 6).reshape(B, ng * G, hp, wp)
     return x  # padded planes, query pixel major
 
 
