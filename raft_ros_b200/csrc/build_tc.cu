@@ -442,27 +442,31 @@ __global__ void __launch_bounds__(256)
 prep_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __nv_bfloat16 *__restrict__ a_hi,
             __nv_bfloat16 *__restrict__ a_lo, __nv_bfloat16 *__restrict__ b_hi, __nv_bfloat16 *__restrict__ b_lo,
             int D, int Dp, int N, int with_lo) {
-  __shared__ float tile[32][33];
+  // one block: 64 channels x 32 pixels.  Loads are coalesced along the pixels (128 B per warp),
+  // stores along the channels as bf16 pairs (128 B per warp = one whole row of the K-major tile).
+  __shared__ float tile[64][33];
   const int which = blockIdx.z & 1, b = blockIdx.z >> 1;
   const float *src = (which ? f2 : f1) + (size_t)b * D * N;
   __nv_bfloat16 *hi = (which ? b_hi : a_hi) + (size_t)b * N * Dp;
   __nv_bfloat16 *lo = (which ? b_lo : a_lo) + (size_t)b * N * Dp;
-  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 32;
+  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < 8; ++i) {
     const int d = d0 + ty + 8 * i, p = p0 + tx;
     tile[ty + 8 * i][tx] = (d < D && p < N) ? __ldg(src + (size_t)d * N + p) : 0.0f;
   }
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int p = p0 + ty + 8 * i, d = d0 + tx;
-    if (p < N && d < Dp) {
-      const float x = tile[tx][ty + 8 * i];
-      const __nv_bfloat16 xh = __float2bfloat16_rn(x);
-      hi[(size_t)p * Dp + d] = xh;
-      if (with_lo) lo[(size_t)p * Dp + d] = __float2bfloat16_rn(x - __bfloat162float(xh));
+    const int pl = ty + 8 * i, p = p0 + pl, d = d0 + 2 * tx;
+    if (p < N) {  // Dp is a multiple of 64: d + 1 < Dp
+      const float x0 = tile[2 * tx][pl], x1 = tile[2 * tx + 1][pl];
+      const __nv_bfloat162 h2 = __floats2bfloat162_rn(x0, x1);
+      *reinterpret_cast<__nv_bfloat162 *>(hi + (size_t)p * Dp + d) = h2;
+      if (with_lo)
+        *reinterpret_cast<__nv_bfloat162 *>(lo + (size_t)p * Dp + d) =
+            __floats2bfloat162_rn(x0 - __bfloat162float(h2.x), x1 - __bfloat162float(h2.y));
     }
   }
 }
@@ -580,7 +584,7 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   __nv_bfloat16 *b_lo = x3 ? reinterpret_cast<__nv_bfloat16 *>(base + 3 * per_map) : b_hi;
 
   {
-    dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 32), (unsigned)(2 * B));
+    dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
     prep_kernel<<<grid, 256, 0, st>>>(f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0);
     RC_CUDA(cudaGetLastError());
   }
