@@ -120,15 +120,20 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
 /*
  * The TILED volume layout (no counterpart in the reference; it is what CorrBlock keeps internally
  * when no gradient is wanted).  Level l of row p = (b, query pixel q) -- h_l x w_l floats in the
- * row layout -- is cut into tiles of 2 rows x 8 floats (64 B), and the tiles of G = RC_TILE_GROUP
- * consecutive query pixels are interleaved:
- *     [B][ceil(h*w/G)][hp/2][wp/8][G pixels][2][8],  hp = h_l rounded up to 2, wp = w_l rounded up to 8,
- * rc_corr_tiled_level_elems floats per level, zeros in every padding element a lookup can
- * reach.  A 10x10 lookup window then covers a few 64 B tiles instead of ten 40 B row segments
- * that straddle DRAM fill granules (-28 % DRAM reads per lookup); neighbouring query pixels look
- * at neighbouring places, so the G copies of a tile that a group of pixels needs are G*64
- * contiguous bytes; and every tile is 64 B aligned whatever h and w are, so the build writes
- * whole 128 B lines for ragged sizes too (2.3x faster build at 47x156).
+ * row layout -- is cut into tiles of 2 rows x 8 floats (64 B = 4 chunks of 16 B, chunk
+ * k = 2*(y%2) + (x%8)/4), and the tiles of G = RC_TILE_GROUP = 32 consecutive query pixels are
+ * interleaved:
+ *     [B][ceil(h*w/G)][hp/2][wp/8][G pixels][4 chunks][4],  hp = h_l rounded up to 2, wp = w_l rounded up to 8,
+ * pixel u = q%G of a group keeping chunk k at position k ^ ((u >> 1) & 3).  Element (b, q, y, x):
+ *     ((((b*ceil(h*w/G) + q/G) * (hp/2) + y/2) * (wp/8) + x/8) * G + u) * 16 + (k ^ ((u>>1)&3)) * 4 + x%4.
+ * rc_corr_tiled_level_elems floats per level, zeros in every padding element a lookup can reach.
+ * Why: (1) a 10x10 lookup window covers a few 64 B tiles instead of ten 40 B row segments that
+ * straddle DRAM fill granules; (2) neighbouring query pixels look at neighbouring places, so the
+ * tiles a group of pixels needs are contiguous and DRAM sees long bursts (lookup 60 -> 47 us);
+ * (3) the build's epilogue warp (32 query pixels = one group) holds two whole tiles per pixel = 4 KB
+ * of contiguous bytes, which it lays out in shared memory without bank conflicts (hence the chunk
+ * swizzle) and hands to the bulk-copy engine -- for any h and w (the row layout degrades to
+ * partial-sector writes on ragged widths: 2.3x slower build at 47x156).
  *
  * rc_corr_build_pyramid_tiled : rc_corr_build_pyramid writing that layout.  RC_PREC_BF16X3 /
  *                     RC_PREC_BF16 only, num_levels <= 4, level pointers 64-byte aligned and
@@ -140,7 +145,7 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
  *                     0: tiled -> rows).
  */
 #ifndef RC_TILE_GROUP
-#define RC_TILE_GROUP 32 /* 8, 16 or 32; a build-time constant of the library */
+#define RC_TILE_GROUP 32 /* fixed: one warp of the build epilogue */
 #endif
 int rc_corr_tile_group(void); /* the RC_TILE_GROUP the library was built with */
 int rc_corr_tiled_level_elems(int B, int h, int w, int level, size_t *elems);

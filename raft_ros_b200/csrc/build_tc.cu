@@ -258,14 +258,26 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       const size_t grow0 = (size_t)b * N + prow0;        // first row of the volume for this warp
       const int x0 = nx * PW;
       // row layout: first element of this warp's patch columns in row grow0 of each level;
-      // tiled layout: the patch's first tile (tile-row 0) of the warp's first group of 8 query pixels
+      // tiled layout: the patch's first tile (tile-row 0) of the warp's group of 32 query pixels
       constexpr int G = kTileGroup, TS = 16 * G;  // query pixels per group, floats per tile of a group
-      const size_t grp0 = (size_t)b * P.ng + prow0 / G;  // prow0 is a multiple of 32, G divides 32
+      const size_t grp0 = (size_t)b * P.ng + prow0 / G;  // prow0 is a multiple of 32 = G
       float *const g0 = TILED ? P.lv.p[0] + grp0 * pitch0 + nx * (4 * TS) : P.lv.p[0] + grow0 * pitch0 + x0;
       float *const g1 = TILED ? P.lv.p[1] + grp0 * pitch1 + nx * (2 * TS) : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
       float *const g2 = TILED ? P.lv.p[2] + grp0 * pitch2 + nx * TS : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
-      float *const g3 = TILED ? P.lv.p[3] + (grp0 + lane / G) * pitch3 + (nx >> 1) * TS + (lane % G) * 16 + (nx & 1) * 4
+      float *const g3 = TILED ? P.lv.p[3] + grp0 * pitch3 + (nx >> 1) * TS + lane * 16
                               : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
+      // TILED: the staging buffer may still be being read by this warp's last bulk store
+      auto buf_ready = [&]() {
+        if (lane == 0) bulk_wait_read0();
+        __syncwarp();
+      };
+      // two whole tiles per query pixel -> global: one 4 KB bulk copy when the group and both tiles
+      // are complete (the warp moves on while the copy engine drains it), per-lane stores at edges
+      auto put_tiles = [&](const float *ch, float *gdst, int tiles_valid) {
+        buf_ready();
+        if (rows_valid >= 32 && tiles_valid >= 2) bulk_tiles32(buf, ch, lane, gdst);
+        else store_tiles32<G>(buf, ch, lane, gdst, rows_valid, tiles_valid);
+      };
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN + hf * (TN / 2));
@@ -311,7 +323,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = v0[16 * c2 + 8 + i];
                 ch[24 + i] = v1[16 * c2 + 8 + i];
               }
-              store_tiles32<G>(buf, ch, lane, gt + c2 * (2 * TS), pitch0, rows_valid, tiles - 2 * c2);
+              put_tiles(ch, gt + c2 * (2 * TS), tiles - 2 * c2);
             }
           }
         } else {
@@ -344,8 +356,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 ch[16 + i] = l1prev[8 + i];
                 ch[24 + i] = l1[8 + i];
               }
-              store_tiles32<G>(buf, ch, lane, g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS), pitch1, rows_valid,
-                               P.tpr[1] - nx * 2);
+              put_tiles(ch, g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS), P.tpr[1] - nx * 2);
             }
           } else {
             if (y1 < h1) store_rows<16>(buf, l1, lane, g1 + (size_t)y1 * w1, pitch1, rows_valid, w1 - (x0 >> 1), vec1);
@@ -370,9 +381,10 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                     if (nx * 8 + i >= w2 || y2 >= h2) l2[i] = 0.0f;
                 }
                 // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
-                if (2 * ny < h2)
-                  store_halftile8<G>(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * TS) + hf * 8, pitch2, rows_valid,
-                                     nx < P.tpr[2]);
+                if (2 * ny < h2) {
+                  buf_ready();
+                  store_halftile8<G>(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * TS), hf, rows_valid, nx < P.tpr[2]);
+                }
               } else {
                 if (y2 < h2) store_rows<8>(buf, l2, lane, g2 + (size_t)y2 * w2, pitch2, rows_valid, w2 - (x0 >> 2), vec2);
               }
@@ -383,6 +395,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       if (L > 3) {
         if (hf == 1) {
           // publish this half's level-2 row (8 floats per query pixel) through our staging buffer
+          if constexpr (TILED) buf_ready();
           sts128(buf + lane * 32, l2[0], l2[1], l2[2], l2[3]);
           sts128(buf + lane * 32 + 16, l2[4], l2[5], l2[6], l2[7]);
           __threadfence_block();
@@ -408,7 +421,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
               if (i >= cv3 || ny >= h3) l3[i] = 0.0f;
             // a quarter of a level-3 tile: row ny & 1, columns 4 (nx & 1) .. +3 (16 B, always aligned)
             if (ny < ((h3 + 1) & ~1) && (nx >> 1) < P.tpr[3] && lane < rows_valid)
-              stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * TS) + (ny & 1) * 8, make_float4(l3[0], l3[1], l3[2], l3[3]));
+              stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * TS) + (((((ny & 1) << 1) | (nx & 1)) ^ tile_sw(lane)) << 2),
+                     make_float4(l3[0], l3[1], l3[2], l3[3]));
           } else if (ny < h3 && lane < rows_valid) {
             float *d = g3 + (size_t)ny * w3;
             if (vec3 && cv3 >= 4) {
@@ -425,6 +439,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       if (acc == 0) acc_phase ^= 1;
     }
     if (L > 3 && hf == 1 && peer_pending) asm volatile("bar.sync %0, 64;" ::"r"(bar_free) : "memory");
+    if (TILED && lane == 0) bulk_wait_all();  // our shared memory must outlive the last bulk store
   }
 
   tc_fence_before();
@@ -666,9 +681,9 @@ int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h,
 }
 
 // ------------------------------------------------------------------ tiled <-> row layout of one level
-// Row layout: (B*N, hl, wl).  Tiled layout: [B][ceil(N/G)][hp/2][wp/8][G pixels][2][8] -- the tiles of
-// G = RC_TILE_GROUP consecutive query pixels are interleaved, so that a group's copies of one tile
-// are G*64 contiguous bytes.  The loop walks the TILED array (the padded, larger one): converting to it
+// Row layout: (B*N, hl, wl).  Tiled layout: [B][ceil(N/G)][hp/2][wp/8][G pixels][4 chunks of 16 B] -- the
+// tiles of G = 32 consecutive query pixels are interleaved (a group's copies of one tile are 2 KB of
+// contiguous bytes) and pixel u keeps chunk k = 2*(row & 1) + (column half) at position k ^ ((u >> 1) & 3).  The loop walks the TILED array (the padded, larger one): converting to it
 // writes every padding element (zero), converting from it skips them.
 template <bool TO_TILED>
 __global__ void __launch_bounds__(256)
@@ -680,9 +695,10 @@ relayout_kernel(const float *__restrict__ src, float *__restrict__ dst, int B, i
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long grp = i / gstride;
     const int e = (int)(i - grp * gstride);
-    const int tile = e / (16 * G), u = (e >> 4) % G, in = e & 15;
+    const int tile = e / (16 * G), u = (e >> 4) % G;
+    const int k = ((e >> 2) & 3) ^ ((u >> 1) & 3);  // chunk stored at this position
     const int ty = tile / tpr, tx = tile - ty * tpr;
-    const int y = ty * 2 + (in >> 3), x = tx * 8 + (in & 7);
+    const int y = ty * 2 + (k >> 1), x = tx * 8 + (k & 1) * 4 + (e & 3);
     const int b = (int)(grp / ng), p = (int)(grp - (long long)b * ng) * G + u;
     const bool inside = y < hl && x < wl && p < N;
     const long long r = ((long long)b * N + p) * hl * wl + (long long)y * wl + x;

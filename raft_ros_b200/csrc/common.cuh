@@ -33,9 +33,10 @@ struct ConstLevelPtrs {
   const float *p[RC_MAX_LEVELS];
 };
 
-// TILED layout: query pixels whose tiles are interleaved (include/raftcorr.h); 8, 16 or 32
+// TILED layout: query pixels whose tiles are interleaved (include/raftcorr.h) = one warp of the
+// build epilogue
 constexpr int kTileGroup = RC_TILE_GROUP;
-static_assert(kTileGroup == 8 || kTileGroup == 16 || kTileGroup == 32, "RC_TILE_GROUP");
+static_assert(kTileGroup == 32, "RC_TILE_GROUP is the build epilogue's warp: 32");
 
 // host launchers implemented in the .cu files (all return RC_* codes)
 int launch_build_simt(const float *f1, const float *f2, int B, int D, int h, int w,

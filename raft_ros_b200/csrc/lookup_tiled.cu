@@ -132,19 +132,21 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
       const int wb = (wl + 3) & ~3;
       const int cg = (c.x0 & ~3) + 4 * tc;
       const bool okx = (tc < 3 || (c.x0 & 3) == 3) && (unsigned)cg < (unsigned)wb;
-      // group of kTileGroup query pixels: [tile][pixel][2][8]; this lane: its pixel, tile column cg/8
+      // group of G = 32 query pixels: [tile][pixel u][4 chunks], chunk k = 2*(row & 1) + (column half) stored
+      // at position k ^ ((u >> 1) & 3) (the build's bank-conflict-free staging order, build_tc.cu)
       constexpr int G = kTileGroup;
       const int ng = (N + G - 1) / G;
       const size_t grp = (size_t)c.b * ng + c.p0 / G;
-      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * G) +
-                          ((cg >> 3) * (16 * G) + (c.p0 % G + tu) * 16 + (cg & 7));
+      const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg >> 2) & 1;
+      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * G) + ((cg >> 3) * (16 * G) + u * 16);
       const int trs = tpr * 16 * G;  // floats per tile-row of a group
+      const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);  // chunk position for even / odd rows
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
       for (int r = 0; r < 10; ++r) {
         const int ya = c.y0 + r;
         const bool ok = okx && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? (ya >> 1) * trs + (ya & 1) * 8 : 0;
+        const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
         copy16(dst + (unsigned)(r * PS) * 4u, ok ? base + off : pick_level(lv, 0), ok);
       }
     }

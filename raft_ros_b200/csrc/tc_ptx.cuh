@@ -252,15 +252,48 @@ __device__ __forceinline__ void store_rows(uint32_t buf, const float *v, int lan
   }
 }
 
-// ---- stores into the TILED layout: [group of G query pixels][tile][pixel][2][8] (include/raftcorr.h).
-// The warp's 32 rows (query pixels) are 32/G aligned groups; `g` points at (group of row 0, first
-// tile, pixel 0), `gstride` is the distance between groups in floats.
+// ---- stores into the TILED layout (include/raftcorr.h):
+//   [group of G = 32 query pixels][tile][pixel u][4 chunks of 16 B], chunk k = 2*(tile row) + (column half),
+//   stored at position k ^ ((u >> 1) & 3).
+// The warp's 32 rows (query pixels) are one group; `g` points at (group, first tile, pixel 0).
+// The chunk swizzle is what lets a warp write its pixels' tiles into shared memory in exactly the
+// global order without bank conflicts, so that a plain bulk copy can move them.
+__device__ __forceinline__ int tile_sw(int u) { return (u >> 1) & 3; }
 
-// v = two whole tiles per row (32 floats).  One instruction stores one tile of one group:
-// 8 pixels x 64 B = 512 contiguous bytes.
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store(void *gdst, uint32_t ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(ssrc), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// Fast path: v = two whole tiles per query pixel (32 floats: tile 0 row 0, tile 0 row 1, tile 1
+// row 0, tile 1 row 1), all 32 pixels and both tiles valid.  The warp lays the 4 KB out in shared
+// memory in global order and lane 0 hands them to the bulk-copy engine: the warp does not wait
+// for the store to drain (the caller waits for the buffer to be READ before reusing it).
+// (Two 2 KB copies on alternating halves of the buffer, one always outstanding, measured slower.)
+__device__ __forceinline__ void bulk_tiles32(uint32_t buf, const float *v, int lane, float *__restrict__ g) {
+  const int sw = tile_sw(lane);
+#pragma unroll
+  for (int t = 0; t < 2; ++t)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      sts128(buf + t * 2048 + lane * 64 + ((k ^ sw) << 4), v[16 * t + 4 * k], v[16 * t + 4 * k + 1], v[16 * t + 4 * k + 2],
+             v[16 * t + 4 * k + 3]);
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    bulk_store(g, buf, 4096);
+    bulk_commit();
+  }
+}
+
+// Edge path (partial group or a single valid tile): same data through per-lane stores.
 template <int G>
 __device__ __forceinline__ void store_tiles32(uint32_t buf, const float *v, int lane, float *__restrict__ g,
-                                              size_t gstride, int rows_valid, int tiles_valid) {
+                                              int rows_valid, int tiles_valid) {
+  static_assert(G == 32, "one warp = one group");
 #pragma unroll
   for (int c = 0; c < 8; ++c)
     sts128(buf + lane * 128 + ((c ^ (lane & 7)) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
@@ -271,17 +304,17 @@ __device__ __forceinline__ void store_tiles32(uint32_t buf, const float *v, int 
     const int t = i & 1;
     const int row = (i >> 1) * 8 + pix;
     const float4 val = lds128(buf + row * 128 + ((((t << 2) | ch) ^ pix) << 4));
-    if (t < tiles_valid && row < rows_valid)
-      stg128(g + (size_t)(row / G) * gstride + t * (16 * G) + (row % G) * 16 + ch * 4, val);
+    if (t < tiles_valid && row < rows_valid) stg128(g + t * (16 * G) + row * 16 + ((ch ^ tile_sw(row)) << 2), val);
   }
   __syncwarp();
 }
 
-// v = one 8-float tile row per query pixel (a 32 B sector, tile row `half`).  One instruction
-// stores 16 pixels x 32 B.
+// v = one 8-float tile row per query pixel (tile row `half`: chunks 2*half, 2*half+1).  One
+// instruction stores 16 pixels x 32 B.
 template <int G>
-__device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, int lane, float *__restrict__ g,
-                                                size_t gstride, int rows_valid, bool tile_valid) {
+__device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, int lane, float *__restrict__ g, int half,
+                                                int rows_valid, bool tile_valid) {
+  static_assert(G == 32, "one warp = one group");
   sts128(buf + lane * 32 + ((0 ^ ((lane >> 2) & 1)) << 4), v[0], v[1], v[2], v[3]);
   sts128(buf + lane * 32 + ((1 ^ ((lane >> 2) & 1)) << 4), v[4], v[5], v[6], v[7]);
   __syncwarp();
@@ -290,7 +323,7 @@ __device__ __forceinline__ void store_halftile8(uint32_t buf, const float *v, in
   for (int i = 0; i < 2; ++i) {
     const int row = i * 16 + pixl;
     const float4 val = lds128(buf + row * 32 + ((ch ^ ((row >> 2) & 1)) << 4));
-    if (tile_valid && row < rows_valid) stg128(g + (size_t)(row / G) * gstride + (row % G) * 16 + ch * 4, val);
+    if (tile_valid && row < rows_valid) stg128(g + row * 16 + (((half * 2 + ch) ^ tile_sw(row)) << 2), val);
   }
   __syncwarp();
 }

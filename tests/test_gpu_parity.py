@@ -483,8 +483,8 @@ def test_no_writes_outside_outputs(rr, geom, precision):
 
 # ----------------------------------------------------------------------------- tiled volume layout
 def _tile_levels(levels, B):
-    """(B*N,1,hl,wl) rows -> [B][ceil(N/G)][ceil2(hl)/2][ceil8(wl)/8][G][2][8] zero-padded, pixel-interleaved
-    tiles (test-side conversion in torch; layout documented in include/raftcorr.h)."""
+    """(B*N,1,hl,wl) rows -> [B][ceil(N/G)][ceil2(hl)/2][ceil8(wl)/8][G][4 swizzled 16 B chunks] zero-padded,
+    pixel-interleaved tiles (test-side conversion in torch; layout documented in include/raftcorr.h)."""
     from raft_ros_b200 import _lib
     G = int(_lib.lib().rc_corr_tile_group())
     out = []
@@ -493,16 +493,25 @@ def _tile_levels(levels, B):
         N = P // B
         hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + G - 1) // G
         x = torch.nn.functional.pad(lv.view(B, N, hl, wl), (0, wp - wl, 0, hp - hl, 0, ng * G - N))
-        x = x.view(B, ng, G, hp // 2, 2, wp // 8, 8).permute(0, 1, 3, 5, 2, 4, 6)  # b, g, ty, tx, u, r, c
-        out.append(x.contiguous().view(-1))
+        x = x.view(B, ng, G, hp // 2, 2, wp // 8, 2, 4).permute(0, 1, 3, 5, 2, 4, 6, 7)  # b, g, ty, tx, u, r, half, c
+        x = x.reshape(B, ng, hp // 2, wp // 8, G, 4, 4)  # chunk k = 2 r + half
+        out.append(x.gather(5, _chunk_perm(G).view(1, 1, 1, 1, G, 4, 1).expand_as(x)).contiguous().view(-1))
     return out
+
+
+def _chunk_perm(G):
+    """position -> chunk stored there, per pixel u of a group: k = pos ^ ((u >> 1) & 3) (an involution)."""
+    u = torch.arange(G, device=DEV).view(G, 1)
+    return torch.arange(4, device=DEV).view(1, 4) ^ ((u >> 1) & 3)
 
 
 def _untile(flat, B, N, hl, wl):
     from raft_ros_b200 import _lib
     G = int(_lib.lib().rc_corr_tile_group())
     hp, wp, ng = (hl + 1) // 2 * 2, (wl + 7) // 8 * 8, (N + G - 1) // G
-    x = flat.view(B, ng, hp // 2, wp // 8, G, 2, 8).permute(0, 1, 4, 2, 5, 3, 6).reshape(B, ng * G, hp, wp)
+    x = flat.view(B, ng, hp // 2, wp // 8, G, 4, 4)
+    x = x.gather(5, _chunk_perm(G).view(1, 1, 1, 1, G, 4, 1).expand_as(x))  # undo the chunk swizzle
+    x = x.view(B, ng, hp // 2, wp // 8, G, 2, 8).permute(0, 1, 4, 2, 5, 3, 6).reshape(B, ng * G, hp, wp)
     return x  # padded planes, query pixel major
 
 
