@@ -47,7 +47,7 @@ def main(path):
             tk = r[ix["Source"]].split()
             if tk:
                 ops.add((tk[1] if tk[0].startswith("@") and len(tk) > 1 else tk[0]).split(".")[0])
-        marks = [m for m in ("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "SYNCS", "UTCBAR", "HMMA", "LDGSTS") if m in ops]
+        marks = [m for m in ("UTCHMMA", "UTMALDG", "UTMASTG", "UBLKCP", "LDTM", "SYNCS", "UTCBAR", "HMMA", "LDGSTS") if m in ops]
         print("## SASS mnemonics present:", ", ".join(marks))
 
 
