@@ -228,32 +228,54 @@ class _GradState:
     """
 
     def __init__(self):
-        self.levels = None        # detached pyramid, read by the lookups
+        self.levels = None        # detached pyramid in the row layout, read by the lookups ...
+        self.tiled = None         # ... or in the tiled layout (then `levels` is only made on demand)
+        self.shapes = None        # [(B*N, 1, h_l, w_l)] of the row layout
+        self.geom = None          # (B, h, w)
+        self.device = None
         self.grad_levels = None   # allocated lazily by the first lookup backward of a pass
 
 
 def _alloc_like_levels(levels):
-    sizes = [lv.numel() for lv in levels]
+    return _alloc_levels([tuple(lv.shape) for lv in levels], levels[0].device)
+
+
+def _alloc_levels(shapes, device):
+    """zeroed gradient pyramid (row layout), one allocation"""
+    sizes = [int(torch.Size(sh).numel()) for sh in shapes]
     offs, total = [], 0
     for s_ in sizes:
         offs.append(total)
         total += (s_ + 63) // 64 * 64
-    flat = torch.zeros(total, dtype=torch.float32, device=levels[0].device)
-    return [flat[o:o + n].view(lv.shape) for o, n, lv in zip(offs, sizes, levels)]
+    flat = torch.zeros(total, dtype=torch.float32, device=device)
+    return [flat[o:o + n].view(sh) for o, n, sh in zip(offs, sizes, shapes)]
+
+
+def _use_tiled(num_levels, radius, precision) -> bool:
+    return (radius == 4 and 1 <= num_levels <= 4 and _precision_code(precision) != _lib.RC_PREC_FP32
+            and os.environ.get("RAFT_CORR_LAYOUT", "tiled") != "rows")
 
 
 class _BuildPyramidFn(torch.autograd.Function):
-    """outputs: (token, level_0, ..., level_{L-1}).  Gradients may arrive through the levels
-    (generic autograd use of `corr_pyramid`) and/or through `state.grad_levels` (the lookups)."""
+    """outputs: (token, level_0, ..., level_{L-1}) in the row layout, or (token,) alone when the
+    pyramid is kept in the tiled layout (`tiled=True`).  Gradients may arrive through the levels
+    (generic autograd use of `corr_pyramid`) and/or through `state.grad_levels` (the lookups and,
+    in the tiled case, `_UntileFn`)."""
 
     @staticmethod
-    def forward(ctx, fmap1, fmap2, num_levels, precision, state):
+    def forward(ctx, fmap1, fmap2, num_levels, precision, state, tiled):
         ctx.save_for_backward(fmap1, fmap2)
         ctx.state = state
         ctx.precision = precision
+        B, _, h, w = fmap1.shape
+        state.geom, state.device = (B, h, w), fmap1.device
+        state.shapes = [(B * h * w, 1, hl, wl) for hl, wl in level_shapes(h, w, num_levels)]
+        token = torch.zeros(1, dtype=torch.float32, device=fmap1.device)
+        if tiled:
+            state.tiled = build_pyramid_tiled_raw(fmap1, fmap2, num_levels, precision)
+            return (token,)
         levels = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
         state.levels = [lv.detach() for lv in levels]
-        token = torch.zeros(1, dtype=torch.float32, device=fmap1.device)
         return (token,) + tuple(levels)
 
     @staticmethod
@@ -267,12 +289,35 @@ class _BuildPyramidFn(torch.autograd.Function):
             if g is None:
                 continue
             if gl is None:
-                gl = _alloc_like_levels(state.levels)
+                gl = _alloc_levels(state.shapes, state.device)
             gl[l].add_(g.view(gl[l].shape))
         if gl is None:
-            return torch.zeros_like(fmap1), torch.zeros_like(fmap2), None, None, None
+            return torch.zeros_like(fmap1), torch.zeros_like(fmap2), None, None, None, None
         df1, df2 = build_bwd_raw(gl, fmap1, fmap2, precision=ctx.precision)
-        return df1.to(fmap1.dtype), df2.to(fmap2.dtype), None, None, None
+        return df1.to(fmap1.dtype), df2.to(fmap2.dtype), None, None, None, None
+
+
+class _UntileFn(torch.autograd.Function):
+    """`corr_pyramid` of a block that keeps its pyramid tiled: row-layout copies of the levels whose
+    gradients flow into the block's single gradient pyramid (and from there into the build)."""
+
+    @staticmethod
+    def forward(ctx, token, state):
+        ctx.state = state
+        B, h, w = state.geom
+        return tuple(relayout_raw(t, B, h * w, sh[2], sh[3], to_tiled=False) for t, sh in zip(state.tiled, state.shapes))
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, *grad_levels):
+        state = ctx.state
+        for l, g in enumerate(grad_levels):
+            if g is None:
+                continue
+            if state.grad_levels is None:
+                state.grad_levels = _alloc_levels(state.shapes, state.device)
+            state.grad_levels[l].add_(g.view(state.grad_levels[l].shape))
+        return torch.zeros(1, dtype=torch.float32, device=state.device), None
 
 
 class _LookupFn(torch.autograd.Function):
@@ -303,6 +348,8 @@ class _LookupTokenFn(torch.autograd.Function):
         ctx.radius = radius
         ctx.state = state
         ctx.save_for_backward(coords)
+        if state.tiled is not None:
+            return lookup_tiled_raw(state.tiled, coords, radius)
         return lookup_raw(state.levels, coords, radius)
 
     @staticmethod
@@ -311,7 +358,7 @@ class _LookupTokenFn(torch.autograd.Function):
         (coords,) = ctx.saved_tensors
         state = ctx.state
         if state.grad_levels is None:
-            state.grad_levels = _alloc_like_levels(state.levels)
+            state.grad_levels = _alloc_levels(state.shapes, state.device)
         lookup_bwd_raw(grad_out, coords, state.grad_levels, ctx.radius)
         return None, torch.zeros(1, dtype=torch.float32, device=grad_out.device), None, None
 
@@ -341,12 +388,13 @@ class CorrBlock:
         self._tiled = None      # tiled levels (inference fast path) or None
         self._rows = None       # row-layout levels (reference attribute), lazily made from _tiled
         self._geom = None
+        tiled = _use_tiled(num_levels, radius, precision)
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
             self._state = _GradState()
-            out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state)
-            self._token, self._rows = out[0], list(out[1:])
-        elif (radius == 4 and 1 <= num_levels <= 4 and _precision_code(precision) != _lib.RC_PREC_FP32
-              and os.environ.get("RAFT_CORR_LAYOUT", "tiled") != "rows"):
+            out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state, tiled)
+            self._token = out[0]
+            self._rows = None if tiled else list(out[1:])
+        elif tiled:
             self._tiled = build_pyramid_tiled_raw(fmap1, fmap2, num_levels, precision)
             self._geom = (fmap1.shape[0], fmap1.shape[2], fmap1.shape[3])
         else:
@@ -354,6 +402,9 @@ class CorrBlock:
 
     @property
     def corr_pyramid(self):
+        if self._rows is None and self._token is not None:
+            # training block with a tiled pyramid: differentiable row-layout copies
+            self._rows = list(_UntileFn.apply(self._token, self._state))
         if self._rows is None:
             B, h, w = self._geom
             self._rows = [relayout_raw(t, B, h * w, hl, wl, to_tiled=False)
@@ -364,12 +415,21 @@ class CorrBlock:
     def corr_pyramid(self, levels):
         self._rows = list(levels)
         self._tiled = None  # the lookups follow the assigned pyramid
+        self._token = None
 
     def __call__(self, coords):
-        if self._token is not None and torch.is_grad_enabled():
-            return _LookupTokenFn.apply(coords, self._token, self._state, self.radius)
+        if self._token is not None:
+            if torch.is_grad_enabled():
+                return _LookupTokenFn.apply(coords, self._token, self._state, self.radius)
+            st = self._state  # a block built for training, looked up under no_grad
+            if st.tiled is not None:
+                return lookup_tiled_raw(st.tiled, coords, self.radius)
+            return lookup_raw(st.levels, coords, self.radius)
         if self._tiled is not None:
             return lookup_tiled_raw(self._tiled, coords, self.radius)
+        if torch.is_grad_enabled() and any(lv.requires_grad for lv in self._rows):
+            # an assigned pyramid that is part of someone else's graph: generic differentiable path
+            return _LookupFn.apply(coords, self.radius, *self._rows)
         return lookup_raw(self._rows, coords, self.radius)
 
     @staticmethod
@@ -377,7 +437,7 @@ class CorrBlock:
         """(B,D,h,w) x2 -> (B,h,w,1,h,w): fmap1^T fmap2 / sqrt(D) (reference core/corr.py:52-60)."""
         B, _, h, w = fmap1.shape
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
-            _, vol = _BuildPyramidFn.apply(fmap1, fmap2, 1, precision, _GradState())
+            _, vol = _BuildPyramidFn.apply(fmap1, fmap2, 1, precision, _GradState(), False)
         else:
             (vol,) = build_pyramid_raw(fmap1, fmap2, 1, precision)
         return vol.view(B, h, w, 1, h, w)

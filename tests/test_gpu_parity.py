@@ -201,11 +201,14 @@ def test_build_bwd_vs_oracle(rr, dims, precision, tol):
     assert relmax(n(d1), w1) <= tol and relmax(n(d2), w2) <= tol, (relmax(n(d1), w1), relmax(n(d2), w2))
 
 
-def test_autograd_paths(rr):
+@pytest.mark.parametrize("prec", ["fp32", "bf16x3"])
+def test_autograd_paths(rr, prec):
     """(a) CorrBlock's own lookups accumulate into one gradient pyramid; (b) user code may also
     differentiate through `corr_pyramid` tensors directly; (c) a second backward pass over a
-    retained graph starts from zero again; all against torch autograd of the same math."""
+    retained graph starts from zero again; all against torch autograd of the same math.  fp32 keeps
+    the pyramid in the row layout, bf16x3 in the tiled one (`corr_pyramid` = differentiable copies)."""
     from oracle import torch_port as TP
+    gtol = 2e-5 if prec == "fp32" else 1e-4
     B, D, h, w, r = 2, 64, 20, 24, 4
     g = torch.Generator(device="cpu").manual_seed(7)
     f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
@@ -224,7 +227,8 @@ def test_autograd_paths(rr):
     blk = {}
 
     def our_build(x, y):
-        blk["b"] = rr.CorrBlock(x, y, radius=r, precision="fp32")
+        blk["b"] = rr.CorrBlock(x, y, radius=r, precision=prec)
+        assert (blk["b"]._state.tiled is not None) == (prec != "fp32")
         return blk["b"].corr_pyramid
 
     ours = loss_of(our_build, lambda pyr, c: blk["b"](c), a, b)
@@ -238,7 +242,11 @@ def test_autograd_paths(rr):
     ref = loss_of(lambda x, y: TP.build_pyramid(x, y, 4), lambda pyr, c: TP.lookup(pyr, c, r), ra, rb)
     ref.backward()
     assert abs(float(ours) - float(ref)) <= 1e-4 * abs(float(ref))
-    assert relmax(n(ga1), n(ra.grad)) <= 2e-5 and relmax(n(gb1), n(rb.grad)) <= 2e-5
+    assert relmax(n(ga1), n(ra.grad)) <= gtol and relmax(n(gb1), n(rb.grad)) <= gtol
+    # a block built for training can also be looked up under no_grad
+    with torch.no_grad():
+        again = blk["b"](coords[0])
+    assert not again.requires_grad and relmax(n(again), n(TP.lookup(TP.build_pyramid(f1, f2, 4), coords[0], r))) <= 1e-4
     # CorrBlock.corr
     a2, b2 = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
     v = rr.CorrBlock.corr(a2, b2, precision="bf16x3")
