@@ -147,6 +147,39 @@ def test_build_vs_oracle(rr, shape, precision):
         assert normwise(got, want[l]) <= tol["norm"], (shape, l, normwise(got, want[l]))
 
 
+def _fuzz_geometries(count=12, seed=20261106):
+    rng = np.random.default_rng(seed)
+    out = []
+    while len(out) < count:
+        L = int(rng.integers(1, 5))
+        h, w = int(rng.integers(8, 31)), int(rng.integers(8, 51))
+        if (h >> (L - 1)) < 1 or (w >> (L - 1)) < 1:
+            continue
+        out.append((int(rng.integers(1, 4)), int(rng.integers(8, 301)), h, w, L))
+    return out
+
+
+@pytest.mark.parametrize("geom", _fuzz_geometries())
+def test_corrblock_random_geometries(rr, geom):
+    """CorrBlock as a user gets it (default precision, tiled pyramid, one build + one lookup) on random
+    small geometries -- odd sizes, channel counts that are not multiples of 64, 1 to 4 levels -- against
+    the oracle end to end."""
+    B, D, h, w, L = geom
+    rng = np.random.default_rng(seed_of(geom))
+    f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    coords = make_coords("sigma4", B, h, w, rng)
+    want_pyr = O.corr_build(f1, f2, L)
+    want = O.corr_lookup(want_pyr, coords, 4)
+    blk = rr.CorrBlock(t(f1), t(f2), num_levels=L, radius=4)
+    assert blk._tiled is not None
+    got = n(blk(t(coords)))
+    assert got.shape == want.shape and np.isfinite(got).all()
+    assert relmax(got, want) <= 1e-4, (geom, relmax(got, want))
+    for l in range(L):
+        assert relmax(n(blk.corr_pyramid[l]), want_pyr[l]) <= BUILD_TOL["bf16x3"]["rel"], (geom, l)
+
+
 @pytest.mark.parametrize("kind", ["grid", "sigma0.5", "sigma4", "sigma32", "oob", "border", "huge"])
 @pytest.mark.parametrize("shape", SHAPES[:4])
 def test_lookup_vs_oracle(rr, shape, kind):
