@@ -203,9 +203,14 @@ __device__ __forceinline__ void split4(const float (&g)[4], bf16x4 &hi, bf16x4 &
   }
 }
 
+// LV = number of pyramid levels (compile time: the level loop is unrolled and every per-column
+// quantity -- the cell of each coarser level a column falls into, whether it is inside the floor-mode
+// pooled area, whether its value differs from the previous column's -- is computed once per thread,
+// outside the row loop; the first version recomputed them per element and was issue-bound).
+template <int LV>
 __global__ void __launch_bounds__(256)
 fold_split_kernel(ConstLevelPtrs glv, __nv_bfloat16 *__restrict__ c_hi, __nv_bfloat16 *__restrict__ c_lo,
-                  __nv_bfloat16 *__restrict__ t_hi, __nv_bfloat16 *__restrict__ t_lo, int h, int w, int L, int pitch,
+                  __nv_bfloat16 *__restrict__ t_hi, __nv_bfloat16 *__restrict__ t_lo, int h, int w, int pitch,
                   float scale, int vec_in) {
   __shared__ float tile[64][65];
   const int N = h * w;
@@ -214,12 +219,24 @@ fold_split_kernel(ConstLevelPtrs glv, __nv_bfloat16 *__restrict__ c_hi, __nv_bfl
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const size_t item = (size_t)b * N;
   const int q = q0 + tx * 4;
-  // per-column geometry of this thread's 4 columns is the same for every row it handles
-  int yy[4], xx[4];
+  // per-column geometry of this thread's 4 columns: the same for every row it handles
+  int idx[LV > 1 ? LV - 1 : 1][4];  // cell of level l+1 under column j, or -1
+  {
+    int yy[4], xx[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    yy[j] = (q + j) / w;
-    xx[j] = (q + j) - yy[j] * w;
+    for (int j = 0; j < 4; ++j) {
+      yy[j] = (q + j) / w;
+      xx[j] = (q + j) - yy[j] * w;
+    }
+#pragma unroll
+    for (int l = 1; l < LV; ++l) {
+      const int hl = h >> l, wl = w >> l;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int y = yy[j] >> l, x = xx[j] >> l;
+        idx[l - 1][j] = (q + j < N && y < hl && x < wl) ? y * wl + x : -1;
+      }
+    }
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -237,22 +254,17 @@ fold_split_kernel(ConstLevelPtrs glv, __nv_bfloat16 *__restrict__ c_hi, __nv_bfl
           if (q + j < N) g[j] = __ldg(g0 + j);
       }
       float wgt = 1.0f;
-      for (int l = 1; l < L; ++l) {
-        const int hl = h >> l, wl = w >> l;
+#pragma unroll
+      for (int l = 1; l < LV; ++l) {
         wgt *= 0.25f;
-        const float *gl = pick_level(glv, l) + rp * ((size_t)hl * wl);
-        int last = -1;
-        float lastv = 0.0f;
+        const float *gl = glv.p[l] + rp * (size_t)((h >> l) * (w >> l));
+        float v = 0.0f;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int y = yy[j] >> l, x = xx[j] >> l;
-          if (q + j < N && y < hl && x < wl) {
-            const int idx = y * wl + x;
-            if (idx != last) {
-              last = idx;
-              lastv = __ldg(gl + idx);
-            }
-            g[j] = fmaf(wgt, lastv, g[j]);
+          const int id = idx[l - 1][j];
+          if (id >= 0) {
+            if (j == 0 || id != idx[l - 1][j - 1]) v = __ldg(gl + id);  // neighbours mostly share a cell
+            g[j] = fmaf(wgt, v, g[j]);
           }
         }
       }
@@ -400,7 +412,16 @@ int launch_build_bwd_tc(const ConstLevelPtrs &glv, const float *f1, const float 
   {
     dim3 grid((unsigned)((N + 63) / 64), (unsigned)((N + 63) / 64), (unsigned)B);
     const int vec_in = (N % 4 == 0 && (reinterpret_cast<uintptr_t>(glv.p[0]) & 15) == 0) ? 1 : 0;
-    fold_split_kernel<<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, L, pitch, scale, vec_in);
+    switch (L) {
+      case 1: fold_split_kernel<1><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 2: fold_split_kernel<2><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 3: fold_split_kernel<3><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 4: fold_split_kernel<4><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 5: fold_split_kernel<5><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 6: fold_split_kernel<6><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      case 7: fold_split_kernel<7><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+      default: fold_split_kernel<8><<<grid, 256, 0, st>>>(glv, c_hi, c_lo, t_hi, t_lo, h, w, pitch, scale, vec_in); break;
+    }
     RC_CUDA(cudaGetLastError());
     const long long rows = (long long)B * D;
     const int blocks = 148 * 8;
