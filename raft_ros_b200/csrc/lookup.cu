@@ -194,35 +194,60 @@ lookup_bwd_kernel(LevelPtrs glv, const float *__restrict__ coords, const float *
   __syncthreads();
 
   float *__restrict__ gvol = pick_level(glv, lvl);
+  // The read-modify-write of a patch is latency-bound (one dependent DRAM round trip per pixel), so
+  // PB pixels are handled together: all their loads are issued before the first add / store.  Rows
+  // of different query pixels never alias, which is what makes the reordering legal.
+  constexpr int PB = 2;
+  static_assert(kPixPerWarp % PB == 0, "pixel batch");
 #pragma unroll 1
-  for (int u = 0; u < kPixPerWarp; ++u) {
-    const int pix = warp * kPixPerWarp + u;
-    const int p = p0 + pix;
-    if (p >= N) break;  // warp-uniform
-    float dx, dy;
-    const float cx = __ldg(coords + ((size_t)b * 2 + 0) * N + p) * inv;
-    const float cy = __ldg(coords + ((size_t)b * 2 + 1) * N + p) * inv;
-    const int x0 = safe_floor_int(cx, &dx) - R;
-    const int y0 = safe_floor_int(cy, &dy) - R;
-    const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
-    const float w10 = dy * (1.0f - dx), w11 = dy * dx;
-    float *row = gvol + ((size_t)b * N + p) * ((size_t)hl * wl);
+  for (int u0 = 0; u0 < kPixPerWarp; u0 += PB) {
+    float *dst[PB][NE];
+    float add[PB][NE];
 #pragma unroll
-    for (int k = 0; k < NE; ++k) {
-      const int e = lane + 32 * k;
-      const int py = e / PN, px = e - py * PN;
-      const int gy = y0 + py, gx = x0 + px;
-      if (e < NPATCH && gy >= 0 && gy < hl && gx >= 0 && gx < wl) {
-        // patch cell (py,px) receives from taps (i,j) in {px-1,px} x {py-1,py}
-        float s = 0.0f;
-        if (py < RD && px < RD) s = tile[(px * RD + py) * TS + pix] * w00;
-        if (py < RD && px > 0) s = fmaf(tile[((px - 1) * RD + py) * TS + pix], w01, s);
-        if (py > 0 && px < RD) s = fmaf(tile[(px * RD + py - 1) * TS + pix], w10, s);
-        if (py > 0 && px > 0) s = fmaf(tile[((px - 1) * RD + py - 1) * TS + pix], w11, s);
-        float *dst = row + (size_t)gy * wl + gx;
-        *dst += s;
+    for (int v = 0; v < PB; ++v) {
+      const int pix = warp * kPixPerWarp + u0 + v;
+      const int p = p0 + pix;
+      const bool pvalid = p < N;  // warp-uniform
+      float dx = 0.f, dy = 0.f;
+      int x0 = 0, y0 = 0;
+      if (pvalid) {
+        const float cx = __ldg(coords + ((size_t)b * 2 + 0) * N + p) * inv;
+        const float cy = __ldg(coords + ((size_t)b * 2 + 1) * N + p) * inv;
+        x0 = safe_floor_int(cx, &dx) - R;
+        y0 = safe_floor_int(cy, &dy) - R;
+      }
+      const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
+      const float w10 = dy * (1.0f - dx), w11 = dy * dx;
+      float *row = gvol + ((size_t)b * N + (pvalid ? p : 0)) * ((size_t)hl * wl);
+#pragma unroll
+      for (int k = 0; k < NE; ++k) {
+        const int e = lane + 32 * k;
+        const int py = e / PN, px = e - py * PN;
+        const int gy = y0 + py, gx = x0 + px;
+        dst[v][k] = nullptr;
+        add[v][k] = 0.0f;
+        if (pvalid && e < NPATCH && gy >= 0 && gy < hl && gx >= 0 && gx < wl) {
+          // patch cell (py,px) receives from taps (i,j) in {px-1,px} x {py-1,py}
+          float s = 0.0f;
+          if (py < RD && px < RD) s = tile[(px * RD + py) * TS + pix] * w00;
+          if (py < RD && px > 0) s = fmaf(tile[((px - 1) * RD + py) * TS + pix], w01, s);
+          if (py > 0 && px < RD) s = fmaf(tile[(px * RD + py - 1) * TS + pix], w10, s);
+          if (py > 0 && px > 0) s = fmaf(tile[((px - 1) * RD + py - 1) * TS + pix], w11, s);
+          dst[v][k] = row + (size_t)gy * wl + gx;
+          add[v][k] = s;
+        }
       }
     }
+    float old[PB][NE];
+#pragma unroll
+    for (int v = 0; v < PB; ++v)
+#pragma unroll
+      for (int k = 0; k < NE; ++k) old[v][k] = dst[v][k] ? *dst[v][k] : 0.0f;
+#pragma unroll
+    for (int v = 0; v < PB; ++v)
+#pragma unroll
+      for (int k = 0; k < NE; ++k)
+        if (dst[v][k]) *dst[v][k] = old[v][k] + add[v][k];
   }
 }
 
