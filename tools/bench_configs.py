@@ -2,7 +2,7 @@
 comparators of BASELINE.md section 5 (the reference's own torch ops on the B200, and its
 unmodified alt_cuda_corr binary from oracle/_ref).  Prints one JSON object per measurement.
 
-    python tools/bench_configs.py [headline] [kitti] [train] [alt4k]
+    python tools/bench_configs.py [headline] [sintel32] [kitti] [train] [altsmall] [alt4k]
 """
 import json
 import os
@@ -137,9 +137,11 @@ def alt_case(H=270, W=480, name="alt_2160x3840"):
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["headline", "kitti", "train", "alt4k"]
+    which = sys.argv[1:] or ["headline", "sintel32", "kitti", "train", "alt4k"]
     if "headline" in which:
         fwd_case("sintel_440x1024_b8_k12", 8, 256, 55, 128, 12)
+    if "sintel32" in which:
+        fwd_case("sintel_440x1024_b8_k32", 8, 256, 55, 128, 32)
     if "kitti" in which:
         fwd_case("kitti_376x1248_b8_k24", 8, 256, 47, 156, 24)
     if "train" in which:
