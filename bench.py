@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--levels", type=int, default=4)
     ap.add_argument("--radius", type=int, default=4)
     ap.add_argument("--precision", default=os.environ.get("RAFT_CORR_PRECISION", "bf16x3"),
-                    choices=["fp32", "bf16x3", "bf16"])
+                    choices=["fp32", "bf16x3", "bf16", "bf16_vol16"])
     ap.add_argument("--l2-fetch", type=int, default=int(os.environ.get("RAFT_CORR_L2_FETCH", "0")),
                     help="set cudaLimitMaxL2FetchGranularity (32/64/128); 0 = leave the driver default")
     ap.add_argument("--layout", default=os.environ.get("RAFT_CORR_LAYOUT", "tiled"), choices=["tiled", "rows"],
@@ -56,12 +56,13 @@ def parse():
     return ap.parse_args()
 
 
-def algorithmic_bytes(B, N, D, h, w, L, r, K):
+def algorithmic_bytes(B, N, D, h, w, L, r, K, s_vol=4):
     """read both fmaps once, write every pyramid element once, and per
-    lookup read the (2r+2)^2 integer patch per level, write L*(2r+1)^2 fp32, read 2 coords."""
-    pyr = sum(N * (h >> l) * (w >> l) for l in range(L)) * 4
+    lookup read the (2r+2)^2 integer patch per level, write L*(2r+1)^2 fp32, read 2 coords.
+    s_vol = bytes per volume element (4, or 2 for precision bf16_vol16)."""
+    pyr = sum(N * (h >> l) * (w >> l) for l in range(L)) * s_vol
     build = B * (2 * N * D * 4 + pyr)
-    lookup = B * N * (L * (2 * r + 2) ** 2 * 4 + L * (2 * r + 1) ** 2 * 4 + 8)
+    lookup = B * N * (L * (2 * r + 2) ** 2 * s_vol + L * (2 * r + 1) ** 2 * 4 + 8)
     return build, lookup, build + K * lookup
 
 
@@ -358,7 +359,7 @@ def run_ours(args):
         return
 
     peak, peak_src = peaks()
-    b_build, b_look, b_total = algorithmic_bytes(B, N, D, h, w, L, r, K)
+    b_build, b_look, b_total = algorithmic_bytes(B, N, D, h, w, L, r, K, 2 if args.precision == "bf16_vol16" else 4)
     kern = {
         "build": {"launches_per_step": 2, "ms": build_ms, "alg_bytes": b_build, "gbs": b_build / (build_ms * 1e-3) / 1e9,
                   "share_of_step": build_ms / ms_step, "flops": 2.0 * B * N * N * D * (3 if args.precision == "bf16x3" else 1),
@@ -376,7 +377,8 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup"}[args.precision],
+        "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup",
+                  "bf16_vol16": "bf16 (f32 accumulate), fp16 volume + f32 lookup"}[args.precision],
         "data": "synthetic", "config": workload_config(args, "gpu"), "precision": args.precision,
         "roofline": roofline, "kernels": kern, "clocks": clocks, "gpu_launches": int(args.steps * (2 + K)),
         "l2_fetch_granularity": l2_fetch, "layout": "tiled" if tiled else "rows",

@@ -46,6 +46,10 @@ extern "C" {
 #define RC_PREC_BF16X3 1 /* tcgen05, bf16 hi/lo split operands, 3 MMAs, fp32 accumulate;  */
                          /* normwise error ~1e-5: the fp32-class tensor-core path         */
 #define RC_PREC_BF16 2   /* tcgen05, single bf16 pass, fp32 accumulate; ~2e-3 normwise    */
+#define RC_PREC_BF16_VOL16 3 /* RC_PREC_BF16 with the pyramid STORED as fp16 (saturating to  */
+                             /* +-65504): half the bytes of the build and of every lookup's  */
+                             /* reads; tiled layout only (rc_corr_build_pyramid_tiled +       */
+                             /* rc_corr_lookup_tiled16_fwd); +2.4e-4 relative storage error   */
 
 int rc_version(void);
 const char *rc_last_error(void);
@@ -136,7 +140,7 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
  * partial-sector writes on ragged widths: 2.3x slower build at 47x156).
  *
  * rc_corr_build_pyramid_tiled : rc_corr_build_pyramid writing that layout.  RC_PREC_BF16X3 /
- *                     RC_PREC_BF16 only, num_levels <= 4, level pointers 64-byte aligned and
+ *                     RC_PREC_BF16 (/ RC_PREC_BF16_VOL16, below) only, num_levels <= 4, level pointers 64-byte aligned and
  *                     rc_corr_tiled_level_elems floats each.  Same workspace as the row-layout build.
  * rc_corr_lookup_tiled_fwd    : rc_corr_lookup_fwd reading it.  Same coords / out contract;
  *                     radius 4 only.
@@ -156,6 +160,24 @@ int rc_corr_lookup_tiled_fwd(const float *const *level_ptrs, const float *coords
                              int h, int w, int num_levels, int radius, void *stream);
 int rc_corr_relayout_level(const float *src, float *dst, int B, int N, int hl, int wl, int to_tiled,
                            void *stream);
+
+/*
+ * The 16-bit flavour of the tiled layout (RC_PREC_BF16_VOL16): the same structure with fp16
+ * elements, tiles of 2 rows x 16 halves (still 64 B = 4 chunks of 16 B = 8 halves, chunk
+ * k = 2*(y%2) + (x%16)/8), wp = w_l rounded up to 16:
+ *     [B][ceil(h*w/32)][hp/2][wp/16][32 pixels][4 chunks][8 halves].
+ * rc_corr_tiled16_level_elems : number of fp16 elements of a level.
+ * rc_corr_build_pyramid_tiled  with precision = RC_PREC_BF16_VOL16 writes it (level pointers
+ *                     then address fp16 data).
+ * rc_corr_lookup_tiled16_fwd  : rc_corr_lookup_tiled_fwd reading it (fp32 interpolation and output).
+ * rc_corr_relayout16_level    : tiled fp16 -> row-layout fp32 (to_tiled = 0) or back (rounding,
+ *                     saturating; padding zeroed).
+ */
+int rc_corr_tiled16_level_elems(int B, int h, int w, int level, size_t *elems);
+int rc_corr_lookup_tiled16_fwd(const void *const *level_ptrs, const float *coords, float *out, int B,
+                               int h, int w, int num_levels, int radius, void *stream);
+int rc_corr_relayout16_level(const void *src, void *dst, int B, int N, int hl, int wl, int to_tiled,
+                             void *stream);
 
 /*
  * Gradient of the lookup w.r.t. the pyramid (coords carry no gradient: they are detached at

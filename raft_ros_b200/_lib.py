@@ -21,6 +21,7 @@ RC_OK = 0
 RC_PREC_FP32 = 0
 RC_PREC_BF16X3 = 1
 RC_PREC_BF16 = 2
+RC_PREC_BF16_VOL16 = 3
 RC_MAX_LEVELS = 8
 RC_MAX_RADIUS = 8
 
@@ -101,6 +102,9 @@ SIGNATURES = {
     "rc_corr_tiled_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
     "rc_corr_build_pyramid_tiled": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
     "rc_corr_relayout_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rc_corr_tiled16_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
+    "rc_corr_lookup_tiled16_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rc_corr_relayout16_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_tiled_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_bwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), _i, _i, _i, _i, _i, _vp]),
     "rc_corr_build_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),

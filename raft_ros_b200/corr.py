@@ -17,11 +17,13 @@ import torch
 
 from . import _lib
 
-_PRECISIONS = {"fp32": _lib.RC_PREC_FP32, "bf16x3": _lib.RC_PREC_BF16X3, "bf16": _lib.RC_PREC_BF16}
+_PRECISIONS = {"fp32": _lib.RC_PREC_FP32, "bf16x3": _lib.RC_PREC_BF16X3, "bf16": _lib.RC_PREC_BF16,
+               "bf16_vol16": _lib.RC_PREC_BF16_VOL16}
 
 #: arithmetic of the all-pairs contraction when the caller does not say: "bf16x3" is the
 #: fp32-class tensor-core path (error-compensated bf16 operands, ~1e-5 normwise), "bf16" the
-#: single-pass fast path, "fp32" plain fp32 FMA on CUDA cores.
+#: single-pass fast path, "fp32" plain fp32 FMA on CUDA cores, "bf16_vol16" = "bf16" with the
+#: pyramid stored as fp16 (inference with radius 4 and <= 4 levels only; half the HBM traffic).
 DEFAULT_PRECISION = os.environ.get("RAFT_CORR_PRECISION", "bf16x3")
 
 
@@ -89,16 +91,19 @@ def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
     return levels
 
 
-def tiled_level_elems(B: int, N: int, hl: int, wl: int) -> int:
-    """floats of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems):
-    [B][ceil(N/G)][hp/2][wp/8][G][2][8], G = rc_corr_tile_group()."""
+def tiled_level_elems(B: int, N: int, hl: int, wl: int, vol16: bool = False) -> int:
+    """elements of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems /
+    rc_corr_tiled16_level_elems): [B][ceil(N/G)][hp/2][wp/cw][G][2][cw], G = rc_corr_tile_group(),
+    cw = 8 floats or 16 halves."""
     G = int(_lib.lib().rc_corr_tile_group())
-    return B * ((N + G - 1) // G) * G * ((hl + 1) & ~1) * ((wl + 7) & ~7)
+    cw = 16 if vol16 else 8
+    return B * ((N + G - 1) // G) * G * ((hl + 1) & ~1) * ((wl + cw - 1) & ~(cw - 1))
 
 
 def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
                             precision: Optional[str] = None, scale: float = 0.0) -> List[torch.Tensor]:
-    """rc_corr_build_pyramid_tiled: (B,D,h,w) x2 -> list of flat fp32 levels in the TILED layout."""
+    """rc_corr_build_pyramid_tiled: (B,D,h,w) x2 -> list of flat levels in the TILED layout (fp32, or
+    fp16 for precision "bf16_vol16")."""
     _require_cuda(fmap1, "fmap1")
     _require_cuda(fmap2, "fmap2")
     if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
@@ -111,8 +116,9 @@ def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels
     prec = _precision_code(precision)
     L = _lib.lib()
     with torch.cuda.device(f1.device):
-        sizes = [tiled_level_elems(B, h * w, hl, wl) for hl, wl in shapes]  # multiples of 128 floats
-        flat = torch.empty(sum(sizes), dtype=torch.float32, device=f1.device)
+        vol16 = prec == _lib.RC_PREC_BF16_VOL16
+        sizes = [tiled_level_elems(B, h * w, hl, wl, vol16) for hl, wl in shapes]  # multiples of 64 bytes
+        flat = torch.empty(sum(sizes), dtype=torch.float16 if vol16 else torch.float32, device=f1.device)
         levels, o = [], 0
         for s_ in sizes:
             levels.append(flat[o:o + s_])
@@ -127,17 +133,23 @@ def build_pyramid_tiled_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels
     return levels
 
 
-def relayout_raw(src: torch.Tensor, B: int, N: int, hl: int, wl: int, to_tiled: bool) -> torch.Tensor:
-    """rc_corr_relayout_level: one level, row layout (B*N, 1, hl, wl) <-> tiled layout (flat)."""
+def relayout_raw(src: torch.Tensor, B: int, N: int, hl: int, wl: int, to_tiled: bool, vol16: bool = False) -> torch.Tensor:
+    """rc_corr_relayout_level / rc_corr_relayout16_level: one level, row layout (B*N, 1, hl, wl) fp32 <->
+    tiled layout (flat; fp16 when vol16)."""
     _require_cuda(src, "level")
-    s = src if (src.dtype == torch.float32 and src.is_contiguous()) else _f32c(src)
+    if to_tiled or not vol16:
+        s = src if (src.dtype == torch.float32 and src.is_contiguous()) else _f32c(src)
+    else:
+        s = src if (src.dtype == torch.float16 and src.is_contiguous()) else src.detach().half().contiguous()
     with torch.cuda.device(s.device):
         if to_tiled:
-            dst = torch.empty(tiled_level_elems(B, N, hl, wl), dtype=torch.float32, device=s.device)
+            dst = torch.empty(tiled_level_elems(B, N, hl, wl, vol16), dtype=torch.float16 if vol16 else torch.float32,
+                              device=s.device)
         else:
             dst = torch.empty((B * N, 1, hl, wl), dtype=torch.float32, device=s.device)
-        rc = _lib.lib().rc_corr_relayout_level(s.data_ptr(), dst.data_ptr(), B, N, hl, wl, 1 if to_tiled else 0, _stream())
-        _lib.check(rc, "rc_corr_relayout_level")
+        fn = _lib.lib().rc_corr_relayout16_level if vol16 else _lib.lib().rc_corr_relayout_level
+        rc = fn(s.data_ptr(), dst.data_ptr(), B, N, hl, wl, 1 if to_tiled else 0, _stream())
+        _lib.check(rc, "rc_corr_relayout16_level" if vol16 else "rc_corr_relayout_level")
     return dst
 
 
@@ -150,15 +162,17 @@ def lookup_tiled_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radiu
     B, _, h, w = c.shape
     nl = len(levels)
     shapes = level_shapes(h, w, nl)
+    vol16 = levels[0].dtype == torch.float16
     for l, (t, (hl, wl)) in enumerate(zip(levels, shapes)):
-        if t.numel() != tiled_level_elems(B, h * w, hl, wl) or t.dtype != torch.float32 or not t.is_contiguous():
+        if (t.numel() != tiled_level_elems(B, h * w, hl, wl, vol16) or t.dtype != levels[0].dtype
+                or t.dtype not in (torch.float32, torch.float16) or not t.is_contiguous()):
             raise RuntimeError(f"tiled level {l} does not match a {B}x{h}x{w} problem")
     rd = 2 * radius + 1
     with torch.cuda.device(c.device):
         out = torch.empty((B, nl * rd * rd, h, w), dtype=torch.float32, device=c.device)
-        rc = _lib.lib().rc_corr_lookup_tiled_fwd(_lib.ptr_array([t.data_ptr() for t in levels]), c.data_ptr(),
-                                                 out.data_ptr(), B, h, w, nl, radius, _stream())
-        _lib.check(rc, "rc_corr_lookup_tiled_fwd")
+        fn = _lib.lib().rc_corr_lookup_tiled16_fwd if vol16 else _lib.lib().rc_corr_lookup_tiled_fwd
+        rc = fn(_lib.ptr_array([t.data_ptr() for t in levels]), c.data_ptr(), out.data_ptr(), B, h, w, nl, radius, _stream())
+        _lib.check(rc, "rc_corr_lookup_tiled16_fwd" if vol16 else "rc_corr_lookup_tiled_fwd")
     return out
 
 
@@ -389,6 +403,11 @@ class CorrBlock:
         self._rows = None       # row-layout levels (reference attribute), lazily made from _tiled
         self._geom = None
         tiled = _use_tiled(num_levels, radius, precision)
+        if _precision_code(precision) == _lib.RC_PREC_BF16_VOL16:
+            # the fp16 volume exists only where the fused tiled kernels do
+            if not tiled or (torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)):
+                raise RuntimeError("precision 'bf16_vol16' is an inference mode for radius 4 and at most 4 levels "
+                                   "(tiled layout); use 'bf16' or 'bf16x3' here")
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
             self._state = _GradState()
             out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state, tiled)
@@ -407,7 +426,7 @@ class CorrBlock:
             self._rows = list(_UntileFn.apply(self._token, self._state))
         if self._rows is None:
             B, h, w = self._geom
-            self._rows = [relayout_raw(t, B, h * w, hl, wl, to_tiled=False)
+            self._rows = [relayout_raw(t, B, h * w, hl, wl, to_tiled=False, vol16=t.dtype == torch.float16)
                           for t, (hl, wl) in zip(self._tiled, level_shapes(h, w, self.num_levels))]
         return self._rows
 
@@ -468,6 +487,8 @@ class AlternateCorrBlock:
             fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
             self.pyramid.append((fmap1, fmap2))
         self._prec = _precision_code(precision)
+        if self._prec == _lib.RC_PREC_BF16_VOL16:
+            raise ValueError("precision 'bf16_vol16' applies to CorrBlock (there is no volume here); use 'bf16'")
         f1, f2 = self.pyramid[0]
         self._tc = (self._prec != _lib.RC_PREC_FP32 and radius == 4 and 1 <= num_levels <= 4
                     and f1.shape == f2.shape and f1.dim() == 4)

@@ -147,7 +147,7 @@ int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, i
   if (int rc = check_geometry("rc_corr_build_pyramid_tiled", B, h, w, num_levels)) return rc;
   RC_CHECK_ARG(fmap1 && fmap2 && level_ptrs, "rc_corr_build_pyramid_tiled: null pointer");
   RC_CHECK_ARG(D > 0, "rc_corr_build_pyramid_tiled: D must be positive");
-  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16) {
+  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16 && precision != RC_PREC_BF16_VOL16) {
     set_error("rc_corr_build_pyramid_tiled: only the tensor-core precisions write the tiled layout (got %d)",
               precision);
     return RC_ERR_UNSUPPORTED;
@@ -160,6 +160,36 @@ int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, i
   if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
   return launch_build_tc_tiled(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale, workspace,
                                workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_tiled16_level_elems(int B, int h, int w, int level, size_t *elems) {
+  RC_CHECK_ARG(elems, "rc_corr_tiled16_level_elems: null output");
+  RC_CHECK_ARG(B > 0, "rc_corr_tiled16_level_elems: B must be positive");
+  int hl = 0, wl = 0;
+  if (int rc = rc_level_dims(h, w, level, &hl, &wl)) return rc;
+  const size_t groups = (size_t)B * (((size_t)h * w + RC_TILE_GROUP - 1) / RC_TILE_GROUP);
+  *elems = groups * RC_TILE_GROUP * (size_t)((hl + 1) & ~1) * (size_t)((wl + 15) & ~15);
+  return RC_OK;
+}
+
+int rc_corr_lookup_tiled16_fwd(const void *const *level_ptrs, const float *coords, float *out, int B,
+                               int h, int w, int num_levels, int radius, void *stream) {
+  if (int rc = check_geometry("rc_corr_lookup_tiled16_fwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(level_ptrs && coords && out, "rc_corr_lookup_tiled16_fwd: null pointer");
+  ConstLevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_lookup_tiled16_fwd: level %d pointer is null", l);
+    RC_CHECK_ARG((reinterpret_cast<uintptr_t>(level_ptrs[l]) & 15) == 0, "rc_corr_lookup_tiled16_fwd: level %d must be 16-byte aligned", l);
+    lv.p[l] = static_cast<const float *>(level_ptrs[l]);
+  }
+  return launch_lookup_tiled16_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_relayout16_level(const void *src, void *dst, int B, int N, int hl, int wl, int to_tiled,
+                             void *stream) {
+  RC_CHECK_ARG(src && dst, "rc_corr_relayout16_level: null pointer");
+  RC_CHECK_ARG(B > 0 && N > 0 && hl > 0 && wl > 0, "rc_corr_relayout16_level: bad shape");
+  return launch_relayout16(src, dst, B, N, hl, wl, to_tiled != 0, static_cast<cudaStream_t>(stream));
 }
 
 int rc_corr_relayout_level(const float *src, float *dst, int B, int N, int hl, int wl, int to_tiled,

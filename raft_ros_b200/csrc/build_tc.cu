@@ -23,6 +23,7 @@
 //                 i+1 overlap the epilogue of tile i.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cstdlib>
 #include <mutex>
@@ -83,12 +84,15 @@ struct Cfg {
 // four whole tiles per query pixel, one store instruction writes one tile of 8 pixels = 512
 // contiguous bytes, and every tile is 64 B aligned whatever h and w are, so the stores are whole
 // 128 B lines for ragged sizes too.
-template <int NPASS, int NCTA, bool TILED>
+// V16 (TILED only): the volume is stored as fp16 (saturating), tiles of 2 rows x 16 halves = the
+// same 64 B / 4 chunks per pixel, so the layout code is shared: the warp's row pair is two tiles.
+template <int NPASS, int NCTA, bool TILED, bool V16 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                 const Params P) {
   using C = Cfg<NPASS, NCTA>;
+  static_assert(!V16 || TILED, "the 16-bit volume exists in the tiled layout only");
   // NCTA == 2: the kernel runs as clusters of two CTAs on one TPC.  The pair computes a 256 x 256
   // tile with tcgen05.mma.cta_group::2: each CTA stages its own 128 query pixels (A) and HALF of
   // the patch (B, 4 of the 8 rows), which halves the B-operand shared-memory traffic per SM;
@@ -261,11 +265,19 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
       // tiled layout: the patch's first tile (tile-row 0) of the warp's group of 32 query pixels
       constexpr int G = kTileGroup, TS = 16 * G;  // query pixels per group, floats per tile of a group
       const size_t grp0 = (size_t)b * P.ng + prow0 / G;  // prow0 is a multiple of 32 = G
-      float *const g0 = TILED ? P.lv.p[0] + grp0 * pitch0 + nx * (4 * TS) : P.lv.p[0] + grow0 * pitch0 + x0;
-      float *const g1 = TILED ? P.lv.p[1] + grp0 * pitch1 + nx * (2 * TS) : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
-      float *const g2 = TILED ? P.lv.p[2] + grp0 * pitch2 + nx * TS : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
-      float *const g3 = TILED ? P.lv.p[3] + grp0 * pitch3 + (nx >> 1) * TS + lane * 16
-                              : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
+      // (V16: the same expressions in 32-bit words; a tile is 16 columns wide, so half as many tiles per patch)
+      float *const g0 = V16     ? P.lv.p[0] + grp0 * pitch0 + nx * (2 * TS)
+                        : TILED ? P.lv.p[0] + grp0 * pitch0 + nx * (4 * TS)
+                                : P.lv.p[0] + grow0 * pitch0 + x0;
+      float *const g1 = V16     ? P.lv.p[1] + grp0 * pitch1 + nx * TS
+                        : TILED ? P.lv.p[1] + grp0 * pitch1 + nx * (2 * TS)
+                                : P.lv.p[1] + grow0 * pitch1 + (x0 >> 1);
+      float *const g2 = V16     ? P.lv.p[2] + grp0 * pitch2 + (nx >> 1) * TS + lane * 16
+                        : TILED ? P.lv.p[2] + grp0 * pitch2 + nx * TS
+                                : P.lv.p[2] + grow0 * pitch2 + (x0 >> 2);
+      float *const g3 = V16     ? P.lv.p[3] + grp0 * pitch3 + (nx >> 2) * TS + lane * 16
+                        : TILED ? P.lv.p[3] + grp0 * pitch3 + (nx >> 1) * TS + lane * 16
+                                : P.lv.p[3] + (grow0 + lane) * pitch3 + (x0 >> 3);  // direct: thread <-> row
       // TILED: the staging buffer may still be being read by this warp's last bulk store
       auto buf_ready = [&]() {
         if (lane == 0) bulk_wait_read0();
@@ -277,6 +289,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         buf_ready();
         if (rows_valid >= 32 && tiles_valid >= 2) bulk_tiles32(buf, ch, lane, gdst);
         else store_tiles32<G>(buf, ch, lane, gdst, rows_valid, tiles_valid);
+      };
+      // V16: pack two neighbouring columns into one word of fp16 (saturating: no infinities)
+      auto pack = [](float lo_col, float hi_col) {
+        uint32_t r;
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_col), "f"(lo_col));
+        return __uint_as_float(r);
       };
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
@@ -308,7 +326,20 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           v1[i] *= P.scale;
         }
         const int y0 = ny * PH + hf * 4 + 2 * j;
-        if constexpr (TILED) {
+        if constexpr (V16) {
+          // rows y0, y0+1 x 32 columns = two tiles of 2 x 16 halves
+          if (y0 < h) {
+            float ch[32];
+#pragma unroll
+            for (int t2 = 0; t2 < 2; ++t2)
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                ch[16 * t2 + i] = pack(v0[16 * t2 + 2 * i], v0[16 * t2 + 2 * i + 1]);
+                ch[16 * t2 + 8 + i] = pack(v1[16 * t2 + 2 * i], v1[16 * t2 + 2 * i + 1]);
+              }
+            put_tiles(ch, g0 + (size_t)(y0 >> 1) * (P.tpr[0] * TS), P.tpr[0] - nx * 2);
+          }
+        } else if constexpr (TILED) {
           // rows y0, y0+1 = one tile-row; columns beyond w (and row h of an odd h) are zero accumulators
           if (y0 < h) {
             float *const gt = g0 + (size_t)(y0 >> 1) * (P.tpr[0] * TS);
@@ -347,7 +378,21 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
               for (int i = 0; i < 16; ++i)
                 if (nx * 16 + i >= w1 || y1 >= h1) l1[i] = 0.0f;
             }
-            if (j == 1 && y1 - 1 < h1) {
+            if (V16 && j == 1 && y1 - 1 < h1) {
+              // two rows x 16 columns = ONE tile: 64 B per pixel, stored straight from registers
+              // (four 16 B chunks at their swizzled positions; a 2 KB run per warp)
+              if (lane < rows_valid && nx < P.tpr[1]) {
+                float *gt = g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS) + lane * 16;
+                const int sw = tile_sw(lane);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float *src = (k >> 1) ? l1 : l1prev;
+                  const int c0 = (k & 1) * 8;
+                  stg128(gt + ((k ^ sw) << 2), make_float4(pack(src[c0], src[c0 + 1]), pack(src[c0 + 2], src[c0 + 3]),
+                                                          pack(src[c0 + 4], src[c0 + 5]), pack(src[c0 + 6], src[c0 + 7])));
+                }
+              }
+            } else if (!V16 && j == 1 && y1 - 1 < h1) {
               float ch[32];
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -380,8 +425,14 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                   for (int i = 0; i < 8; ++i)
                     if (nx * 8 + i >= w2 || y2 >= h2) l2[i] = 0.0f;
                 }
-                // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
-                if (2 * ny < h2) {
+                if constexpr (V16) {
+                  // one patch = half a level-2 tile (8 of its 16 columns); this warp holds row hf of it:
+                  // chunk 2 hf + (nx & 1), 16 B per pixel
+                  if (2 * ny < h2 && (nx >> 1) < P.tpr[2] && lane < rows_valid)
+                    stg128(g2 + (size_t)ny * (P.tpr[2] * TS) + ((((hf << 1) | (nx & 1)) ^ tile_sw(lane)) << 2),
+                           make_float4(pack(l2[0], l2[1]), pack(l2[2], l2[3]), pack(l2[4], l2[5]), pack(l2[6], l2[7])));
+                } else if (2 * ny < h2) {
+                  // one patch = one level-2 tile; this warp holds its row hf (8 floats = one 32 B sector)
                   buf_ready();
                   store_halftile8<G>(buf, l2, lane, g2 + (size_t)ny * (P.tpr[2] * TS), hf, rows_valid, nx < P.tpr[2]);
                 }
@@ -419,6 +470,17 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
 #pragma unroll
             for (int i = 0; i < 4; ++i)
               if (i >= cv3 || ny >= h3) l3[i] = 0.0f;
+            if constexpr (V16) {
+              // an eighth of a level-3 tile: row ny & 1, columns 4 (nx & 3) .. +3 = half of chunk
+              // 2 (ny & 1) + ((nx >> 1) & 1).  The last patch column also zeroes the half chunk
+              // that no patch covers (a lookup may fetch it).
+              if (ny < ((h3 + 1) & ~1) && (nx >> 2) < P.tpr[3] && lane < rows_valid) {
+                float *d = g3 + (size_t)(ny >> 1) * (P.tpr[3] * TS) +
+                           (((((ny & 1) << 1) | ((nx >> 1) & 1)) ^ tile_sw(lane)) << 2) + (nx & 1) * 2;
+                *reinterpret_cast<float2 *>(d) = make_float2(pack(l3[0], l3[1]), pack(l3[2], l3[3]));
+                if ((nx & 1) == 0 && nx + 1 >= P.nt_x) *reinterpret_cast<float2 *>(d + 2) = make_float2(0.f, 0.f);
+              }
+            } else
             // a quarter of a level-3 tile: row ny & 1, columns 4 (nx & 1) .. +3 (16 B, always aligned)
             if (ny < ((h3 + 1) & ~1) && (nx >> 1) < P.tpr[3] && lane < rows_valid)
               stg128(g3 + (size_t)(ny >> 1) * (P.tpr[3] * TS) + (((((ny & 1) << 1) | (nx & 1)) ^ tile_sw(lane)) << 2),
@@ -529,12 +591,12 @@ static int sm_count() {
   return n;
 }
 
-template <int NPASS, int NCTA, bool TILED>
+template <int NPASS, int NCTA, bool TILED, bool V16 = false>
 static int launch(const CUtensorMap &ah, const CUtensorMap &al, const CUtensorMap &bh, const CUtensorMap &bl,
                   const Params &P, cudaStream_t st) {
   using C = Cfg<NPASS, NCTA>;
   static_assert(C::kSmemBytes <= 227 * 1024, "shared memory budget");
-  auto kern = build_tc_kernel<NPASS, NCTA, TILED>;
+  auto kern = build_tc_kernel<NPASS, NCTA, TILED, V16>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
   const long long units = sm_count() / NCTA;  // one CTA (or CTA pair) per SM (per TPC)
   const unsigned grid = (unsigned)((P.total_tiles < units ? P.total_tiles : units) * NCTA);
@@ -590,6 +652,11 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   }
   const int N = h * w, Dp = round_up64(D);
   const bool x3 = precision == RC_PREC_BF16X3;
+  const bool v16 = precision == RC_PREC_BF16_VOL16;
+  if (v16 && !tiled) {
+    set_error("RC_PREC_BF16_VOL16 exists in the tiled layout only (rc_corr_build_pyramid_tiled)");
+    return RC_ERR_UNSUPPORTED;
+  }
   const int ncta = tc::ctas_per_tile();
   const size_t per_map = ((size_t)B * N * Dp * 2 + 255) / 256 * 256;
   uint8_t *base = static_cast<uint8_t *>(ws);
@@ -637,9 +704,11 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   }
   for (int l = L; l < 4; ++l) P.lv.p[l] = lv.p[0];  // never dereferenced; keeps the table non-null
   for (int l = 0; l < 4; ++l) {
-    const int hp = ((h >> l) + 1) & ~1, wp = ((w >> l) + 7) & ~7;
-    P.tpr[l] = wp >> 3;
-    P.gstride[l] = (long long)hp * wp * kTileGroup;
+    // tile = 2 rows x 8 floats, or 2 rows x 16 halves; gstride in 32-bit words
+    const int cw = v16 ? 16 : 8;
+    const int hp = ((h >> l) + 1) & ~1, wp = ((w >> l) + cw - 1) & ~(cw - 1);
+    P.tpr[l] = wp / cw;
+    P.gstride[l] = (long long)hp * wp * kTileGroup / (v16 ? 2 : 1);
   }
 
   P.ng = (N + kTileGroup - 1) / kTileGroup;
@@ -655,7 +724,10 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
         set_error("rc_corr_build_pyramid_tiled: level %d must be 64-byte aligned", l);
         return RC_ERR_INVALID;
       }
-    if (ncta == 2)
+    if (v16)
+      rc = ncta == 2 ? tc::launch<1, 2, true, true>(tmAh, tmAl, tmBh, tmBl, P, st)
+                     : tc::launch<1, 1, true, true>(tmAh, tmAl, tmBh, tmBl, P, st);
+    else if (ncta == 2)
       rc = x3 ? tc::launch<3, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st);
     else
       rc = x3 ? tc::launch<3, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st);
@@ -714,6 +786,44 @@ int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, 
   if (blocks > 148LL * 32) blocks = 148LL * 32;
   if (to_tiled) relayout_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
   else relayout_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+// The same for the 16-bit volume: tiled fp16 (tiles of 2 rows x 16 halves) <-> row-layout fp32.
+template <bool TO_TILED>
+__global__ void __launch_bounds__(256)
+relayout16_kernel(const void *__restrict__ src_, void *__restrict__ dst_, int B, int N, int hl, int wl) {
+  const int hp = (hl + 1) & ~1, wp = (wl + 15) & ~15, tpr = wp >> 4;
+  constexpr int G = kTileGroup;
+  const int ng = (N + G - 1) / G;
+  const long long gstride = (long long)hp * wp * G, total = (long long)B * ng * gstride;  // in halves
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long grp = i / gstride;
+    const int e = (int)(i - grp * gstride);
+    const int tile = e / (32 * G), u = (e >> 5) % G;   // 32 halves per pixel per tile
+    const int k = ((e >> 3) & 3) ^ ((u >> 1) & 3);    // chunk stored at this position
+    const int ty = tile / tpr, tx = tile - ty * tpr;
+    const int y = ty * 2 + (k >> 1), x = tx * 16 + (k & 1) * 8 + (e & 7);
+    const int b = (int)(grp / ng), p = (int)(grp - (long long)b * ng) * G + u;
+    const bool inside = y < hl && x < wl && p < N;
+    const long long r = ((long long)b * N + p) * hl * wl + (long long)y * wl + x;
+    if (TO_TILED) {
+      const float v = inside ? __ldg(static_cast<const float *>(src_) + r) : 0.0f;
+      static_cast<__half *>(dst_)[i] = __float2half_rn(fminf(fmaxf(v, -65504.0f), 65504.0f));
+    } else if (inside) {
+      static_cast<float *>(dst_)[r] = __half2float(static_cast<const __half *>(src_)[i]);
+    }
+  }
+}
+
+int launch_relayout16(const void *src, void *dst, int B, int N, int hl, int wl, bool to_tiled, cudaStream_t st) {
+  const long long total = (long long)B * ((N + kTileGroup - 1) / kTileGroup) * kTileGroup * ((hl + 1) & ~1) * ((wl + 15) & ~15);
+  if (total <= 0) return RC_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148LL * 32) blocks = 148LL * 32;
+  if (to_tiled) relayout16_kernel<true><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
+  else relayout16_kernel<false><<<(unsigned)blocks, 256, 0, st>>>(src, dst, B, N, hl, wl);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
 }

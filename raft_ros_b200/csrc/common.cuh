@@ -52,6 +52,10 @@ int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h,
                           size_t ws_bytes, cudaStream_t st);
 int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, bool to_tiled,
                     cudaStream_t st);
+int launch_relayout16(const void *src, void *dst, int B, int N, int hl, int wl, bool to_tiled,
+                      cudaStream_t st);
+int launch_lookup_tiled16_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
+                              int w, int L, int r, cudaStream_t st);
 int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
                       int w, int L, int r, cudaStream_t st);
 int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,

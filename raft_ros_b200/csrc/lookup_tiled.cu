@@ -21,6 +21,8 @@
 //           separable bilinear interpolation from registers, 21 taps per lane;
 //   store   straight from registers: the 8 pixels of a warp are contiguous in the output, so every
 //           store instruction writes whole 32 B sectors.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace rc {
@@ -68,6 +70,10 @@ struct TlCtx {
   float fx, fy;
 };
 
+// V16: the volume is fp16, tiles of 2 rows x 16 halves (same 64 B, same 4 chunks of 16 B = 8 halves):
+// a window row is 2-3 pieces of 8 halves from a multiple-of-8 column, kept as halves in shared memory
+// (48 B per row) and converted when the taps read them; interpolation and output stay fp32.
+template <bool V16>
 __global__ void __launch_bounds__(kTlThreads)
 lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__restrict__ out, int B, int h, int w,
                         int L, int groups_per_item, int total_items) {
@@ -128,26 +134,35 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   auto issue = [&](const TlCtx &c, int stage) {
     if (c.valid) {
       const int hl = h >> c.lvl, wl = w >> c.lvl;
-      const int hp = (hl + 1) & ~1, wp = (wl + 7) & ~7, tpr = wp >> 3;  // tiles per tile-row
-      const int wb = (wl + 3) & ~3;
-      const int cg = (c.x0 & ~3) + 4 * tc;
-      const bool okx = (tc < 3 || (c.x0 & 3) == 3) && (unsigned)cg < (unsigned)wb;
+      constexpr int CW = V16 ? 16 : 8;       // columns per tile
+      constexpr int PC = V16 ? 8 : 4;        // columns per 16 B piece
+      const int hp = (hl + 1) & ~1, wp = (wl + CW - 1) & ~(CW - 1), tpr = wp / CW;  // tiles per tile-row
+      const int wb = (wl + PC - 1) & ~(PC - 1);
+      const int cg = (c.x0 & ~(PC - 1)) + PC * tc;
+      // pieces a window of 10 columns needs from a multiple-of-PC start: 3, or 4 at offset 3 (fp32);
+      // 2, or 3 at offset 7 (fp16)
+      const bool want = V16 ? (tc < 2 || (tc == 2 && (c.x0 & 7) == 7)) : (tc < 3 || (c.x0 & 3) == 3);
+      const bool okx = want && (unsigned)cg < (unsigned)wb;
       // group of G = 32 query pixels: [tile][pixel u][4 chunks], chunk k = 2*(row & 1) + (column half) stored
-      // at position k ^ ((u >> 1) & 3) (the build's bank-conflict-free staging order, build_tc.cu)
+      // at position k ^ ((u >> 1) & 3) (the build's bank-conflict-free staging order, build_tc.cu).
+      // Offsets are in 32-bit words for both element types (a pixel's tile is 16 words).
       constexpr int G = kTileGroup;
       const int ng = (N + G - 1) / G;
       const size_t grp = (size_t)c.b * ng + c.p0 / G;
-      const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg >> 2) & 1;
-      const float *base = pick_level(lv, c.lvl) + grp * (size_t)(hp * wp * G) + ((cg >> 3) * (16 * G) + u * 16);
-      const int trs = tpr * 16 * G;  // floats per tile-row of a group
+      const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg / PC) & 1;
+      const size_t gwords = (size_t)(hp * wp) * G / (V16 ? 2 : 1);
+      const float *base = pick_level(lv, c.lvl) + grp * gwords + ((cg / CW) * (16 * G) + u * 16);
+      const int trs = tpr * 16 * G;  // words per tile-row of a group
       const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);  // chunk position for even / odd rows
+      constexpr unsigned RB = V16 ? 48u : (unsigned)PS * 4u;  // bytes per patch row in shared memory
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
       for (int r = 0; r < 10; ++r) {
         const int ya = c.y0 + r;
         const bool ok = okx && (unsigned)ya < (unsigned)hl;
         const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
-        copy16(dst + (unsigned)(r * PS) * 4u, ok ? base + off : pick_level(lv, 0), ok);
+        // (fp16 rows hold three pieces: the 4th lane of a pixel has nothing to write)
+        if (!V16 || tc < 3) copy16(dst + (unsigned)r * RB, ok ? base + off : pick_level(lv, 0), ok);
       }
     }
     cp_async_commit();  // always commit (possibly empty) so that the wait counts stay uniform
@@ -175,17 +190,21 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
     // ---- taps: lane (tu, tc) owns window columns 2tc, 2tc+1 and a share of column 8 of pixel tu
     const float dx = cur.fx, dy = cur.fy;
     const float ex = 1.0f - dx, ey = 1.0f - dy;
-    const float *pp = ring + stage * kTlStageFloats + tu * kTlPatch + (cur.x0 & 3);
+    const float *pbase = ring + stage * kTlStageFloats + tu * kTlPatch;
+    // element (row j, window column i) of the patch, as fp32
+    auto at = [&](int j, int i) -> float {
+      if constexpr (V16) return __half2float(reinterpret_cast<const __half *>(pbase)[j * 24 + (cur.x0 & 7) + i]);
+      else return pbase[j * PS + (cur.x0 & 3) + i];
+    };
     const int p = cur.p0 + tu;
     float *o = out + ((size_t)cur.b * CH + (size_t)cur.lvl * NTAP) * N + p;
     const bool pv = p < N;
     {
       // columns 2tc, 2tc+1: horizontal interpolation of the 10 rows, then vertical pairs
-      const float *q = pp + 2 * tc;
       float h0[10], h1[10];
 #pragma unroll
       for (int j = 0; j < 10; ++j) {
-        const float a = q[j * PS], b = q[j * PS + 1], d = q[j * PS + 2];
+        const float a = at(j, 2 * tc), b = at(j, 2 * tc + 1), d = at(j, 2 * tc + 2);
         h0[j] = fmaf(b, dx, a * ex);
         h1[j] = fmaf(d, dx, b * ex);
       }
@@ -200,12 +219,11 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
     }
     {
       // column 8, rows shared out over the 4 lanes of the pixel: lane tc takes j = tc, tc+4 (and 8 for tc = 0)
-      const float *q = pp + 8;
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const int j = tc + 4 * k;
         if (j < RD && (k < 2 || tc == 0)) {
-          const float a = q[j * PS], b = q[j * PS + 1], c2 = q[(j + 1) * PS], d2 = q[(j + 1) * PS + 1];
+          const float a = at(j, 8), b = at(j, 9), c2 = at(j + 1, 8), d2 = at(j + 1, 9);
           const float top = fmaf(b, dx, a * ex), bot = fmaf(d2, dx, c2 * ex);
           if (pv) RC_TL_ST(o + (size_t)(8 * RD + j) * N, fmaf(bot, dy, top * ey));
         }
@@ -220,17 +238,18 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   cp_async_wait<0>();
 }
 
-int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
-                            cudaStream_t st) {
+template <bool V16>
+static int launch_tiled(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
+                        cudaStream_t st, const char *fn) {
   if (r != 4) {
-    set_error("rc_corr_lookup_tiled_fwd: radius %d unsupported on the tiled layout (4 only)", r);
+    set_error("%s: radius %d unsupported on the tiled layout (4 only)", fn, r);
     return RC_ERR_UNSUPPORTED;
   }
   const int N = h * w;
   const int groups = (N + kTlPix - 1) / kTlPix;
   const long long total = (long long)L * B * groups;
   if (total + 4LL * 148 * 32 * kTlWarps > 0x7fffffffLL) {
-    set_error("rc_corr_lookup_tiled_fwd: problem too large");
+    set_error("%s: problem too large", fn);
     return RC_ERR_UNSUPPORTED;
   }
   const size_t smem = sizeof(float) * (size_t)(kTlWarps * kTlStages * kTlStageFloats);
@@ -241,9 +260,9 @@ int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float
   int cached = (dev >= 0 && dev < 64) ? __atomic_load_n(&resident[dev], __ATOMIC_ACQUIRE) : 0;
   if (cached == 0) {
     int sms = 0, ctas_per_sm = 0;
-    RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel<V16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel, kTlThreads, smem));
+    RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel<V16>, kTlThreads, smem));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     cached = sms * ctas_per_sm;
     if (dev >= 0 && dev < 64) __atomic_store_n(&resident[dev], cached, __ATOMIC_RELEASE);
@@ -251,9 +270,19 @@ int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float
   long long grid = cached;
   const long long need = (total + kTlWarps - 1) / kTlWarps;
   if (grid > need) grid = need;
-  lookup_tiled_fwd_kernel<<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);
+  lookup_tiled_fwd_kernel<V16><<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
+}
+
+int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
+                            cudaStream_t st) {
+  return launch_tiled<false>(lv, coords, out, B, h, w, L, r, st, "rc_corr_lookup_tiled_fwd");
+}
+
+int launch_lookup_tiled16_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
+                              cudaStream_t st) {
+  return launch_tiled<true>(lv, coords, out, B, h, w, L, r, st, "rc_corr_lookup_tiled16_fwd");
 }
 
 }  // namespace rc

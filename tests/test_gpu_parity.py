@@ -615,6 +615,83 @@ def test_tiled_build_equals_row_build(rr, geom, prec):
         assert relmax(n(out), n(want)) <= 2e-6, (geom, prec, kind, relmax(n(out), n(want)))
 
 
+@pytest.mark.parametrize("geom", [(1, 64, 8, 32, 4), (2, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 256, 47, 156, 4),
+                                  (1, 128, 17, 20, 4), (2, 200, 16, 18, 2), (1, 64, 9, 65, 1), (1, 256, 55, 128, 4),
+                                  (1, 256, 50, 90, 4), (1, 32, 40, 160, 4)])
+def test_vol16_build_and_lookup(rr, geom):
+    """precision 'bf16_vol16': the pyramid stored as fp16 in the tiled layout.  (a) Untiled, it equals
+    the 'bf16' build rounded to fp16 (same accumulators, same pooling order, one rounding at the store);
+    (b) the fp16 lookup equals the fp32-layout lookup on exactly those rounded values; (c) against the
+    oracle the error stays within the bf16 bound plus the fp16 storage rounding; (d) buffers are
+    pre-filled with NaN so that anything read but never written would show."""
+    from raft_ros_b200 import _lib
+    from raft_ros_b200.corr import build_pyramid_raw, lookup_raw, relayout_raw, tiled_level_elems
+    B, D, h, w, L = geom
+    rng = np.random.default_rng(seed_of(geom, "vol16"))
+    f1n = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2n = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f1, f2 = t(f1n), t(f2n)
+    rows = build_pyramid_raw(f1, f2, L, "bf16")
+    lib = _lib.lib()
+    shapes = O.level_shapes(h, w, L)
+    N = h * w
+    tiled = [torch.full((tiled_level_elems(B, N, hl, wl, True),), float("nan"), dtype=torch.float16, device=DEV)
+             for hl, wl in shapes]
+    ws_bytes = int(lib.rc_corr_build_workspace_bytes(B, D, h, w, 3))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    rc = lib.rc_corr_build_pyramid_tiled(f1.data_ptr(), f2.data_ptr(), B, D, h, w,
+                                         _lib.ptr_array([x.data_ptr() for x in tiled]), L, 3, 0.0, ws.data_ptr(),
+                                         ws_bytes, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.rc_last_error()
+    torch.cuda.synchronize()
+    rounded = []
+    for l, (hl, wl) in enumerate(shapes):
+        back = relayout_raw(tiled[l], B, N, hl, wl, to_tiled=False, vol16=True)
+        want = rows[l].half().float()
+        assert torch.equal(back, want), (geom, l, float((back - want).abs().max()))
+        rounded.append(want)
+        # and the converter's own rows -> tiled direction agrees with what the build wrote (where written)
+        again = relayout_raw(rows[l], B, N, hl, wl, to_tiled=True, vol16=True)
+        assert torch.equal(relayout_raw(again, B, N, hl, wl, to_tiled=False, vol16=True), want)
+    for kind in ("sigma4", "border", "oob", "grid"):
+        coords = t(make_coords(kind, B, h, w, rng))
+        out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
+        rc = lib.rc_corr_lookup_tiled16_fwd(_lib.ptr_array([x.data_ptr() for x in tiled]), coords.data_ptr(),
+                                            out.data_ptr(), B, h, w, L, 4, torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, lib.rc_last_error()
+        want = lookup_raw(rounded, coords, 4)
+        assert torch.isfinite(out).all(), (geom, kind)
+        assert relmax(n(out), n(want)) <= 2e-6, (geom, kind, relmax(n(out), n(want)))
+    want_pyr = O.corr_build(f1n, f2n, L)
+    for l in range(L):
+        assert normwise(n(rounded[l]), want_pyr[l]) <= BUILD_TOL["bf16"]["norm"] + 5e-4, (geom, l)
+
+
+def test_vol16_corrblock_and_limits(rr):
+    """CorrBlock(precision='bf16_vol16'): fp16 tiled pyramid inside, fp32 `corr_pyramid` outside; training,
+    other radii and AlternateCorrBlock refuse it; values beyond the fp16 range saturate instead of overflowing."""
+    rng = np.random.default_rng(5)
+    B, D, h, w = 1, 64, 24, 40
+    f1 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, h, w)).astype(np.float32))
+    coords = t(make_coords("sigma4", B, h, w, rng))
+    blk = rr.CorrBlock(f1, f2, precision="bf16_vol16")
+    assert blk._tiled[0].dtype == torch.float16
+    ref = rr.CorrBlock(f1, f2, precision="bf16")
+    assert relmax(n(blk(coords)), n(ref(coords))) <= 1e-3
+    assert blk.corr_pyramid[0].dtype == torch.float32 and blk.corr_pyramid[0].shape == ref.corr_pyramid[0].shape
+    with pytest.raises(RuntimeError, match="bf16_vol16"):
+        rr.CorrBlock(f1, f2, radius=3, precision="bf16_vol16")
+    with pytest.raises(RuntimeError, match="bf16_vol16"):
+        rr.CorrBlock(f1.clone().requires_grad_(True), f2, precision="bf16_vol16")
+    with pytest.raises(ValueError, match="bf16_vol16"):
+        rr.AlternateCorrBlock(f1, f2, precision="bf16_vol16")
+    big = rr.CorrBlock(f1 * 3e3, f2 * 3e3, precision="bf16_vol16")  # |corr| up to ~1e7 > 65504
+    lv0 = big.corr_pyramid[0]
+    assert torch.isfinite(lv0).all() and float(lv0.abs().max()) == 65504.0
+    assert torch.isfinite(big(coords)).all()
+
+
 def test_tiled_build_rejects(rr):
     from raft_ros_b200 import _lib
     lib = _lib.lib()
