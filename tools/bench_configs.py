@@ -42,7 +42,7 @@ def inputs(B, D, h, w, K, seed=1234):
     return f1, f2, coords
 
 
-def fwd_case(name, B, D, h, w, K, precisions=("bf16x3", "bf16")):
+def fwd_case(name, B, D, h, w, K, precisions=("bf16x3", "bf16", "bf16_vol16")):
     f1, f2, coords = inputs(B, D, h, w, K)
     out = {"case": name, "B": B, "grid": [h, w], "iters": K}
 

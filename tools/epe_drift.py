@@ -79,6 +79,7 @@ def main():
         "CorrBlock_fp32": lambda f1, f2: rr.CorrBlock(f1, f2, radius=4, precision="fp32"),
         "CorrBlock_bf16x3": lambda f1, f2: rr.CorrBlock(f1, f2, radius=4, precision="bf16x3"),
         "CorrBlock_bf16": lambda f1, f2: rr.CorrBlock(f1, f2, radius=4, precision="bf16"),
+        "CorrBlock_bf16_vol16": lambda f1, f2: rr.CorrBlock(f1, f2, radius=4, precision="bf16_vol16"),
         "AlternateCorrBlock_fp32": lambda f1, f2: rr.AlternateCorrBlock(f1, f2, radius=4, precision="fp32"),
         "AlternateCorrBlock_bf16x3": lambda f1, f2: rr.AlternateCorrBlock(f1, f2, radius=4, precision="bf16x3"),
         "AlternateCorrBlock_bf16": lambda f1, f2: rr.AlternateCorrBlock(f1, f2, radius=4, precision="bf16"),
