@@ -51,6 +51,8 @@ def parse():
                     help="HBM layout of the pyramid: 'tiled' is what CorrBlock keeps for inference, "
                          "'rows' the reference's (B*h*w,1,h_l,w_l) arrays")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fast-paths", action="store_true",
+                    help="skip the extra bf16 / bf16_vol16 measurements appended to the default bf16x3 line")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
     return ap.parse_args()
@@ -385,6 +387,27 @@ def run_ours(args):
     }
     if e2e is not None:
         line["e2e"] = e2e
+    if world == 1 and tiled and not args.no_fast_paths and args.precision == "bf16x3":
+        # the same step with the stated-bounds fast paths, for the record (not the headline value)
+        extra = {}
+        for prec in ("bf16", "bf16_vol16"):
+            def fstep():
+                lv = build_pyramid_tiled_raw(f1, f2, L, prec)
+                for k in range(K):
+                    lookup_tiled_raw(lv, coords[k], r)
+            for _ in range(3):
+                fstep()
+            torch.cuda.synchronize()
+            a0, a1 = ev(), ev()
+            a0.record()
+            nrep = max(10, min(args.steps, 30))
+            for _ in range(nrep):
+                fstep()
+            a1.record()
+            torch.cuda.synchronize()
+            ms = a0.elapsed_time(a1) / nrep
+            extra[prec] = {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": nrep}
+        line["fast_paths"] = extra
     if world == 1 and not args.no_cpu_baseline:
         try:
             c = cpu_reference_run(args, 2, 1, min(args.cpu_budget_s, 60.0))
