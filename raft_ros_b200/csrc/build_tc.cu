@@ -379,17 +379,32 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 if (nx * 16 + i >= w1 || y1 >= h1) l1[i] = 0.0f;
             }
             if (V16 && j == 1 && y1 - 1 < h1) {
-              // two rows x 16 columns = ONE tile: 64 B per pixel, stored straight from registers
-              // (four 16 B chunks at their swizzled positions; a 2 KB run per warp)
-              if (lane < rows_valid && nx < P.tpr[1]) {
-                float *gt = g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS) + lane * 16;
+              // two rows x 16 columns = ONE tile, 64 B per pixel: a 2 KB bulk copy per warp (per-lane
+              // 16 B stores at the swizzled positions for an incomplete group)
+              if (nx < P.tpr[1]) {
+                float *gt = g1 + (size_t)(y1 >> 1) * (P.tpr[1] * TS);
                 const int sw = tile_sw(lane);
+                float4 c4[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                   const float *src = (k >> 1) ? l1 : l1prev;
                   const int c0 = (k & 1) * 8;
-                  stg128(gt + ((k ^ sw) << 2), make_float4(pack(src[c0], src[c0 + 1]), pack(src[c0 + 2], src[c0 + 3]),
-                                                          pack(src[c0 + 4], src[c0 + 5]), pack(src[c0 + 6], src[c0 + 7])));
+                  c4[k] = make_float4(pack(src[c0], src[c0 + 1]), pack(src[c0 + 2], src[c0 + 3]),
+                                      pack(src[c0 + 4], src[c0 + 5]), pack(src[c0 + 6], src[c0 + 7]));
+                }
+                if (rows_valid >= 32) {
+                  buf_ready();
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) sts128(buf + lane * 64 + ((k ^ sw) << 4), c4[k].x, c4[k].y, c4[k].z, c4[k].w);
+                  fence_proxy_async_smem();
+                  __syncwarp();
+                  if (lane == 0) {
+                    bulk_store(gt, buf, 2048);
+                    bulk_commit();
+                  }
+                } else if (lane < rows_valid) {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) stg128(gt + lane * 16 + ((k ^ sw) << 2), c4[k]);
                 }
               }
             } else if (!V16 && j == 1 && y1 - 1 < h1) {
