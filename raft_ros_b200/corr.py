@@ -176,6 +176,37 @@ def lookup_tiled_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radiu
     return out
 
 
+class _TiledLookup:
+    """The per-iteration call of an inference CorrBlock with everything that does not change between
+    iterations resolved once (level pointer table, entry point, geometry): the host side of a lookup
+    is then one shape check, one allocation and one C call.  At batch 1 the kernel takes ~8 us, so
+    this is what the call costs."""
+
+    def __init__(self, levels, B, h, w, radius):
+        self.levels = levels  # keeps the storage alive
+        self.B, self.h, self.w, self.nl, self.radius = B, h, w, len(levels), radius
+        self.shape = (B, 2, h, w)
+        self.out_shape = (B, len(levels) * (2 * radius + 1) ** 2, h, w)
+        self.device = levels[0].device
+        vol16 = levels[0].dtype == torch.float16
+        lib = _lib.lib()
+        self.fn = lib.rc_corr_lookup_tiled16_fwd if vol16 else lib.rc_corr_lookup_tiled_fwd
+        self.name = "rc_corr_lookup_tiled16_fwd" if vol16 else "rc_corr_lookup_tiled_fwd"
+        self.ptrs = _lib.ptr_array([t.data_ptr() for t in levels])
+
+    def __call__(self, coords):
+        if (coords.dtype is not torch.float32 or coords.device != self.device or not coords.is_contiguous()
+                or coords.requires_grad or tuple(coords.shape) != self.shape
+                or torch.cuda.current_device() != self.device.index):
+            return lookup_tiled_raw(self.levels, coords, self.radius)  # the checked, general path
+        out = torch.empty(self.out_shape, dtype=torch.float32, device=self.device)
+        rc = self.fn(self.ptrs, coords.data_ptr(), out.data_ptr(), self.B, self.h, self.w, self.nl, self.radius,
+                     torch.cuda.current_stream().cuda_stream)
+        if rc:
+            _lib.check(rc, self.name)
+        return out
+
+
 def lookup_raw(levels: Sequence[torch.Tensor], coords: torch.Tensor, radius: int) -> torch.Tensor:
     """rc_corr_lookup_fwd: (B,2,h,w) coords -> (B, L*(2r+1)^2, h, w) fp32, one launch."""
     _require_cuda(coords, "coords")
@@ -416,6 +447,7 @@ class CorrBlock:
         elif tiled:
             self._tiled = build_pyramid_tiled_raw(fmap1, fmap2, num_levels, precision)
             self._geom = (fmap1.shape[0], fmap1.shape[2], fmap1.shape[3])
+            self._fast = _TiledLookup(self._tiled, *self._geom, radius)
         else:
             self._rows = build_pyramid_raw(fmap1, fmap2, num_levels, precision)
 
@@ -445,7 +477,7 @@ class CorrBlock:
                 return lookup_tiled_raw(st.tiled, coords, self.radius)
             return lookup_raw(st.levels, coords, self.radius)
         if self._tiled is not None:
-            return lookup_tiled_raw(self._tiled, coords, self.radius)
+            return self._fast(coords)
         if torch.is_grad_enabled() and any(lv.requires_grad for lv in self._rows):
             # an assigned pyramid that is part of someone else's graph: generic differentiable path
             return _LookupFn.apply(coords, self.radius, *self._rows)

@@ -51,3 +51,19 @@ for name, bf, lf in (("tiled", tiled_from_rows, lookup_tiled_raw), ("rows", buil
     t1 = time.perf_counter()
     torch.cuda.synchronize()
     print(f"{name}: C ABI only: gpu {e0.elapsed_time(e1) / n * 1e3:.1f} us/launch, host issue {(t1 - t0) / n * 1e6:.1f} us/call")
+
+# the public class at batch 1 (the ROS node's case): host cost per lookup call
+f1b, f2b, cb = f1[:1].contiguous(), f2[:1].contiguous(), coords[:1].contiguous()
+with torch.no_grad():
+    blk = rr.CorrBlock(f1b, f2b)
+    for _ in range(10):
+        blk(cb)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(n):
+        blk(cb)
+    e1.record()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+print(f"CorrBlock batch 1: gpu {e0.elapsed_time(e1) / n * 1e3:.1f} us/lookup, host issue {(t1 - t0) / n * 1e6:.1f} us/call")
