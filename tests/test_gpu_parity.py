@@ -692,6 +692,33 @@ def test_vol16_corrblock_and_limits(rr):
     assert torch.isfinite(big(coords)).all()
 
 
+def test_tiled_equals_rows_at_1080p(rr):
+    """A 1080p pair (feature grid 135x240, 32 400 query pixels, 5.6 GB pyramid, odd height): the tiled
+    pipeline and the row-layout pipeline agree -- pyramid bit for bit, lookups to fp32 rounding -- so the
+    64-bit offsets of both layouts hold beyond 2^31 bytes."""
+    from raft_ros_b200.corr import build_pyramid_raw, build_pyramid_tiled_raw, lookup_raw, lookup_tiled_raw, relayout_raw
+    if torch.cuda.mem_get_info()[0] < 40 * 2 ** 30:
+        pytest.skip("needs 40 GB of free device memory")
+    B, D, h, w, L = 1, 256, 135, 240, 4
+    g = torch.Generator().manual_seed(11)
+    f1 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    f2 = torch.randn(B, D, h, w, generator=g).to(DEV)
+    coords = t(make_coords("sigma4", B, h, w, np.random.default_rng(11)))
+    rows = build_pyramid_raw(f1, f2, L, "bf16")
+    tiled = build_pyramid_tiled_raw(f1, f2, L, "bf16")
+    a, b = lookup_tiled_raw(tiled, coords, 4), lookup_raw(rows, coords, 4)
+    assert torch.isfinite(a).all() and relmax(n(a), n(b)) <= 2e-6
+    for l, (hl, wl) in enumerate(O.level_shapes(h, w, L)):
+        back = relayout_raw(tiled[l], B, h * w, hl, wl, to_tiled=False)
+        assert torch.equal(back, rows[l]), l
+        del back
+    # the last query pixels live beyond 2^31 bytes of level 0: spot-check them against a direct product
+    p = h * w - 5
+    want = (f1.view(D, -1)[:, p].double() @ f2.view(D, -1).double() / 16.0).float()
+    got = rows[0][p].view(-1)
+    assert float((got - want).abs().max()) <= 6e-3 * float(want.abs().max())
+
+
 def test_tiled_build_rejects(rr):
     from raft_ros_b200 import _lib
     lib = _lib.lib()
