@@ -122,6 +122,8 @@ def alt_case(H=270, W=480, name="alt_2160x3840"):
     out = {"case": name, "grid": [H, W]}
     ms = timeit(lambda: blk(coords), warm=2, reps=5)
     out["ours_ms_per_iter"] = ms
+    blk16 = rr.AlternateCorrBlock(f1, f2, num_levels=4, radius=4, precision="bf16")
+    out["ours_bf16_ms_per_iter"] = timeit(lambda: blk16(coords), warm=2, reps=5)
     ext = build_ref.load_module()
     if ext is not None:
         f1n = f1.permute(0, 2, 3, 1).contiguous()
