@@ -17,8 +17,11 @@
 //                           issues hi*hi + hi*lo + lo*hi into the same accumulator)
 //                   warps 0-7 epilogue    (warp = TMEM lane quarter x upper/lower half of the patch;
 //                           tcgen05.ld one spatial row pair at a time; thread <-> query pixel so
-//                           all pooling is in registers; rows are transposed through a swizzled
-//                           per-warp smem buffer and written with st.global.v4, 512 B/instruction)
+//                           all pooling is in registers.  Row layout: rows are transposed through a
+//                           swizzled per-warp smem buffer and written with st.global.v4, 512 B per
+//                           instruction.  Tiled layout (what CorrBlock uses): two whole tiles per
+//                           pixel are staged in global order and leave as one 4 KB bulk copy; the
+//                           V16 flavour packs them to fp16 first)
 //                 TMEM holds two 128x256 fp32 accumulators (all 512 columns): the MMAs of tile
 //                 i+1 overlap the epilogue of tile i.
 #include <cuda.h>

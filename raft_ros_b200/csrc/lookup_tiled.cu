@@ -1,14 +1,15 @@
 // Pyramid lookup on the TILED volume layout (r = 4): warp-autonomous, persistent, cp.async-fed.
 //
-// Same result as lookup_fwd_kernel<4> (reference core/corr.py:29-50).  Every row p of a level is
-// stored as tiles of 2 rows x 8 floats (64 B each, the tiles of a tile-row contiguous, the plane
-// padded with zeros to an even height and a width that is a multiple of 8) instead of h_l rows
-// of w_l floats:
-//     level l of row p : [hp/2][wp/8][2][8] floats, hp = ceil2(h>>l), wp = ceil8(w>>l)
-// A 10x10 window then lies in 5-6 x 2-3 tiles, i.e. in a few contiguous 128-192 B runs, instead
-// of ten 40 B segments that each straddle DRAM fill granules, and every row p starts 64 B aligned
-// whatever w is.  The 2x8 shape is what the build epilogue produces for free: a warp's row pair
-// is 4 whole tiles = 256 contiguous bytes per query pixel (build_tc.cu).
+// Same result as lookup_fwd_kernel<4> (reference core/corr.py:29-50) on the TILED layout of
+// include/raftcorr.h: every row p of a level is cut into tiles of 2 rows x 8 floats (64 B, the
+// plane padded with zeros to an even height and a multiple-of-8 width), the tiles of 32 consecutive
+// query pixels are interleaved, and each pixel's four 16 B chunks sit at swizzled positions:
+//     level l : [B][ceil(N/32)][hp/2][wp/8][32 pixels][4 chunks][4 floats]
+// A 10x10 window then lies in 5-6 x 2-3 tiles = whole DRAM granules instead of ten 40 B segments
+// that straddle them, and -- because neighbouring query pixels look at neighbouring places -- the
+// tiles the 8 pixels of a work item need sit next to each other (DRAM reads per launch: 235 MB in
+// the row layout, 132 MB here).  The shape is what the build epilogue produces for free
+// (build_tc.cu).  The V16 flavour reads an fp16 volume (tiles of 2 x 16 halves).
 //
 // Work item = 8 consecutive query pixels of one level, owned by ONE warp (no block-level sync, no
 // shuffles: lane = pixel x quarter in every phase):
