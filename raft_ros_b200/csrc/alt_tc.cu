@@ -10,8 +10,9 @@
 // 128 x (box) x C contraction: the tile of fmap1 (A, 128 rows) against 32x8 chunks of the box
 // (B, 256 rows, a 4-D TMA box straight out of the NHWC feature map, zero-filled outside the map =
 // the reference's zero padding) on tcgen05, fp32 accumulation in TMEM.  The epilogue thread that
-// owns a query pixel picks its (2r+2)^2 patch out of the accumulator rows, forms the (2r+1)^2
-// bilinear taps and writes them in the final (B, L*(2r+1)^2, H, W) layout.  The redundancy (box
+// owns a query pixel picks its (2r+2)^2 patch out of the accumulator rows (tcgen05.ld of a chunk row,
+// then every register goes to its patch slot under a predicate: the column offset is per pixel),
+// forms the (2r+1)^2 bilinear taps and writes them in the final (B, L*(2r+1)^2, H, W) layout.  The redundancy (box
 // vs. window) is 2-5x for coherent flow and still far cheaper than CUDA-core dot products when
 // the flow is incoherent; correctness never depends on coherence (the box just grows).
 //
@@ -41,8 +42,7 @@ constexpr int kStages = 3;
 constexpr int kEpiWarps = 4, kProducerWarp = 4, kMmaWarp = 5, kThreads = 192;
 constexpr int kPatchStride = NPATCH + 1;         // 101: odd -> conflict-free across lanes
 constexpr int kPatchBytes = 128 * kPatchStride * 4;
-constexpr int kRowBufBytes = 128 * 128;          // one 32-float accumulator row per thread
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kPatchBytes + kRowBufBytes + 256;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kPatchBytes + 256;
 constexpr uint32_t kIdescA = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr int kMaxLevels = 4;
 
@@ -123,8 +123,7 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
   uint8_t *smem = smem_raw + (base_u32 - raw_u32);
   const uint32_t patch_u32 = base_u32 + kStages * kStageBytes;
-  const uint32_t rowbuf_u32 = patch_u32 + kPatchBytes;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes + kPatchBytes + kRowBufBytes);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes + kPatchBytes);
   uint64_t *full = bars, *empty = bars + kStages, *tfull = bars + 2 * kStages, *tempty = tfull + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -211,7 +210,6 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
     const int q = warp & 3;
     const int m = q * 32 + lane;
     const uint32_t patch = patch_u32 + (uint32_t)m * (kPatchStride * 4);
-    const uint32_t rowbuf = rowbuf_u32 + (uint32_t)m * 128;
     int acc = 0;
     uint32_t acc_phase = 0;
     const size_t HW = (size_t)P.H1 * P.W1;
@@ -249,14 +247,14 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
                 tmem_ld32(taddr + rr * CW, v);
                 tmem_ld_wait();
                 if (need) {
+                  // window column px of this pixel is accumulator column cbase + px: every register goes
+                  // straight to its patch slot under a predicate (no bounce through a row buffer; the
+                  // epilogue has issue slots to spare, shared-memory round trips it has not)
+                  const int cbase = x0 - ox;
+                  const uint32_t prow = patch + (uint32_t)((py * PN - cbase) * 4);
 #pragma unroll
-                  for (int c = 0; c < 8; ++c) sts128(rowbuf + c * 16, v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
-                  const int cbase = x0 - ox;  // accumulator column of window column 0
-#pragma unroll
-                  for (int px = 0; px < PN; ++px) {
-                    const int col = cbase + px;
-                    if ((unsigned)col < (unsigned)CW) sts32(patch + (py * PN + px) * 4, lds32(rowbuf + col * 4));
-                  }
+                  for (int c = 0; c < CW; ++c)
+                    if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[c]);
                 }
               }
             }
