@@ -143,7 +143,7 @@ int rc_corr_lookup_fwd(const float *const *level_ptrs, const float *coords, floa
  *                     RC_PREC_BF16 (/ RC_PREC_BF16_VOL16, below) only, num_levels <= 4, level pointers 64-byte aligned and
  *                     rc_corr_tiled_level_elems floats each.  Same workspace as the row-layout build.
  * rc_corr_lookup_tiled_fwd    : rc_corr_lookup_fwd reading it.  Same coords / out contract;
- *                     radius 4 only.
+ *                     radius 3 (raft-small) or 4 (raft-things).
  * rc_corr_relayout_level      : converts one level (hl x wl per row, N = h*w query pixels per batch
  *                     item) between the layouts (to_tiled != 0: rows -> tiled, padding zeroed;
  *                     0: tiled -> rows).

@@ -297,7 +297,7 @@ def _alloc_levels(shapes, device):
 
 
 def _use_tiled(num_levels, radius, precision) -> bool:
-    return (radius == 4 and 1 <= num_levels <= 4 and _precision_code(precision) != _lib.RC_PREC_FP32
+    return (radius in (3, 4) and 1 <= num_levels <= 4 and _precision_code(precision) != _lib.RC_PREC_FP32
             and os.environ.get("RAFT_CORR_LAYOUT", "tiled") != "rows")
 
 
@@ -417,7 +417,7 @@ class CorrBlock:
     pooling level fused, each level written once).  `precision` is an extension: see
     DEFAULT_PRECISION.
 
-    Inference (no gradient wanted, radius 4, <= 4 levels, a tensor-core precision) keeps the
+    With radius 3 or 4, <= 4 levels and a tensor-core precision the block keeps the
     pyramid in the TILED layout (include/raftcorr.h) that the lookup kernel reads with 35 % less
     DRAM traffic; `corr_pyramid` then converts to the reference's row layout on first access (a
     copy: writing into it does not change what the lookups read -- assign `corr_pyramid` to
@@ -437,7 +437,7 @@ class CorrBlock:
         if _precision_code(precision) == _lib.RC_PREC_BF16_VOL16:
             # the fp16 volume exists only where the fused tiled kernels do
             if not tiled or (torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)):
-                raise RuntimeError("precision 'bf16_vol16' is an inference mode for radius 4 and at most 4 levels "
+                raise RuntimeError("precision 'bf16_vol16' is an inference mode for radius 3 or 4 and at most 4 levels "
                                    "(tiled layout); use 'bf16' or 'bf16x3' here")
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
             self._state = _GradState()

@@ -74,11 +74,13 @@ struct TlCtx {
 // V16: the volume is fp16, tiles of 2 rows x 16 halves (same 64 B, same 4 chunks of 16 B = 8 halves):
 // a window row is 2-3 pieces of 8 halves from a multiple-of-8 column, kept as halves in shared memory
 // (48 B per row) and converted when the taps read them; interpolation and output stay fp32.
-template <bool V16>
+// RR = window radius: 4 (raft-things) or 3 (raft-small, the ROS node's `is_small`).
+template <bool V16, int RR>
 __global__ void __launch_bounds__(kTlThreads)
 lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, float *__restrict__ out, int B, int h, int w,
                         int L, int groups_per_item, int total_items) {
-  constexpr int R = 4, RD = 9, NTAP = 81, PS = kTlPS;
+  constexpr int R = RR, RD = 2 * R + 1, PN = RD + 1, NTAP = RD * RD, PS = kTlPS;
+  static_assert(R == 3 || R == 4, "tap assignment below is written for radius 3 and 4");
   extern __shared__ __align__(16) float smem[];
   const int N = h * w;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -140,9 +142,9 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
       const int hp = (hl + 1) & ~1, wp = (wl + CW - 1) & ~(CW - 1), tpr = wp / CW;  // tiles per tile-row
       const int wb = (wl + PC - 1) & ~(PC - 1);
       const int cg = (c.x0 & ~(PC - 1)) + PC * tc;
-      // pieces a window of 10 columns needs from a multiple-of-PC start: 3, or 4 at offset 3 (fp32);
-      // 2, or 3 at offset 7 (fp16)
-      const bool want = V16 ? (tc < 2 || (tc == 2 && (c.x0 & 7) == 7)) : (tc < 3 || (c.x0 & 3) == 3);
+      // pieces a window of PN columns needs from a multiple-of-PC start (r = 4: 3, or 4 at offset 3 in
+      // fp32; 2, or 3 at offset 7 in fp16)
+      const bool want = PC * tc < (c.x0 & (PC - 1)) + PN;  // piece k holds window columns iff PC*k < offset + PN
       const bool okx = want && (unsigned)cg < (unsigned)wb;
       // group of G = 32 query pixels: [tile][pixel u][4 chunks], chunk k = 2*(row & 1) + (column half) stored
       // at position k ^ ((u >> 1) & 3) (the build's bank-conflict-free staging order, build_tc.cu).
@@ -158,7 +160,7 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
       constexpr unsigned RB = V16 ? 48u : (unsigned)PS * 4u;  // bytes per patch row in shared memory
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
-      for (int r = 0; r < 10; ++r) {
+      for (int r = 0; r < PN; ++r) {
         const int ya = c.y0 + r;
         const bool ok = okx && (unsigned)ya < (unsigned)hl;
         const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
@@ -200,11 +202,11 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
     const int p = cur.p0 + tu;
     float *o = out + ((size_t)cur.b * CH + (size_t)cur.lvl * NTAP) * N + p;
     const bool pv = p < N;
-    {
-      // columns 2tc, 2tc+1: horizontal interpolation of the 10 rows, then vertical pairs
-      float h0[10], h1[10];
+    if (tc < RD / 2) {
+      // columns 2tc, 2tc+1: horizontal interpolation of the PN rows, then vertical pairs
+      float h0[PN], h1[PN];
 #pragma unroll
-      for (int j = 0; j < 10; ++j) {
+      for (int j = 0; j < PN; ++j) {
         const float a = at(j, 2 * tc), b = at(j, 2 * tc + 1), d = at(j, 2 * tc + 2);
         h0[j] = fmaf(b, dx, a * ex);
         h1[j] = fmaf(d, dx, b * ex);
@@ -218,7 +220,7 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
         }
       }
     }
-    {
+    if constexpr (R == 4) {
       // column 8, rows shared out over the 4 lanes of the pixel: lane tc takes j = tc, tc+4 (and 8 for tc = 0)
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
@@ -228,6 +230,15 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
           const float top = fmaf(b, dx, a * ex), bot = fmaf(d2, dx, c2 * ex);
           if (pv) RC_TL_ST(o + (size_t)(8 * RD + j) * N, fmaf(bot, dy, top * ey));
         }
+      }
+    } else if (tc == RD / 2) {
+      // r = 3: three lanes own the column pairs 0-5, the fourth the last column (6) on its own
+      float hc[PN];
+#pragma unroll
+      for (int j = 0; j < PN; ++j) hc[j] = fmaf(at(j, RD), dx, at(j, RD - 1) * ex);
+      if (pv) {
+#pragma unroll
+        for (int j = 0; j < RD; ++j) RC_TL_ST(o + (size_t)((RD - 1) * RD + j) * N, fmaf(hc[j + 1], dy, hc[j] * ey));
       }
     }
     __syncwarp();
@@ -239,13 +250,9 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   cp_async_wait<0>();
 }
 
-template <bool V16>
-static int launch_tiled(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
-                        cudaStream_t st, const char *fn) {
-  if (r != 4) {
-    set_error("%s: radius %d unsupported on the tiled layout (4 only)", fn, r);
-    return RC_ERR_UNSUPPORTED;
-  }
+template <bool V16, int RR>
+static int launch_tiled_r(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L,
+                          cudaStream_t st, const char *fn) {
   const int N = h * w;
   const int groups = (N + kTlPix - 1) / kTlPix;
   const long long total = (long long)L * B * groups;
@@ -255,15 +262,15 @@ static int launch_tiled(const ConstLevelPtrs &lv, const float *coords, float *ou
   }
   const size_t smem = sizeof(float) * (size_t)(kTlWarps * kTlStages * kTlStageFloats);
   // resident CTAs per device: asked once per device (this runs every RAFT iteration)
-  static int resident[64] = {};
+  static int resident[64] = {};  // (one table per instantiation)
   int dev = 0;
   RC_CUDA(cudaGetDevice(&dev));
   int cached = (dev >= 0 && dev < 64) ? __atomic_load_n(&resident[dev], __ATOMIC_ACQUIRE) : 0;
   if (cached == 0) {
     int sms = 0, ctas_per_sm = 0;
-    RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel<V16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RC_CUDA(cudaFuncSetAttribute(lookup_tiled_fwd_kernel<V16, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel<V16>, kTlThreads, smem));
+    RC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, lookup_tiled_fwd_kernel<V16, RR>, kTlThreads, smem));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     cached = sms * ctas_per_sm;
     if (dev >= 0 && dev < 64) __atomic_store_n(&resident[dev], cached, __ATOMIC_RELEASE);
@@ -271,9 +278,18 @@ static int launch_tiled(const ConstLevelPtrs &lv, const float *coords, float *ou
   long long grid = cached;
   const long long need = (total + kTlWarps - 1) / kTlWarps;
   if (grid > need) grid = need;
-  lookup_tiled_fwd_kernel<V16><<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);
+  lookup_tiled_fwd_kernel<V16, RR><<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
+}
+
+template <bool V16>
+static int launch_tiled(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,
+                        cudaStream_t st, const char *fn) {
+  if (r == 4) return launch_tiled_r<V16, 4>(lv, coords, out, B, h, w, L, st, fn);
+  if (r == 3) return launch_tiled_r<V16, 3>(lv, coords, out, B, h, w, L, st, fn);
+  set_error("%s: radius %d unsupported on the tiled layout (3 and 4 only)", fn, r);
+  return RC_ERR_UNSUPPORTED;
 }
 
 int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h, int w, int L, int r,

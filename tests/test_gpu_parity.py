@@ -155,7 +155,7 @@ def _fuzz_geometries(count=12, seed=20261106):
         h, w = int(rng.integers(8, 31)), int(rng.integers(8, 51))
         if (h >> (L - 1)) < 1 or (w >> (L - 1)) < 1:
             continue
-        out.append((int(rng.integers(1, 4)), int(rng.integers(8, 301)), h, w, L))
+        out.append((int(rng.integers(1, 4)), int(rng.integers(8, 301)), h, w, L, 4 if len(out) % 3 else 3))
     return out
 
 
@@ -164,14 +164,14 @@ def test_corrblock_random_geometries(rr, geom):
     """CorrBlock as a user gets it (default precision, tiled pyramid, one build + one lookup) on random
     small geometries -- odd sizes, channel counts that are not multiples of 64, 1 to 4 levels -- against
     the oracle end to end."""
-    B, D, h, w, L = geom
+    B, D, h, w, L, radius = geom
     rng = np.random.default_rng(seed_of(geom))
     f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
     f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
     coords = make_coords("sigma4", B, h, w, rng)
     want_pyr = O.corr_build(f1, f2, L)
-    want = O.corr_lookup(want_pyr, coords, 4)
-    blk = rr.CorrBlock(t(f1), t(f2), num_levels=L, radius=4)
+    want = O.corr_lookup(want_pyr, coords, radius)
+    blk = rr.CorrBlock(t(f1), t(f2), num_levels=L, radius=radius)
     assert blk._tiled is not None
     got = n(blk(t(coords)))
     assert got.shape == want.shape and np.isfinite(got).all()
@@ -681,7 +681,7 @@ def test_vol16_corrblock_and_limits(rr):
     assert relmax(n(blk(coords)), n(ref(coords))) <= 1e-3
     assert blk.corr_pyramid[0].dtype == torch.float32 and blk.corr_pyramid[0].shape == ref.corr_pyramid[0].shape
     with pytest.raises(RuntimeError, match="bf16_vol16"):
-        rr.CorrBlock(f1, f2, radius=3, precision="bf16_vol16")
+        rr.CorrBlock(f1, f2, radius=2, precision="bf16_vol16")
     with pytest.raises(RuntimeError, match="bf16_vol16"):
         rr.CorrBlock(f1.clone().requires_grad_(True), f2, precision="bf16_vol16")
     with pytest.raises(ValueError, match="bf16_vol16"):
@@ -760,9 +760,10 @@ def test_corrblock_layouts_agree(rr, monkeypatch):
     assert float(blk(coords).abs().max()) == 0.0
 
 
+@pytest.mark.parametrize("radius", [4, 3])
 @pytest.mark.parametrize("kind", ["grid", "sigma4", "sigma32", "oob", "border", "huge"])
 @pytest.mark.parametrize("geom", [(2, 27, 40, 4), (1, 23, 39, 3), (1, 55, 128, 4), (3, 16, 16, 4)])
-def test_lookup_on_tiled_layout(rr, geom, kind):
+def test_lookup_on_tiled_layout(rr, geom, kind, radius):
     """rc_corr_lookup_tiled_fwd (2x8-tiled volume rows, cp.async-fed persistent kernel) gives the
     row-layout lookup's result on every geometry, including widths / heights that need padding."""
     from raft_ros_b200 import _lib
@@ -771,16 +772,23 @@ def test_lookup_on_tiled_layout(rr, geom, kind):
     rng = np.random.default_rng(seed_of(geom, kind))
     levels = [t(rng.standard_normal((B * h * w, 1, hl, wl)).astype(np.float32)) for hl, wl in O.level_shapes(h, w, L)]
     coords = t(make_coords(kind, B, h, w, rng))
-    want = lookup_raw(levels, coords, 4)
+    want = lookup_raw(levels, coords, radius)
     tiles = _tile_levels(levels, B)
-    out = torch.full((B, L * 81, h, w), float("nan"), device=DEV)
+    out = torch.full((B, L * (2 * radius + 1) ** 2, h, w), float("nan"), device=DEV)
     lib = _lib.lib()
     rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),
-                                      B, h, w, L, 4, torch.cuda.current_stream().cuda_stream)
+                                      B, h, w, L, radius, torch.cuda.current_stream().cuda_stream)
     assert rc == 0, lib.rc_last_error()
     torch.cuda.synchronize()
     assert torch.isfinite(out).all()
-    assert relmax(n(out), n(want)) <= 2e-6, (geom, kind, relmax(n(out), n(want)))
+    assert relmax(n(out), n(want)) <= 2e-6, (geom, kind, radius, relmax(n(out), n(want)))
+    # the fp16 flavour on the same (rounded) values
+    from raft_ros_b200.corr import relayout_raw, lookup_tiled_raw
+    shapes = O.level_shapes(h, w, L)
+    t16 = [relayout_raw(lv, B, h * w, hl, wl, to_tiled=True, vol16=True) for lv, (hl, wl) in zip(levels, shapes)]
+    got16 = lookup_tiled_raw(t16, coords, radius)
+    want16 = lookup_raw([lv.half().float() for lv in levels], coords, radius)
+    assert relmax(n(got16), n(want16)) <= 2e-6, (geom, kind, radius, "fp16 volume")
     rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),
-                                      B, h, w, L, 3, torch.cuda.current_stream().cuda_stream)
+                                      B, h, w, L, 5, torch.cuda.current_stream().cuda_stream)
     assert rc == 3 and b"radius" in lib.rc_last_error()
