@@ -235,7 +235,7 @@ def run_ours(args):
     from raft_ros_b200 import _lib
     from raft_ros_b200.corr import build_pyramid_raw, build_pyramid_tiled_raw, lookup_raw, lookup_tiled_raw
 
-    tiled = args.layout == "tiled" and args.precision != "fp32" and args.radius == 4 and args.levels <= 4
+    tiled = args.layout == "tiled" and args.precision != "fp32" and args.radius in (3, 4) and args.levels <= 4
     os.environ["RAFT_CORR_LAYOUT"] = "tiled" if tiled else "rows"  # the e2e arm's CorrBlock follows
     build_fn = build_pyramid_tiled_raw if tiled else build_pyramid_raw
     look_fn = lookup_tiled_raw if tiled else lookup_raw
