@@ -91,11 +91,21 @@ def build_pyramid_raw(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int,
     return levels
 
 
+_TILE_GROUP = None
+
+
+def _tile_group() -> int:
+    global _TILE_GROUP
+    if _TILE_GROUP is None:
+        _TILE_GROUP = int(_lib.lib().rc_corr_tile_group())
+    return _TILE_GROUP
+
+
 def tiled_level_elems(B: int, N: int, hl: int, wl: int, vol16: bool = False) -> int:
     """elements of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems /
     rc_corr_tiled16_level_elems): [B][ceil(N/G)][hp/2][wp/cw][G][2][cw], G = rc_corr_tile_group(),
     cw = 8 floats or 16 halves."""
-    G = int(_lib.lib().rc_corr_tile_group())
+    G = _tile_group()
     cw = 16 if vol16 else 8
     return B * ((N + G - 1) // G) * G * ((hl + 1) & ~1) * ((wl + cw - 1) & ~(cw - 1))
 
