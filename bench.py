@@ -153,11 +153,11 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- CPU (reference) arm
 def cpu_reference_run(args, steps, warmup, budget_s):
-    """The reference's CPU CorrBlock path (torch CPU kernels: MKL sgemm, avg_pool2d,
-    grid_sample), via oracle/torch_port.py (op-for-op port; the reference checkout itself is not
-    on the GPU box).  One step = ONE frame pair of the workload: build + K lookups."""
+    """The reference's CPU CorrBlock path on the box's host cores.  When the reference's own `core/`
+    package was ferried to this machine (oracle/_ref/core/, oracle/build_ref_core.py) the timed code IS the
+    reference's unmodified `core/corr.py::CorrBlock` (kind "reference"); otherwise the op-for-op port
+    oracle/torch_port.py (kind "port").  One step = ONE frame pair of the workload: build + K lookups."""
     import torch
-    from oracle import torch_port as TP
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
@@ -169,12 +169,32 @@ def cpu_reference_run(args, steps, warmup, budget_s):
     base = torch.stack([xs, ys], 0)[None]
     flows = torch.cumsum(0.5 * torch.randn(args.iters, 1, 2, h, w, generator=g), 0)
 
-    def step():
-        pyr = TP.build_pyramid(f1, f2, args.levels)
-        s = 0.0
-        for k in range(args.iters):
-            s += float(TP.lookup(pyr, base + flows[k], args.radius)[0, 0, 0, 0])
-        return s
+    ref_core = None
+    try:
+        from oracle import build_ref_core
+        ref_core = build_ref_core.load()
+    except Exception as e:
+        log(f"[bench] reference core/ package unavailable ({e}); timing the port")
+    if ref_core is not None:
+        kind = "reference"
+        RefCorrBlock = ref_core.corr.CorrBlock
+
+        def step():
+            blk = RefCorrBlock(f1, f2, num_levels=args.levels, radius=args.radius)
+            s = 0.0
+            for k in range(args.iters):
+                s += float(blk(base + flows[k])[0, 0, 0, 0])
+            return s
+    else:
+        kind = "port"
+        from oracle import torch_port as TP
+
+        def step():
+            pyr = TP.build_pyramid(f1, f2, args.levels)
+            s = 0.0
+            for k in range(args.iters):
+                s += float(TP.lookup(pyr, base + flows[k], args.radius)[0, 0, 0, 0])
+            return s
 
     t_start = time.perf_counter()
     with torch.no_grad():
@@ -191,8 +211,9 @@ def cpu_reference_run(args, steps, warmup, budget_s):
                 break
     mean = sum(times) / len(times)
     return {"pairs_per_s": 1.0 / mean, "ms_per_step": mean * 1e3, "steps_timed": len(times), "cores": cores,
-            "threads": torch.get_num_threads(),
-            "sample": f"1 frame pair per step (of the {args.batch}-pair batch): build + {args.iters} lookups, fp32, "
+            "threads": torch.get_num_threads(), "kind": kind,
+            "sample": f"{'core/corr.py CorrBlock (unmodified, oracle/_ref/core)' if kind == 'reference' else 'oracle/torch_port.py'}: "
+                      f"1 frame pair per step (of the {args.batch}-pair batch): build + {args.iters} lookups, fp32, "
                       f"{len(times)} timed steps, mean"}
 
 
@@ -205,15 +226,15 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": r["pairs_per_s"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "steps_timed": r["steps_timed"], "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, "cpu"),
-        "cpu_baseline": {"value": r["pairs_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "config": workload_config(args), "where": "cpu",
+        "cpu_baseline": {"value": r["pairs_per_s"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
         "e2e": {"value": r["pairs_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, where):
+def workload_config(args):
     h, w = args.height // 8, args.width // 8
     return {
         "workload": f"sintel 436x1024 padded to {args.height}x{args.width}: feature grid {h}x{w}, D={args.dim}, "
@@ -222,7 +243,6 @@ def workload_config(args, where):
         "batch_per_gpu": args.batch, "iters": args.iters, "levels": args.levels, "radius": args.radius,
         "feature_grid": [h, w], "dim": args.dim,
         "l2": "pyramid per step (2.09 GB fp32 at batch 8) far exceeds the 126 MB L2; no explicit flush",
-        "where": where,
     }
 
 
@@ -406,7 +426,7 @@ def run_ours(args):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (hi/lo split, f32 accumulate) + f32 lookup", "bf16": "bf16 (f32 accumulate) + f32 lookup",
                   "bf16_vol16": "bf16 (f32 accumulate), fp16 volume + f32 lookup"}[args.precision],
-        "data": "synthetic", "config": workload_config(args, "gpu"), "precision": args.precision,
+        "data": "synthetic", "config": workload_config(args), "where": "gpu", "precision": args.precision,
         "roofline": roofline, "kernels": kern, "clocks": clocks, "gpu_launches": int(args.steps * (2 + K)),
         "l2_fetch_granularity": l2_fetch, "layout": "tiled" if tiled else "rows",
     }
@@ -436,7 +456,7 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         try:
             c = cpu_reference_run(args, 2, 1, min(args.cpu_budget_s, 60.0))
-            line["cpu_baseline"] = {"value": c["pairs_per_s"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"]}
+            line["cpu_baseline"] = {"value": c["pairs_per_s"], "unit": UNIT, "cores": c["cores"], "kind": c["kind"], "sample": c["sample"]}
         except Exception as e:
             log(f"[bench] cpu baseline failed: {e}")
     print(json.dumps(line), flush=True)

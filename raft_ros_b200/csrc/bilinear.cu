@@ -2,7 +2,10 @@
 // (core/utils/utils.py:57-71 = F.grid_sample(img, grid, align_corners=True), bilinear,
 // zeros padding) without the normalise / un-normalise round trip.
 //   img (M, C, H, W), coords (M, Ho, Wo, 2) [x, y] in pixels -> out (M, C, Ho, Wo)
-//   optional mask (M, Ho, Wo, 1): 1 where 0 < x < W-1 and 0 < y < H-1 (utils.py:67-69)
+//   optional mask (M, Ho, Wo, 1): the reference's rule, evaluated as the reference evaluates it
+//   (utils.py:61-62,67-69): xg = 2*x/(W-1) - 1 in fp32 (one rounding per operation, IEEE division),
+//   mask = -1 < xg < 1 and -1 < yg < 1.  It differs from "0 < x < W-1" only within an ulp of the two
+//   borders, where the normalised coordinate rounds onto +-1.
 #include "common.cuh"
 
 namespace rc {
@@ -21,7 +24,11 @@ __global__ void bilinear_fwd_kernel(const float *__restrict__ img, const float *
     const bool ya = y0 >= 0 && y0 < H, yb = y0 + 1 >= 0 && y0 + 1 < H;
     const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx;
     const float w10 = dy * (1.0f - dx), w11 = dy * dx;
-    if (mask) mask[s] = (c.x > 0.0f && c.y > 0.0f && c.x < (float)(W - 1) && c.y < (float)(H - 1)) ? 1.0f : 0.0f;
+    if (mask) {
+      const float xg = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, c.x), (float)(W - 1)), 1.0f);
+      const float yg = __fsub_rn(__fdiv_rn(__fmul_rn(2.0f, c.y), (float)(H - 1)), 1.0f);
+      mask[s] = (xg > -1.0f && yg > -1.0f && xg < 1.0f && yg < 1.0f) ? 1.0f : 0.0f;
+    }
     for (int ch = 0; ch < C; ++ch) {
       const float *im = img + ((size_t)m * C + ch) * ((size_t)H * W);
       float v = 0.0f;
