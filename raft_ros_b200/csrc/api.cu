@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -20,6 +21,14 @@ void set_error(const char *fmt, ...) {
 int cuda_fail(cudaError_t e, const char *what) {
   set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
   return RC_ERR_CUDA;
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("RAFT_CORR_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
 }
 
 static int check_geometry(const char *fn, int B, int h, int w, int L) {

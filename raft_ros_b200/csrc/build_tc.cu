@@ -118,6 +118,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();  // persistent and wholly resident: the next kernel's CTAs follow ours as they leave
 
   if (warp == kProducerWarp && lane == 0) {
     for (int s = 0; s < C::kStages; ++s) {
@@ -154,6 +155,10 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      // Everything above (barriers, TMEM, tensor-map prefetch) ran while the layout prepass was still
+      // draining; its output is read from here on.  The MMA and epilogue roles only ever act on what
+      // this thread has loaded, so they are ordered behind this wait as well.
+      pdl_wait();
       for (long long t = unit0; t < P.total_tiles; t += unit_step) {
         const int b = (int)(t / tiles_per_item);
         const int rem = (int)(t - (long long)b * tiles_per_item);
@@ -546,6 +551,8 @@ prep_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __nv_bfl
   __nv_bfloat16 *lo = (which ? b_lo : a_lo) + (size_t)b * N * Dp;
   const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  pdl_launch_dependents();
+  pdl_wait();
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int d = d0 + ty + 8 * i, p = p0 + tx;
@@ -623,13 +630,15 @@ static int launch(const CUtensorMap &ah, const CUtensorMap &al, const CUtensorMa
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = NCTA;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // set up while the prepass drains
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   RC_CUDA(cudaLaunchKernelEx(&cfg, kern, ah, al, bh, bl, P));
   RC_CUDA(cudaGetLastError());
   return RC_OK;
@@ -685,8 +694,7 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
 
   {
     dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
-    prep_kernel<<<grid, 256, 0, st>>>(f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0);
-    RC_CUDA(cudaGetLastError());
+    RC_CUDA(launch_pdl(prep_kernel, grid, dim3(256), 0, st, f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0));
   }
 
   CUtensorMap tmAh, tmAl, tmBh, tmBl;

@@ -26,6 +26,29 @@ int cuda_fail(cudaError_t e, const char *what);
     if (e__ != cudaSuccess) return rc::cuda_fail(e__, #call); \
   } while (0)
 
+// Programmatic dependent launch between this library's back-to-back kernels (on unless
+// RAFT_CORR_PDL=0; read once per process)
+bool pdl_enabled();
+
+#ifdef __CUDACC__
+// <<<grid, block, smem, st>>> with cudaLaunchAttributeProgrammaticStreamSerialization: the kernel may
+// be set up while its predecessor in the stream drains; it calls pdl_wait() before touching memory.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 struct LevelPtrs {
   float *p[RC_MAX_LEVELS];
 };
@@ -109,6 +132,15 @@ __device__ __forceinline__ int safe_floor_int(float v, float *frac) {
   // fmaxf/fminf drop a NaN operand; everything beyond +-2^24 is outside any feature grid anyway
   return __float2int_rz(fminf(fmaxf(f, -16777216.0f), 16777216.0f));
 }
+
+// Programmatic dependent launch (no-ops in a kernel launched without the attribute).
+//   pdl_launch_dependents: the next kernel of the stream may be set up as soon as every CTA of this
+//     grid has got here (its CTAs still only become resident as ours leave).
+//   pdl_wait: returns once every earlier kernel of the stream has completed and its writes are visible.
+//     Nothing that an earlier kernel may have produced is read, and no global memory is written,
+//     before it.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ float ld_stream(const float *p) {
   float v;

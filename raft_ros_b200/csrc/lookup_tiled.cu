@@ -95,6 +95,13 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
   int dl = it0 / per_level, db = (it0 - dl * per_level) / groups_per_item, dg = it0 - dl * per_level - db * groups_per_item;
   const int s_l = stride / per_level, s_b = (stride - s_l * per_level) / groups_per_item,
             s_g = stride - s_l * per_level - s_b * groups_per_item;
+  // Programmatic dependent launch (the launcher sets cudaLaunchAttributeProgrammaticStreamSerialization):
+  // this grid is persistent and wholly resident, so the next kernel in the stream may be set up at once
+  // -- its CTAs take the places of ours as they exit -- while everything above ran before the previous
+  // kernel in the stream had finished.  Nothing produced by earlier kernels (coordinates, volume) is
+  // read, and nothing is written, before the wait.
+  pdl_launch_dependents();
+  pdl_wait();
   auto next_raw = [&]() {
     TlRaw r{dl, db, dg * kTlPix, dl < L ? 1 : 0, 0.f, 0.f};
     if (r.valid) {
@@ -278,8 +285,8 @@ static int launch_tiled_r(const ConstLevelPtrs &lv, const float *coords, float *
   long long grid = cached;
   const long long need = (total + kTlWarps - 1) / kTlWarps;
   if (grid > need) grid = need;
-  lookup_tiled_fwd_kernel<V16, RR><<<(unsigned)grid, kTlThreads, smem, st>>>(lv, coords, out, B, h, w, L, groups, (int)total);
-  RC_CUDA(cudaGetLastError());
+  RC_CUDA(launch_pdl(lookup_tiled_fwd_kernel<V16, RR>, dim3((unsigned)grid), dim3(kTlThreads), smem, st, lv, coords, out, B, h,
+                     w, L, groups, (int)total));
   return RC_OK;
 }
 

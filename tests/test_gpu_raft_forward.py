@@ -86,6 +86,19 @@ def test_reference_forward_through_dropins(ref_core, monkeypatch, small, alterna
     assert torch.isfinite(flow_our).all()
     epe = float((flow_our - flow_ref).norm(dim=1).mean())
     mag = float(flow_ref.norm(dim=1).mean())
-    print(f"[raft.forward small={small} alternate={alternate}] mean |flow| {mag:.3f} px, EPE vs reference {epe:.5f} px, "
-          f"reference run-to-run {noise:.5f} px")
+
+    # sensitivity: the same forward with the correlation features off by 1 % must move the flow by far more
+    # than the bound, otherwise the bound would say nothing about the operator
+    class Off(rr.CorrBlock):
+        def __call__(self, coords):
+            return super().__call__(coords) * 1.01
+
+    monkeypatch.setattr(core.raft, "CorrBlock", Off)
+    monkeypatch.setattr(core.raft, "AlternateCorrBlock", Off)
+    with torch.no_grad():
+        flow_off, _ = model(im1, im2, iters=12, test_mode=True)
+    sens = float((flow_off - flow_ref).norm(dim=1).mean())
+    print(f"[raft.forward small={small} alternate={alternate}] mean |flow| {mag:.3f} px, EPE vs reference {epe:.3e} px, "
+          f"reference run-to-run {noise:.3e} px, EPE with corr features off by 1 % {sens:.3e} px")
     assert epe <= EPE_BOUND["bf16x3"], (epe, noise, mag)
+    assert sens > 10 * max(epe, 1e-7), (sens, epe)
