@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--no-fast-paths", action="store_true",
                     help="skip the extra bf16 / bf16_vol16 measurements appended to the default bf16x3 line")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true",
+                    help="skip the comparator leg: the reference's own torch ops / alt_cuda_corr binary on this GPU")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0)
     return ap.parse_args()
 
@@ -69,17 +71,24 @@ def algorithmic_bytes(B, N, D, h, w, L, r, K, s_vol=4):
 
 
 def measured_traffic(kernel, args, layout="rows"):
-    """dram__bytes_read + dram__bytes_write per launch of `kernel` from the committed ncu capture
-    (profiles/traffic.json); only valid for the configuration it was captured on."""
-    p = os.path.join(ROOT, "profiles", "traffic.json")
+    """Per-launch memory traffic of `kernel` from this round's committed `ncu --set full` capture
+    (profiles/r02_traffic.json, written by tools/ncu_traffic.py from the .ncu-rep; it records the commit
+    it was captured at).  Only valid for the configuration it was captured on, else None.
+    Returns (dram_read + dram_write, detail dict)."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
     default = (args.batch, args.height, args.width, args.dim, args.levels, args.radius, args.precision)
-    if default != (8, 440, 1024, 256, 4, 4, "bf16x3") or not os.path.exists(p):
-        return None
+    if default != (8, 440, 1024, 256, 4, 4, "bf16x3") or layout != "tiled" or not os.path.exists(p):
+        return None, None
     try:
         d = json.load(open(p))
-        return float(d[layout][kernel]) if layout in d else (float(d[kernel]) if layout == "rows" else None)
+        k = d["kernels"][kernel]
+        detail = {"dram_read": k["dram_read"], "dram_write": k["dram_write"], "sm_write": k["sm_write"],
+                  "sm_read": k.get("sm_read"), "kernel_us_under_ncu": k.get("us"), "commit": d.get("commit"),
+                  "note": "dram_write counts only what reached DRAM before the kernel ended; sm_write is what the SMs "
+                          "stored (l1tex__m_l1tex2xbar_write_bytes): in the bench loop the rest drains during the next launch"}
+        return float(k["dram_read"]) + float(k["dram_write"]), detail
     except Exception:
-        return None
+        return None, None
 
 
 def peaks():
@@ -215,6 +224,97 @@ def cpu_reference_run(args, steps, warmup, budget_s):
             "sample": f"{'core/corr.py CorrBlock (unmodified, oracle/_ref/core)' if kind == 'reference' else 'oracle/torch_port.py'}: "
                       f"1 frame pair per step (of the {args.batch}-pair batch): build + {args.iters} lookups, fp32, "
                       f"{len(times)} timed steps, mean"}
+
+
+def gpu_reference_run(args, f1, f2, coords, our_value):
+    """Comparator leg, outside every timed region of this repository's own numbers: the reference's own code
+    on the SAME GPU.  (1) Its torch-op CorrBlock (core/corr.py unmodified from oracle/_ref/core when ferried,
+    else the op-for-op port), same batch, fp32 with TF32 off: build + K lookups.  (2) Its compiled
+    alt_cuda_corr binary (oracle/_ref) against AlternateCorrBlock at config 5 (2160x3840 -> 270x480), one
+    iteration = 4 levels."""
+    import torch
+
+    import raft_ros_b200 as rr
+
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    K, L, r = args.iters, args.levels, args.radius
+    B = f1.shape[0]
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+
+    def timeit(fn, warm, reps):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    out = {}
+    ref_core = None
+    try:
+        from oracle import build_ref_core
+        ref_core = build_ref_core.load()
+    except Exception:
+        pass
+    if ref_core is not None:
+        RefCorrBlock = ref_core.corr.CorrBlock
+        kind = "reference (core/corr.py unmodified, torch ops on this GPU)"
+
+        def ref_step():
+            blk = RefCorrBlock(f1, f2, num_levels=L, radius=r)
+            for k in range(K):
+                blk(coords[k])
+    else:
+        from oracle import torch_port as TP
+        kind = "port (oracle/torch_port.py, torch ops on this GPU)"
+
+        def ref_step():
+            pyr = TP.build_pyramid(f1, f2, L)
+            for k in range(K):
+                TP.lookup(pyr, coords[k], r)
+
+    import warnings
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        ms = timeit(ref_step, 2, 5)
+    out["corrblock"] = {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "kind": kind,
+                        "ours_over_reference": our_value / (B / (ms * 1e-3))}
+    torch.cuda.empty_cache()
+    # on-the-fly path at 4K
+    try:
+        from oracle import build_ref
+        ext = build_ref.load_module()
+    except Exception:
+        ext = None
+    if r == 4 and torch.cuda.mem_get_info()[0] > 8 * 2 ** 30:
+        H, W, D = 270, 480, 256
+        g = torch.Generator().manual_seed(5)
+        a1 = torch.randn(1, D, H, W, generator=g).to(f1.device)
+        a2 = torch.randn(1, D, H, W, generator=g).to(f1.device)
+        c4 = (rr.coords_grid(1, H, W, "cpu") + 2.0 * torch.randn(1, 2, H, W, generator=g)).to(f1.device)
+        alt = {"workload": "2160x3840 -> 270x480, D=256, 4 levels r=4, one iteration"}
+        for prec in ("bf16x3", "bf16"):
+            blk = rr.AlternateCorrBlock(a1, a2, num_levels=4, radius=4, precision=prec)
+            alt[f"ours_{prec}_ms"] = timeit(lambda: blk(c4), 2, 10)
+        if ext is not None:
+            blk = rr.AlternateCorrBlock(a1, a2, num_levels=4, radius=4)
+            f1n = a1.permute(0, 2, 3, 1).contiguous()
+            f2n = [x[1].permute(0, 2, 3, 1).contiguous() for x in blk.pyramid[:4]]
+            cs = [(c4.permute(0, 2, 3, 1) / 2 ** i).reshape(1, 1, H, W, 2).contiguous() for i in range(4)]
+
+            def ref_alt():
+                for i in range(4):
+                    ext.forward(f1n, f2n[i], cs[i], 4)
+
+            alt["reference_binary_ms"] = timeit(ref_alt, 1, 3)
+            alt["kind"] = "reference (alt_cuda_corr compiled unmodified, oracle/_ref)"
+        out["alt_corr_4k"] = alt
+    return out
 
 
 def run_reference(args):
@@ -415,10 +515,11 @@ def run_ours(args):
                    "share_of_step": look_ms * K / ms_step},
     }
     dom = "build" if build_ms >= look_ms * K else "lookup"
+    traffic, traffic_ncu = measured_traffic(dom, args, "tiled" if tiled else "rows")
     roofline = {"bound": "hbm", "kernel": "build_tc_kernel (prep + fused volume/pyramid)" if dom == "build"
                 else ("lookup_tiled_fwd_kernel" if tiled else "lookup_fwd_kernel"),
                 "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kern[dom]["gbs"] / peak,
-                "traffic": measured_traffic(dom, args, "tiled" if tiled else "rows"), "peak_source": peak_src,
+                "traffic": traffic, "traffic_ncu": traffic_ncu, "peak_source": peak_src,
                 "whole_step": {"alg_bytes": b_total, "gbs": b_total / (ms_step * 1e-3) / 1e9,
                                "frac": b_total / (ms_step * 1e-3) / 1e9 / peak}}
     line = {
@@ -453,6 +554,11 @@ def run_ours(args):
             ms = a0.elapsed_time(a1) / nrep
             extra[prec] = {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": nrep}
         line["fast_paths"] = extra
+    if world == 1 and not args.no_gpu_reference:
+        try:
+            line["gpu_reference"] = gpu_reference_run(args, f1, f2, coords, value)
+        except Exception as e:
+            log(f"[bench] gpu reference leg failed: {type(e).__name__}: {e}")
     if world == 1 and not args.no_cpu_baseline:
         try:
             c = cpu_reference_run(args, 2, 1, min(args.cpu_budget_s, 60.0))

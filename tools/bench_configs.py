@@ -111,6 +111,16 @@ def train_case():
     print(json.dumps(out), flush=True)
 
 
+def alt_only(precision, H=270, W=480):
+    """one precision of the on-the-fly kernel alone (ncu captures)"""
+    g = torch.Generator().manual_seed(1234)
+    f1 = torch.randn(1, 256, H, W, generator=g).to(DEV)
+    f2 = torch.randn(1, 256, H, W, generator=g).to(DEV)
+    coords = (rr.coords_grid(1, H, W, "cpu") + 2.0 * torch.randn(1, 2, H, W, generator=g)).to(DEV)
+    blk = rr.AlternateCorrBlock(f1, f2, num_levels=4, radius=4, precision=precision)
+    print(json.dumps({"case": f"alt4k_{precision}", "ms_per_iter": timeit(lambda: blk(coords), warm=2, reps=5)}), flush=True)
+
+
 def alt_case(H=270, W=480, name="alt_2160x3840"):
     """config 5: on-the-fly correlation, one iteration = 4 levels; vs the reference's binary."""
     B, D = 1, 256
@@ -152,3 +162,7 @@ if __name__ == "__main__":
         alt_case(55, 128, "alt_440x1024")
     if "alt4k" in which:
         alt_case()
+    if "alt4k_x3" in which:
+        alt_only("bf16x3")
+    if "alt4k_bf16" in which:
+        alt_only("bf16")
