@@ -226,6 +226,62 @@ def cpu_reference_run(args, steps, warmup, budget_s):
                       f"{len(times)} timed steps, mean"}
 
 
+def fused_convc1_run(args, f1, f2, coords):
+    """Its own key, never the headline: the step with every lookup fused into the motion encoder's convc1 + ReLU
+    (CorrBlock.lookup_convc1 = rc_corr_lookup_convc1_fwd, fp16 operands) against the unfused pair it replaces on
+    the same GPU (this repository's lookup, then cuDNN's 1x1 convolution + ReLU under fp16 autocast, as the
+    reference's --mixed_precision update block runs it)."""
+    import torch
+    import torch.nn.functional as F
+
+    import raft_ros_b200 as rr
+
+    K, L, r = args.iters, args.levels, args.radius
+    B, _, h, w = f1.shape
+    cout = 256 if r == 4 else 96
+    g = torch.Generator().manual_seed(7)
+    cin = L * (2 * r + 1) ** 2
+    W = (torch.randn(cout, cin, 1, 1, generator=g) / cin ** 0.5).to(f1.device)
+    bias = (0.1 * torch.randn(cout, generator=g)).to(f1.device)
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+
+    def timeit(fn, warm=3, reps=20):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    out = {"what": f"1 build + {K} x (lookup -> convc1 {cin}->{cout} 1x1 + ReLU), batch {B}", "operands": "fp16"}
+    N = h * w
+    for prec in (args.precision, "bf16_vol16"):
+        def fused_step():
+            blk = rr.CorrBlock(f1, f2, num_levels=L, radius=r, precision=prec)
+            for k in range(K):
+                blk.lookup_convc1(coords[k], W, bias)
+
+        def unfused_step():
+            blk = rr.CorrBlock(f1, f2, num_levels=L, radius=r, precision=prec)
+            for k in range(K):
+                with torch.autocast("cuda", dtype=torch.float16):
+                    F.relu(F.conv2d(blk(coords[k]), W, bias))
+
+        blk = rr.CorrBlock(f1, f2, num_levels=L, radius=r, precision=prec)
+        with torch.no_grad():
+            ms_f, ms_u = timeit(fused_step), timeit(unfused_step)
+            us_call = timeit(lambda: blk.lookup_convc1(coords[0], W, bias), reps=50) * 1e3
+        s_vol = 2 if prec == "bf16_vol16" else 4
+        alg = B * N * (L * (2 * r + 2) ** 2 * s_vol + cout * 4 + 8)  # read the integer patches, write Cout fp32, read coords
+        out[prec] = {"value": B / (ms_f * 1e-3), "unit": UNIT, "ms_per_step": ms_f, "unfused_ms_per_step": ms_u,
+                     "fused_call_us": us_call, "fused_call_alg_bytes": alg, "fused_call_gbs": alg / (us_call * 1e-6) / 1e9}
+    return out
+
+
 def gpu_reference_run(args, f1, f2, coords, our_value):
     """Comparator leg, outside every timed region of this repository's own numbers: the reference's own code
     on the SAME GPU.  (1) Its torch-op CorrBlock (core/corr.py unmodified from oracle/_ref/core when ferried,
@@ -554,6 +610,11 @@ def run_ours(args):
             ms = a0.elapsed_time(a1) / nrep
             extra[prec] = {"value": B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": nrep}
         line["fast_paths"] = extra
+    if world == 1 and tiled and not args.no_fast_paths and args.radius in (3, 4) and args.levels <= 4:
+        try:
+            line["fused"] = fused_convc1_run(args, f1, f2, coords)
+        except Exception as e:
+            log(f"[bench] fused lookup+convc1 leg failed: {type(e).__name__}: {e}")
     if world == 1 and not args.no_gpu_reference:
         try:
             line["gpu_reference"] = gpu_reference_run(args, f1, f2, coords, value)

@@ -180,6 +180,31 @@ int rc_corr_relayout16_level(const void *src, void *dst, int B, int N, int hl, i
                              void *stream);
 
 /*
+ * The lookup FUSED into its only consumer, the motion encoder's 1x1 convolution convc1 + ReLU
+ * (core/update.py:83,90: `cor = F.relu(self.convc1(corr))`; raft-small :66,72), so that the
+ * (B, L*(2r+1)^2, h, w) lookup result of core/corr.py:29-50 is never written to or re-read from
+ * global memory:
+ *     out[b, o, y, x] = relu(bias[o] + sum_c weight[o, c] * CorrBlock.__call__(coords)[b, c, y, x])
+ * levels : the TILED pyramid, fp32 (vol_fp16 = 0) or fp16 (vol_fp16 = 1), as for the tiled lookups.
+ * wprep  : the convolution's weight (Cout, L*(2r+1)^2) fp32, converted once per model by
+ *          rc_corr_convc1_prep_weight into rc_corr_convc1_weight_bytes() bytes of 16-bit operands
+ *          (K of every level zero-padded to whole tensor-core K blocks).
+ * bf16_ops : 0 = fp16 operands (taps and weights rounded to fp16, saturating -- the arithmetic
+ *          the reference's --mixed_precision autocast gives this convolution), 1 = bf16 operands.
+ *          One tensor-core pass, fp32 accumulation, fp32 bias / ReLU / output either way.
+ * out    : (B, Cout, h, w) fp32.  Cout a multiple of 16, <= 256 (256 raft-things, 96 raft-small);
+ *          radius 3 or 4; num_levels <= 4.
+ * This is a stated-bounds fast path beside rc_corr_lookup_tiled_fwd (whose fp32 result followed
+ * by an fp32 convolution is what the reference computes without autocast), not a replacement.
+ */
+size_t rc_corr_convc1_weight_bytes(int Cout, int num_levels, int radius);
+int rc_corr_convc1_prep_weight(const float *weight, void *wprep, int Cout, int num_levels, int radius,
+                               int bf16_ops, void *stream);
+int rc_corr_lookup_convc1_fwd(const void *const *level_ptrs, int vol_fp16, const float *coords,
+                              const void *wprep, const float *bias, float *out, int B, int h, int w,
+                              int num_levels, int radius, int Cout, int bf16_ops, void *stream);
+
+/*
  * Gradient of the lookup w.r.t. the pyramid (coords carry no gradient: they are detached at
  * core/raft.py:123).  Replaces what autograd does through core/corr.py:45 /
  * F.grid_sample's backward, but deterministically: row p of every level is only ever

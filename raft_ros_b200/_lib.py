@@ -106,6 +106,9 @@ SIGNATURES = {
     "rc_corr_lookup_tiled16_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_relayout16_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_tiled_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rc_corr_convc1_weight_bytes": (_sz, [_i, _i, _i]),
+    "rc_corr_convc1_prep_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "rc_corr_lookup_convc1_fwd": (_i, [ctypes.POINTER(_vp), _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_lookup_bwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), _i, _i, _i, _i, _i, _vp]),
     "rc_corr_build_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "rc_corr_build_bwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _sz, _vp]),

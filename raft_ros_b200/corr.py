@@ -493,6 +493,59 @@ class CorrBlock:
             return _LookupFn.apply(coords, self.radius, *self._rows)
         return lookup_raw(self._rows, coords, self.radius)
 
+    def lookup_convc1(self, coords, weight, bias, operands="fp16"):
+        """`F.relu(F.conv2d(self(coords), weight, bias))` in ONE launch (rc_corr_lookup_convc1_fwd): the lookup
+        fused into its only consumer, the motion encoder's 1x1 convolution convc1 + ReLU (reference
+        core/update.py:83,90; raft-small :66,72), so the (B, L*(2r+1)^2, h, w) lookup result is never
+        written to global memory.  Extension: the reference has no such call; `self(coords)` stays.
+
+        weight: (Cout, L*(2r+1)^2) or (Cout, L*(2r+1)^2, 1, 1) fp32, bias: (Cout,) fp32; Cout a multiple of 16, <= 256.
+        operands: "fp16" (taps and weights rounded to fp16, fp32 accumulate -- what the reference's
+        --mixed_precision autocast does to this convolution) or "bf16".  Returns (B, Cout, h, w) fp32.
+        Inference blocks on the tiled layout only (radius 3 or 4, <= 4 levels, a tensor-core precision).
+        The converted weights are cached on the block per (weight storage, version, operands)."""
+        if self._tiled is None:
+            raise RuntimeError("lookup_convc1 needs an inference CorrBlock on the tiled layout "
+                               "(radius 3 or 4, at most 4 levels, precision bf16x3 / bf16 / bf16_vol16, no gradient)")
+        if operands not in ("fp16", "bf16"):
+            raise ValueError(f"operands must be 'fp16' or 'bf16', got {operands!r}")
+        _require_cuda(coords, "coords")
+        _require_cuda(weight, "weight")
+        _require_cuda(bias, "bias")
+        B, h, w = self._geom
+        nl, r = self.num_levels, self.radius
+        K = nl * (2 * r + 1) ** 2
+        if weight.dim() == 4 and weight.shape[2:] == (1, 1):
+            weight = weight[:, :, 0, 0]
+        if weight.dim() != 2 or weight.shape[1] != K or bias.shape != (weight.shape[0],):
+            raise RuntimeError(f"expected weight (Cout, {K}[, 1, 1]) and bias (Cout,); got {tuple(weight.shape)}, {tuple(bias.shape)}")
+        Cout = weight.shape[0]
+        if tuple(coords.shape) != (B, 2, h, w):
+            raise RuntimeError(f"coords must be {(B, 2, h, w)}, got {tuple(coords.shape)}")
+        c = _f32c(coords)
+        L = _lib.lib()
+        bf = 1 if operands == "bf16" else 0
+        with torch.cuda.device(c.device):
+            key = (weight.data_ptr(), weight._version, bias.data_ptr(), bias._version, bf)
+            cache = self.__dict__.setdefault("_convc1_cache", {})
+            if key not in cache:
+                cache.clear()
+                nbytes = int(L.rc_corr_convc1_weight_bytes(Cout, nl, r))
+                if nbytes == 0:
+                    raise RuntimeError(f"lookup_convc1: unsupported Cout={Cout}, levels={nl}, radius={r}")
+                wp = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
+                w32 = _f32c(weight)
+                _lib.check(L.rc_corr_convc1_prep_weight(w32.data_ptr(), wp.data_ptr(), Cout, nl, r, bf, _stream()),
+                           "rc_corr_convc1_prep_weight")
+                cache[key] = (wp, _f32c(bias))
+            wp, b32 = cache[key]
+            out = torch.empty((B, Cout, h, w), dtype=torch.float32, device=c.device)
+            vol16 = 1 if self._tiled[0].dtype == torch.float16 else 0
+            rc = L.rc_corr_lookup_convc1_fwd(self._fast.ptrs, vol16, c.data_ptr(), wp.data_ptr(), b32.data_ptr(), out.data_ptr(),
+                                             B, h, w, nl, r, Cout, bf, _stream())
+            _lib.check(rc, "rc_corr_lookup_convc1_fwd")
+        return out
+
     @staticmethod
     def corr(fmap1, fmap2, precision=None):
         """(B,D,h,w) x2 -> (B,h,w,1,h,w): fmap1^T fmap2 / sqrt(D) (reference core/corr.py:52-60)."""

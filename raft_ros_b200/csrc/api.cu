@@ -194,6 +194,43 @@ int rc_corr_lookup_tiled16_fwd(const void *const *level_ptrs, const float *coord
   return launch_lookup_tiled16_fwd(lv, coords, out, B, h, w, num_levels, radius, static_cast<cudaStream_t>(stream));
 }
 
+size_t rc_corr_convc1_weight_bytes(int Cout, int num_levels, int radius) {
+  if (Cout <= 0 || num_levels <= 0 || num_levels > 4 || (radius != 3 && radius != 4)) return 0;
+  return convc1_weight_bytes(Cout, num_levels, radius);
+}
+
+int rc_corr_convc1_prep_weight(const float *weight, void *wprep, int Cout, int num_levels, int radius, int bf16_ops,
+                               void *stream) {
+  RC_CHECK_ARG(weight && wprep, "rc_corr_convc1_prep_weight: null pointer");
+  RC_CHECK_ARG(Cout > 0 && Cout <= 256 && Cout % 16 == 0, "rc_corr_convc1_prep_weight: Cout %d must be a multiple of 16, at most 256", Cout);
+  RC_CHECK_ARG(num_levels >= 1 && num_levels <= 4, "rc_corr_convc1_prep_weight: num_levels %d outside 1..4", num_levels);
+  RC_CHECK_ARG(radius == 3 || radius == 4, "rc_corr_convc1_prep_weight: radius %d unsupported (3 and 4 only)", radius);
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_corr_convc1_prep_weight: wprep must be 128-byte aligned");
+  return launch_convc1_prep_weight(weight, wprep, Cout, num_levels, radius, bf16_ops != 0, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_lookup_convc1_fwd(const void *const *level_ptrs, int vol_fp16, const float *coords, const void *wprep,
+                              const float *bias, float *out, int B, int h, int w, int num_levels, int radius, int Cout,
+                              int bf16_ops, void *stream) {
+  if (int rc = check_geometry("rc_corr_lookup_convc1_fwd", B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(level_ptrs && coords && wprep && bias && out, "rc_corr_lookup_convc1_fwd: null pointer");
+  RC_CHECK_ARG(Cout > 0 && Cout <= 256 && Cout % 16 == 0, "rc_corr_lookup_convc1_fwd: Cout %d must be a multiple of 16, at most 256", Cout);
+  if (num_levels > 4 || (radius != 3 && radius != 4)) {
+    set_error("rc_corr_lookup_convc1_fwd: radius 3 or 4 and at most 4 levels (got radius %d, %d levels)", radius, num_levels);
+    return RC_ERR_UNSUPPORTED;
+  }
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_corr_lookup_convc1_fwd: wprep must be 128-byte aligned");
+  RC_CHECK_ARG((long long)B * ((h * w + 127) / 128) < 0x7fffffffLL, "rc_corr_lookup_convc1_fwd: problem too large");
+  ConstLevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "rc_corr_lookup_convc1_fwd: level %d pointer is null", l);
+    RC_CHECK_ARG((reinterpret_cast<uintptr_t>(level_ptrs[l]) & 15) == 0, "rc_corr_lookup_convc1_fwd: level %d must be 16-byte aligned", l);
+    lv.p[l] = static_cast<const float *>(level_ptrs[l]);
+  }
+  return launch_lookup_convc1(lv, vol_fp16 != 0, coords, wprep, bias, out, B, h, w, num_levels, radius, Cout, bf16_ops != 0,
+                              static_cast<cudaStream_t>(stream));
+}
+
 int rc_corr_relayout16_level(const void *src, void *dst, int B, int N, int hl, int wl, int to_tiled,
                              void *stream) {
   RC_CHECK_ARG(src && dst, "rc_corr_relayout16_level: null pointer");

@@ -83,6 +83,10 @@ int launch_lookup_fwd(const ConstLevelPtrs &lv, const float *coords, float *out,
                       int w, int L, int r, cudaStream_t st);
 int launch_lookup_tiled_fwd(const ConstLevelPtrs &lv, const float *coords, float *out, int B, int h,
                             int w, int L, int r, cudaStream_t st);
+size_t convc1_weight_bytes(int Cout, int L, int r);
+int launch_convc1_prep_weight(const float *w, void *wp, int Cout, int L, int r, int bf16_ops, cudaStream_t st);
+int launch_lookup_convc1(const ConstLevelPtrs &lv, bool vol16, const float *coords, const void *wp, const float *bias,
+                         float *out, int B, int h, int w, int L, int r, int Cout, int bf16_ops, cudaStream_t st);
 int launch_lookup_bwd(const float *gout, const float *coords, const LevelPtrs &glv, int B, int h,
                       int w, int L, int r, cudaStream_t st);
 size_t build_bwd_workspace_bytes(int B, int D, int h, int w);
