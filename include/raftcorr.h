@@ -261,9 +261,30 @@ int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords,
  *   out    : (B, num_levels*(2r+1)^2, H, W) fp32, fully overwritten, channel order as
  *            rc_corr_lookup_fwd; multiplied by scale (0 -> 1/sqrt(C), core/corr.py:91)
  *   plan   : device scratch of rc_alt_corr_pyramid_plan_bytes(...) bytes, 16 B aligned
- * radius must be 4 and num_levels <= 4 (raft-things geometry); other shapes use rc_alt_corr_fwd.
+ * radius must be 3 or 4 and num_levels <= 4 (raft-small / raft-things); other shapes use rc_alt_corr_fwd.
+ *
+ * rc_alt_prep_fmap_level is rc_alt_prep_fmap for pyramid level `level` (0..3) of the map, straight
+ * from the level-0 fp32 map: the (H>>level, W>>level) average-pooled map of core/corr.py:68-72 is
+ * formed in registers with the same nested 2x2 means (bit-identical to the avg_pool2d chain) and
+ * never written as fp32.
+ *
+ * rc_alt_corr_pyramid_setup / _run split rc_alt_corr_pyramid_fwd into what an AlternateCorrBlock
+ * fixes once (core/corr.py:64-72: the feature maps -> tensor maps, geometry) and what changes per call
+ * (core/corr.py:74: coords).  `setup` is a HOST buffer of rc_alt_corr_pyramid_setup_bytes() bytes owned
+ * by the caller; it holds no pointers to host memory and may be copied.  Here fmap1 may have its own
+ * spatial size (H1, W1) -- a band of query rows of a larger frame, coords and out then are (B, 2, H1, W1)
+ * and (B, L*(2r+1)^2, H1, W1) -- against the full (H2, W2) fmap2 pyramid: that is how one large pair is
+ * split over several GPUs by query rows.
  */
 int rc_alt_prep_fmap(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, void *stream);
+int rc_alt_prep_fmap_level(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level,
+                           void *stream);
+size_t rc_alt_corr_pyramid_setup_bytes(void);
+int rc_alt_corr_pyramid_setup(void *setup, const void *fmap1_hi, const void *fmap1_lo,
+                              const void *const *fmap2_hi, const void *const *fmap2_lo, int B, int H1, int W1,
+                              int H2, int W2, int C, int num_levels, int radius, int precision);
+int rc_alt_corr_pyramid_run(const void *setup, const float *coords, float *out, float scale, void *plan,
+                            size_t plan_bytes, void *stream);
 size_t rc_alt_corr_pyramid_plan_bytes(int B, int H, int W, int num_levels);
 int rc_alt_corr_pyramid_fwd(const void *fmap1_hi, const void *fmap1_lo, const void *const *fmap2_hi,
                             const void *const *fmap2_lo, const float *coords, float *out, int B, int H, int W,

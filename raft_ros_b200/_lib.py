@@ -114,6 +114,10 @@ SIGNATURES = {
     "rc_corr_build_bwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_alt_prep_fmap": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "rc_alt_prep_fmap_level": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "rc_alt_corr_pyramid_setup_bytes": (_sz, []),
+    "rc_alt_corr_pyramid_setup": (_i, [_vp, _vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _i, _i, _i, _i, _i, _i, _i, _i, _i]),
+    "rc_alt_corr_pyramid_run": (_i, [_vp, _vp, _vp, _f, _vp, _sz, _vp]),
     "rc_alt_corr_pyramid_plan_bytes": (_sz, [_i, _i, _i, _i]),
     "rc_alt_corr_pyramid_fwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i,
                                      _i, _f, _vp, _sz, _vp]),

@@ -560,55 +560,89 @@ class CorrBlock:
 class AlternateCorrBlock:
     """On-the-fly windowed correlation, no materialised volume (reference core/corr.py:63-91).
 
-    `pyramid` keeps the reference's attribute: num_levels+1 pairs of average-pooled feature
-    maps.  With precision "bf16x3" (default, fp32-class) or "bf16" and the raft-things geometry
-    (radius 4, <= 4 levels, fmap1 and fmap2 of one shape) every call is ONE tensor-core launch
-    for all levels (rc_alt_corr_pyramid_fwd): the feature maps are converted once here, not
-    re-permuted on every call as in core/corr.py:82-83.  precision="fp32", other radii or shapes
-    use the per-level CUDA-core kernel behind `alt_cuda_corr.forward`.  Forward only, as in the
-    reference.
+    `pyramid` keeps the reference's attribute (num_levels+1 pairs of average-pooled feature maps) but is
+    only computed if somebody reads it: the kernels need neither the pooled fmap1 nor the fp32 pooled
+    fmap2 that core/corr.py:68-72 builds.  With precision "bf16x3" (default, fp32-class) or "bf16", radius
+    3 or 4 and <= 4 levels every call is ONE tensor-core launch for all levels (rc_alt_corr_pyramid_run):
+    the feature maps are pooled, converted and described to the TMA unit once here -- not re-permuted on
+    every call as in core/corr.py:82-83 -- so a call is one shape check, one allocation and one C call.
+    precision="fp32" or other radii use the per-level CUDA-core kernel behind `alt_cuda_corr.forward`.
+    fmap1 may be a band of query rows, (B, C, H1, W1) against the full (B, C, H2, W2) fmap2 (coords in
+    fmap2's frame): how one large pair is split over several GPUs (raft_ros_b200.shard).  Forward only,
+    as in the reference.  A block is used from one stream at a time (its plan scratch is reused).
     """
 
     def __init__(self, fmap1, fmap2, num_levels=4, radius=4, precision=None):
-        from torch.nn import functional as F
-
         self.num_levels = num_levels
         self.radius = radius
         _require_cuda(fmap1, "fmap1")
         _require_cuda(fmap2, "fmap2")
-        self.pyramid = [(fmap1, fmap2)]
-        for _ in range(self.num_levels):
-            fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
-            fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
-            self.pyramid.append((fmap1, fmap2))
+        self._fmaps = (fmap1, fmap2)
+        self._pyramid = None
         self._prec = _precision_code(precision)
         if self._prec == _lib.RC_PREC_BF16_VOL16:
             raise ValueError("precision 'bf16_vol16' applies to CorrBlock (there is no volume here); use 'bf16'")
-        f1, f2 = self.pyramid[0]
-        self._tc = (self._prec != _lib.RC_PREC_FP32 and radius == 4 and 1 <= num_levels <= 4
-                    and f1.shape == f2.shape and f1.dim() == 4)
+        if fmap1.dim() != 4 or fmap2.dim() != 4 or fmap1.shape[:2] != fmap2.shape[:2] or fmap1.device != fmap2.device:
+            raise RuntimeError(f"fmap1/fmap2 must be (B,C,H,W) with the same B, C and device; got {tuple(fmap1.shape)} and "
+                               f"{tuple(fmap2.shape)}")
+        self._tc = self._prec != _lib.RC_PREC_FP32 and radius in (3, 4) and 1 <= num_levels <= 4
         if self._tc:
-            level_shapes(f1.shape[2], f1.shape[3], num_levels)  # raises if a level would be empty
-            want_lo = self._prec == _lib.RC_PREC_BF16X3
-            self._f1_tc = self._prep(f1, want_lo)
-            self._f2_tc = [self._prep(self.pyramid[i][1], want_lo) for i in range(num_levels)]
+            self._setup_tc()
         else:
-            self._f1_nhwc = _f32c(f1.permute(0, 2, 3, 1))
-            self._f2_nhwc = [_f32c(self.pyramid[i][1].permute(0, 2, 3, 1)) for i in range(self.num_levels)]
+            from torch.nn import functional as F
+            self._f1_nhwc = _f32c(fmap1.permute(0, 2, 3, 1))
+            self._f2_nhwc, f2 = [], fmap2
+            for _ in range(self.num_levels):
+                self._f2_nhwc.append(_f32c(f2.permute(0, 2, 3, 1)))
+                f2 = F.avg_pool2d(f2, 2, stride=2)
 
-    @staticmethod
-    def _prep(fmap, want_lo):
-        """(B,C,H,W) fp32 -> K-major bf16 hi (+ lo residual) for the TMA-fed tensor-core kernel."""
-        f = _f32c(fmap)
-        B, C, H, W = f.shape
+    @property
+    def pyramid(self):
+        """[(fmap1, fmap2)] + num_levels x avg_pool2d of both, as core/corr.py:67-72 (computed on first access)."""
+        if self._pyramid is None:
+            from torch.nn import functional as F
+            fmap1, fmap2 = self._fmaps
+            self._pyramid = [(fmap1, fmap2)]
+            for _ in range(self.num_levels):
+                fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
+                fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
+                self._pyramid.append((fmap1, fmap2))
+        return self._pyramid
+
+    def _setup_tc(self):
+        import ctypes
+        L = _lib.lib()
+        f1, f2 = _f32c(self._fmaps[0]), _f32c(self._fmaps[1])
+        B, C, H1, W1 = f1.shape
+        _, _, H2, W2 = f2.shape
+        level_shapes(H2, W2, self.num_levels)  # raises if a level would be empty
+        x3 = self._prec == _lib.RC_PREC_BF16X3
         Cp = (C + 63) // 64 * 64
-        with torch.cuda.device(f.device):
-            hi = torch.empty((B, H, W, Cp), dtype=torch.bfloat16, device=f.device)
-            lo = torch.empty_like(hi) if want_lo else None
-            rc = _lib.lib().rc_alt_prep_fmap(f.data_ptr(), hi.data_ptr(), lo.data_ptr() if want_lo else None,
-                                             B, C, H, W, _stream())
-            _lib.check(rc, "rc_alt_prep_fmap")
-        return hi, lo
+        dev = f1.device
+        with torch.cuda.device(dev):
+            def prep(f, H, W, level):
+                hi = torch.empty((B, H >> level, W >> level, Cp), dtype=torch.bfloat16, device=dev)
+                lo = torch.empty_like(hi) if x3 else None
+                rc = L.rc_alt_prep_fmap_level(f.data_ptr(), hi.data_ptr(), lo.data_ptr() if x3 else None, B, C, H, W, level,
+                                              _stream())
+                _lib.check(rc, "rc_alt_prep_fmap_level")
+                return hi, lo
+
+            self._f1_tc = prep(f1, H1, W1, 0)
+            self._f2_tc = [prep(f2, H2, W2, l) for l in range(self.num_levels)]
+            self._setup = ctypes.create_string_buffer(int(L.rc_alt_corr_pyramid_setup_bytes()))
+            f2_hi = _lib.ptr_array([t[0].data_ptr() for t in self._f2_tc])
+            f2_lo = _lib.ptr_array([t[1].data_ptr() if x3 else None for t in self._f2_tc])
+            rc = L.rc_alt_corr_pyramid_setup(self._setup, self._f1_tc[0].data_ptr(), self._f1_tc[1].data_ptr() if x3 else None,
+                                             f2_hi, f2_lo, B, H1, W1, H2, W2, C, self.num_levels, self.radius, self._prec)
+            _lib.check(rc, "rc_alt_corr_pyramid_setup")
+            self._plan_bytes = int(L.rc_alt_corr_pyramid_plan_bytes(B, H1, W1, self.num_levels))
+            self._plan = torch.empty(self._plan_bytes, dtype=torch.uint8, device=dev)
+        rd = 2 * self.radius + 1
+        self._shape, self._out_shape, self._device = (B, 2, H1, W1), (B, self.num_levels * rd * rd, H1, W1), dev
+        # the reference divides by torch.sqrt(torch.tensor(dim).float()): an fp32 square root (core/corr.py:91)
+        self._scale = 1.0 / float(torch.sqrt(torch.tensor(float(C))))
+        self._run = L.rc_alt_corr_pyramid_run
 
     def __call__(self, coords):
         if self._tc:
@@ -617,7 +651,7 @@ class AlternateCorrBlock:
 
         coords = coords.permute(0, 2, 3, 1)
         B, H, W, _ = coords.shape
-        dim = self.pyramid[0][0].shape[1]
+        dim = self._fmaps[0].shape[1]
         corr_list = []
         for i in range(self.num_levels):
             coords_i = (coords / 2 ** i).reshape(B, 1, H, W, 2).contiguous()
@@ -629,23 +663,15 @@ class AlternateCorrBlock:
 
     def _call_tc(self, coords):
         _require_cuda(coords, "coords")
-        c = _f32c(coords)
-        B, C, H, W = self.pyramid[0][0].shape
-        if tuple(c.shape) != (B, 2, H, W):
-            raise RuntimeError(f"coords must be {(B, 2, H, W)}, got {tuple(c.shape)}")
-        L = _lib.lib()
-        nl, rd = self.num_levels, 2 * self.radius + 1
-        x3 = self._prec == _lib.RC_PREC_BF16X3
-        with torch.cuda.device(c.device):
-            out = torch.empty((B, nl * rd * rd, H, W), dtype=torch.float32, device=c.device)
-            nbytes = int(L.rc_alt_corr_pyramid_plan_bytes(B, H, W, nl))
-            plan = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
-            f2_hi = _lib.ptr_array([t[0].data_ptr() for t in self._f2_tc])
-            f2_lo = _lib.ptr_array([t[1].data_ptr() if x3 else None for t in self._f2_tc])
-            # scale: the reference divides by an fp32 sqrt(dim) (core/corr.py:91)
-            scale = 1.0 / float(torch.sqrt(torch.tensor(float(C))))
-            rc = L.rc_alt_corr_pyramid_fwd(self._f1_tc[0].data_ptr(), self._f1_tc[1].data_ptr() if x3 else None,
-                                           f2_hi, f2_lo, c.data_ptr(), out.data_ptr(), B, H, W, C, nl, self.radius,
-                                           self._prec, scale, plan.data_ptr(), nbytes, _stream())
-            _lib.check(rc, "rc_alt_corr_pyramid_fwd")
+        if tuple(coords.shape) != self._shape:
+            raise RuntimeError(f"coords must be {self._shape}, got {tuple(coords.shape)}")
+        c = coords if (coords.dtype is torch.float32 and coords.is_contiguous() and not coords.requires_grad) else _f32c(coords)
+        if c.device != self._device:
+            raise RuntimeError("coords must be on the feature maps' device")
+        with torch.cuda.device(self._device):
+            out = torch.empty(self._out_shape, dtype=torch.float32, device=self._device)
+            rc = self._run(self._setup, c.data_ptr(), out.data_ptr(), self._scale, self._plan.data_ptr(), self._plan_bytes,
+                           torch.cuda.current_stream().cuda_stream)
+            if rc:
+                _lib.check(rc, "rc_alt_corr_pyramid_run")
         return out

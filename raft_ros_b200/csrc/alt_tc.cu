@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstring>
 #include <mutex>
 
 #include "common.cuh"
@@ -31,24 +32,24 @@ namespace alttc {
 
 using namespace tc;
 
-constexpr int R = 4;                 // window radius this kernel is specialised for
-constexpr int RD = 2 * R + 1, PN = RD + 1, NTAP = RD * RD, NPATCH = PN * PN;
 constexpr int QH = 8, QW = 16;       // query tile (rows x cols) = 128 pixels = TMEM lanes
-constexpr int CW = 32, CHH = 8;      // target chunk (cols x rows) = 256 = TMEM columns
+// target chunk = 256 fmap2 pixels = TMEM columns, in one of two shapes chosen per (tile, level) by the plan:
+// 32 x 8 (wide boxes: level 0 of a 16-wide tile) or 16 x 16 (the small boxes of the coarse levels fit one)
+constexpr int CW0 = 32, CH0 = 8, CW1 = 16, CH1 = 16;
 constexpr int TK = 64, UK = 16;
 constexpr int A_BYTES = 128 * TK * 2, B_BYTES = 256 * TK * 2;
 constexpr int kStageBytes = A_BYTES + B_BYTES;   // one operand pair per stage
 constexpr int kStages = 3;
 constexpr int kEpiWarps = 4, kProducerWarp = 4, kMmaWarp = 5, kThreads = 192;
-constexpr int kPatchStride = NPATCH + 1;         // 101: odd -> conflict-free across lanes
-constexpr int kPatchBytes = 128 * kPatchStride * 4;
+constexpr int kPatchStrideMax = 101;             // (2*4+2)^2 + 1: odd -> conflict-free across lanes
+constexpr int kPatchBytes = 128 * kPatchStrideMax * 4;
 constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kPatchBytes + 256;
 constexpr uint32_t kIdescA = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr int kMaxLevels = 4;
 
 struct Maps {
-  CUtensorMap a[2];               // fmap1 hi, lo: (Cp, W1, H1, B), box (64, 16, 8, 1)
-  CUtensorMap b[kMaxLevels][2];   // fmap2 level l hi, lo: (Cp, W2, H2, B), box (64, 32, 8, 1)
+  CUtensorMap a[2];                  // fmap1 hi, lo: (Cp, W1, H1, B), box (64, 16, 8, 1)
+  CUtensorMap b[kMaxLevels][2][2];   // fmap2 level l, chunk shape s (box (64, 32, 8, 1) / (64, 16, 16, 1)), hi / lo
 };
 
 struct Params {
@@ -58,16 +59,20 @@ struct Params {
   int h2[kMaxLevels], w2[kMaxLevels];
   const float *coords;   // (B, 2, H1, W1)
   float *out;            // (B, L*81, H1, W1)
-  const int4 *plan;      // [tile][level] = {box x0, box y0, chunks in x, chunks in y}
+  const int4 *plan;      // [tile][level] = {box x0, box y0, chunks in x | shape << 16, chunks in y}
   float scale;
 };
 
 // ------------------------------------------------------------------ plan
+template <int R>
 __global__ void __launch_bounds__(128)
 alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B, int H1, int W1, int L, int tiles_x,
-                int tiles_y, long long total_tiles, int h2_0, int w2_0) {
+                int tiles_y, long long total_tiles, int h2_0, int w2_0, int allow_square) {
+  constexpr int PN = 2 * R + 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long tile = (long long)blockIdx.x * 4 + warp;
+  pdl_launch_dependents();
+  pdl_wait();
   if (tile >= total_tiles) return;
   const int per_item = tiles_x * tiles_y;
   const int b = (int)(tile / per_item);
@@ -109,15 +114,25 @@ alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B
     }
     if (lane == 0) {
       int4 e = make_int4(0, 0, 0, 0);
-      if (xmin < xmax && ymin < ymax) e = make_int4(xmin, ymin, (xmax - xmin + CW - 1) / CW, (ymax - ymin + CHH - 1) / CHH);
+      if (xmin < xmax && ymin < ymax) {
+        const int bw = xmax - xmin, bh = ymax - ymin;
+        const int nx0 = (bw + CW0 - 1) / CW0, ny0 = (bh + CH0 - 1) / CH0, nx1 = (bw + CW1 - 1) / CW1, ny1 = (bh + CH1 - 1) / CH1;
+        // fewer chunks = fewer MMAs: what counts in bf16x3 (tensor-bound).  A single bf16 pass is bound by the
+        // epilogue, which skips whole accumulator rows of a 32 x 8 chunk more often: it keeps that shape.
+        e = (allow_square && nx1 * ny1 < nx0 * ny0) ? make_int4(xmin, ymin, nx1 | (1 << 16), ny1) : make_int4(xmin, ymin, nx0, ny0);
+      }
       plan[tile * L + l] = e;
     }
   }
 }
 
 // ------------------------------------------------------------------ main kernel
+template <int R>
 __global__ void __launch_bounds__(kThreads, 1)
 alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
+  constexpr int RD = 2 * R + 1, PN = RD + 1, NTAP = RD * RD, NPATCH = PN * PN;
+  constexpr int kPatchStride = NPATCH + 1;  // odd -> conflict-free across lanes
+  static_assert(kPatchStride <= kPatchStrideMax, "patch buffer");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = smem_u32(smem_raw);
   const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
@@ -127,6 +142,7 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   uint64_t *full = bars, *empty = bars + kStages, *tfull = bars + 2 * kStages, *tempty = tfull + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
 
   if (warp == kProducerWarp && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -143,6 +159,7 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();  // the plan (previous kernel), the coordinates and the feature maps are read from here on
   const uint32_t tmem_base = *tmem_slot;
   const int per_item = P.tiles_x * P.tiles_y;
   const int steps = P.k_blocks * P.npass;  // operand-pair steps per chunk
@@ -157,16 +174,18 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
         const int ty0 = (rem / P.tiles_x) * QH, tx0 = (rem % P.tiles_x) * QW;
         for (int l = 0; l < P.L; ++l) {
           const int4 pl = __ldg(P.plan + t * P.L + l);
+          const int shape = pl.z >> 16, ncx = pl.z & 0xffff;
+          const int cw = shape ? CW1 : CW0, chh = shape ? CH1 : CH0;
           for (int cyi = 0; cyi < pl.w; ++cyi)
-            for (int cxi = 0; cxi < pl.z; ++cxi) {
-              const int ox = pl.x + cxi * CW, oy = pl.y + cyi * CHH;
+            for (int cxi = 0; cxi < ncx; ++cxi) {
+              const int ox = pl.x + cxi * cw, oy = pl.y + cyi * chh;
               for (int s = 0; s < steps; ++s) {
                 const int kb = s / P.npass, pr = s - kb * P.npass;  // pr: 0 hi*hi, 1 hi*lo, 2 lo*hi
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t *sp = smem + stage * kStageBytes;
                 mbar_expect_tx(&full[stage], kStageBytes);
                 tma_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
-                tma_load_4d(sp + A_BYTES, &M.b[l][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
+                tma_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
               }
             }
@@ -180,7 +199,7 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
       for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
         for (int l = 0; l < P.L; ++l) {
           const int4 pl = __ldg(P.plan + t * P.L + l);
-          const int chunks = pl.z * pl.w;
+          const int chunks = (pl.z & 0xffff) * pl.w;
           for (int c = 0; c < chunks; ++c) {
             mbar_wait(&tempty[acc], acc_phase ^ 1);
             tc_fence_after();
@@ -231,29 +250,46 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
 #pragma unroll 4
         for (int i = 0; i < NPATCH; ++i) sts32(patch + i * 4, 0.0f);
         const int4 pl = __ldg(P.plan + t * P.L + l);
+        const int shape = pl.z >> 16, ncx = pl.z & 0xffff;
+        const int cw = shape ? CW1 : CW0, chh = shape ? CH1 : CH0;
         for (int cyi = 0; cyi < pl.w; ++cyi)
-          for (int cxi = 0; cxi < pl.z; ++cxi) {
-            const int ox = pl.x + cxi * CW, oy = pl.y + cyi * CHH;
+          for (int cxi = 0; cxi < ncx; ++cxi) {
+            const int ox = pl.x + cxi * cw, oy = pl.y + cyi * chh;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256);
-            const bool xhit = pvalid && x0 + PN > ox && x0 < ox + CW;
+            const bool xhit = pvalid && x0 + PN > ox && x0 < ox + cw;
+            // window column px of this pixel is chunk column cbase + px: every register goes straight to
+            // its patch slot under a predicate (no bounce through a row buffer; the epilogue has issue
+            // slots to spare, shared-memory round trips it has not)
+            const int cbase = x0 - ox;
 #pragma unroll 1
-            for (int rr = 0; rr < CHH; ++rr) {
-              const int py = oy + rr - y0;
-              const bool need = xhit && (unsigned)py < (unsigned)PN;
-              if (__any_sync(0xffffffffu, need)) {  // tcgen05.ld is warp-collective
+            for (int rr = 0; rr < 8; ++rr) {
+              // 32 accumulator columns per load: one chunk row (32 x 8 chunks) or two (16 x 16 chunks)
+              const int py0 = oy + (shape ? 2 * rr : rr) - y0;
+              const bool need0 = xhit && (unsigned)py0 < (unsigned)PN;
+              const bool need1 = shape && xhit && (unsigned)(py0 + 1) < (unsigned)PN;
+              if (__any_sync(0xffffffffu, need0 || need1)) {  // tcgen05.ld is warp-collective
                 float v[32];
-                tmem_ld32(taddr + rr * CW, v);
+                tmem_ld32(taddr + rr * 32, v);
                 tmem_ld_wait();
-                if (need) {
-                  // window column px of this pixel is accumulator column cbase + px: every register goes
-                  // straight to its patch slot under a predicate (no bounce through a row buffer; the
-                  // epilogue has issue slots to spare, shared-memory round trips it has not)
-                  const int cbase = x0 - ox;
-                  const uint32_t prow = patch + (uint32_t)((py * PN - cbase) * 4);
+                if (shape) {
+                  if (need0) {
+                    const uint32_t prow = patch + (uint32_t)((py0 * PN - cbase) * 4);
 #pragma unroll
-                  for (int c = 0; c < CW; ++c)
+                    for (int c = 0; c < CW1; ++c)
+                      if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[c]);
+                  }
+                  if (need1) {
+                    const uint32_t prow = patch + (uint32_t)(((py0 + 1) * PN - cbase) * 4);
+#pragma unroll
+                    for (int c = 0; c < CW1; ++c)
+                      if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[CW1 + c]);
+                  }
+                } else if (need0) {
+                  const uint32_t prow = patch + (uint32_t)((py0 * PN - cbase) * 4);
+#pragma unroll
+                  for (int c = 0; c < CW0; ++c)
                     if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[c]);
                 }
               }
@@ -325,6 +361,53 @@ alt_prep_kernel(const float *__restrict__ f, __nv_bfloat16 *__restrict__ hi, __n
   }
 }
 
+// The same for pyramid level LVL >= 1 of the feature map WITHOUT materialising the pooled fp32 map: the
+// reference pools iteratively (core/corr.py:68-72, F.avg_pool2d(.., 2, stride=2) of the previous level,
+// floor mode), each level rounded to fp32; the value here is formed by the same nested 2x2 means in the
+// same order (((a + b) + c) + d) * 0.25, so it is bit-identical to the chain.
+template <int LVL>
+__device__ __forceinline__ float pooled_at(const float *__restrict__ plane, int W, int y, int x) {
+  if constexpr (LVL == 0) {
+    return __ldg(plane + (size_t)y * W + x);
+  } else {
+    float s = pooled_at<LVL - 1>(plane, W, 2 * y, 2 * x) + pooled_at<LVL - 1>(plane, W, 2 * y, 2 * x + 1);
+    s += pooled_at<LVL - 1>(plane, W, 2 * y + 1, 2 * x);
+    s += pooled_at<LVL - 1>(plane, W, 2 * y + 1, 2 * x + 1);
+    return s * 0.25f;
+  }
+}
+
+template <int LVL>
+__global__ void __launch_bounds__(256)
+alt_prep_pool_kernel(const float *__restrict__ f, __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo, int C,
+                     int Cp, int H, int W, int with_lo) {
+  __shared__ float tile[32][33];
+  const int Hl = H >> LVL, Wl = W >> LVL, HWl = Hl * Wl;
+  const int b = blockIdx.z;
+  const float *src = f + (size_t)b * C * H * W;
+  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int d = d0 + ty + 8 * i, p = p0 + tx;
+    float v = 0.0f;
+    if (d < C && p < HWl) v = pooled_at<LVL>(src + (size_t)d * H * W, W, p / Wl, p % Wl);
+    tile[ty + 8 * i][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, d = d0 + tx;
+    if (p < HWl && d < Cp) {
+      const float x = tile[tx][ty + 8 * i];
+      const __nv_bfloat16 xh = __float2bfloat16_rn(x);
+      const size_t o = ((size_t)b * HWl + p) * Cp + d;
+      hi[o] = xh;
+      if (with_lo) lo[o] = __float2bfloat16_rn(x - __bfloat162float(xh));
+    }
+  }
+}
+
 // ------------------------------------------------------------------ host
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -369,6 +452,16 @@ static int sm_count() {
   return n;
 }
 
+// Everything about one AlternateCorrBlock that does not change between calls: the tensor maps of the
+// prepared feature maps and the geometry.  A plain host-side blob the caller keeps (no allocation here).
+struct Setup {
+  Maps M;
+  Params P;   // coords / out / plan / scale are filled per call
+  int radius;
+  unsigned magic;
+};
+constexpr unsigned kSetupMagic = 0x52434154u;
+
 }  // namespace alttc
 
 int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW, cudaStream_t st) {
@@ -380,44 +473,66 @@ int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW,
   return RC_OK;
 }
 
+int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level, cudaStream_t st) {
+  using namespace alttc;
+  if (level == 0) return launch_alt_prep(fmap, hi, lo, B, C, H * W, st);
+  const int Cp = (C + 63) / 64 * 64, HWl = (H >> level) * (W >> level);
+  if (HWl <= 0) {
+    set_error("rc_alt_prep_fmap_level: level %d of a %dx%d map is empty", level, H, W);
+    return RC_ERR_INVALID;
+  }
+  dim3 grid((unsigned)((HWl + 31) / 32), (unsigned)(Cp / 32), (unsigned)B);
+  __nv_bfloat16 *h = static_cast<__nv_bfloat16 *>(hi), *l = static_cast<__nv_bfloat16 *>(lo);
+  const int wl = lo != nullptr ? 1 : 0;
+  switch (level) {
+    case 1: alt_prep_pool_kernel<1><<<grid, 256, 0, st>>>(fmap, h, l, C, Cp, H, W, wl); break;
+    case 2: alt_prep_pool_kernel<2><<<grid, 256, 0, st>>>(fmap, h, l, C, Cp, H, W, wl); break;
+    case 3: alt_prep_pool_kernel<3><<<grid, 256, 0, st>>>(fmap, h, l, C, Cp, H, W, wl); break;
+    default:
+      set_error("rc_alt_prep_fmap_level: level %d unsupported (0..3)", level);
+      return RC_ERR_UNSUPPORTED;
+  }
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
 size_t alt_tc_plan_bytes(int B, int H1, int W1, int L) {
   const long long tiles = (long long)B * ((H1 + alttc::QH - 1) / alttc::QH) * ((W1 + alttc::QW - 1) / alttc::QW);
   return (size_t)tiles * L * sizeof(int4);
 }
 
-int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,
-                  const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius, int precision,
-                  float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st) {
+size_t alt_tc_setup_bytes() { return sizeof(alttc::Setup); }
+
+int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo, int B,
+                 int H1, int W1, int H2, int W2, int Cp, int L, int radius, int precision) {
   using namespace alttc;
-  if (radius != R || L < 1 || L > kMaxLevels) {
-    set_error("rc_alt_corr_pyramid_fwd: the tensor-core path covers radius %d and 1..%d levels (got r=%d, L=%d)", R,
-              kMaxLevels, radius, L);
+  if ((radius != 3 && radius != 4) || L < 1 || L > kMaxLevels) {
+    set_error("rc_alt_corr_pyramid: the tensor-core path covers radius 3 or 4 and 1..%d levels (got r=%d, L=%d)", kMaxLevels,
+              radius, L);
     return RC_ERR_UNSUPPORTED;
   }
   if (Cp % TK != 0) {
-    set_error("rc_alt_corr_pyramid_fwd: channel pitch %d must be a multiple of %d", Cp, TK);
+    set_error("rc_alt_corr_pyramid: channel pitch %d must be a multiple of %d", Cp, TK);
     return RC_ERR_INVALID;
   }
-  const size_t need = alt_tc_plan_bytes(B, H1, W1, L);
-  if (plan_ws == nullptr || plan_bytes < need || (reinterpret_cast<uintptr_t>(plan_ws) & 15) != 0) {
-    set_error("rc_alt_corr_pyramid_fwd: plan scratch missing, misaligned or too small (%zu < %zu bytes)", plan_bytes, need);
-    return RC_ERR_WORKSPACE;
-  }
   const bool x3 = precision == RC_PREC_BF16X3;
-  Maps M;
-  if (int rc = map4(&M.a[0], f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
-  if (int rc = map4(&M.a[1], x3 ? f1_lo : f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
-  Params P{};
+  Setup S{};
+  if (int rc = map4(&S.M.a[0], f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
+  if (int rc = map4(&S.M.a[1], x3 ? f1_lo : f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
+  Params &P = S.P;
   for (int l = 0; l < kMaxLevels; ++l) {
     const int ll = l < L ? l : L - 1;
-    P.h2[l] = H1 >> ll;
-    P.w2[l] = W1 >> ll;
+    P.h2[l] = H2 >> ll;
+    P.w2[l] = W2 >> ll;
     if (P.h2[l] < 1 || P.w2[l] < 1) {
-      set_error("rc_alt_corr_pyramid_fwd: level %d of a %dx%d grid is empty", ll, H1, W1);
+      set_error("rc_alt_corr_pyramid: level %d of a %dx%d grid is empty", ll, H2, W2);
       return RC_ERR_INVALID;
     }
-    if (int rc = map4(&M.b[l][0], f2_hi[ll], Cp, P.w2[l], P.h2[l], B, CW, CHH)) return rc;
-    if (int rc = map4(&M.b[l][1], x3 ? f2_lo[ll] : f2_hi[ll], Cp, P.w2[l], P.h2[l], B, CW, CHH)) return rc;
+    for (int sh = 0; sh < 2; ++sh) {
+      const int bw = sh ? CW1 : CW0, bh = sh ? CH1 : CH0;
+      if (int rc = map4(&S.M.b[l][sh][0], f2_hi[ll], Cp, P.w2[l], P.h2[l], B, bw, bh)) return rc;
+      if (int rc = map4(&S.M.b[l][sh][1], x3 ? f2_lo[ll] : f2_hi[ll], Cp, P.w2[l], P.h2[l], B, bw, bh)) return rc;
+    }
   }
   P.B = B; P.H1 = H1; P.W1 = W1; P.L = L;
   P.k_blocks = Cp / TK;
@@ -425,23 +540,56 @@ int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi
   P.tiles_x = (W1 + QW - 1) / QW;
   P.tiles_y = (H1 + QH - 1) / QH;
   P.total_tiles = (long long)B * P.tiles_x * P.tiles_y;
-  P.coords = coords;
-  P.out = out;
-  P.plan = static_cast<const int4 *>(plan_ws);
-  P.scale = scale;
+  S.radius = radius;
+  S.magic = kSetupMagic;
+  memcpy(blob, &S, sizeof(S));
+  return RC_OK;
+}
+
+template <int R>
+static int alt_tc_run_r(const alttc::Setup &S, cudaStream_t st) {
+  using namespace alttc;
+  const Params &P = S.P;
   {
     const unsigned blocks = (unsigned)((P.total_tiles + 3) / 4);
-    alt_plan_kernel<<<blocks, 128, 0, st>>>(coords, static_cast<int4 *>(plan_ws), B, H1, W1, L, P.tiles_x, P.tiles_y,
-                                            P.total_tiles, H1, W1);
-    RC_CUDA(cudaGetLastError());
+    RC_CUDA(launch_pdl(alt_plan_kernel<R>, dim3(blocks), dim3(128), 0, st, P.coords, const_cast<int4 *>(P.plan), P.B, P.H1, P.W1,
+                       P.L, P.tiles_x, P.tiles_y, P.total_tiles, P.h2[0], P.w2[0], P.npass == 3 ? 1 : 0));
   }
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
-  RC_CUDA(cudaFuncSetAttribute(alt_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  RC_CUDA(cudaFuncSetAttribute(alt_tc_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   const long long sms = sm_count();
   const unsigned grid = (unsigned)(P.total_tiles < sms ? P.total_tiles : sms);
-  alt_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(M, P);
-  RC_CUDA(cudaGetLastError());
+  RC_CUDA(launch_pdl(alt_tc_kernel<R>, dim3(grid), dim3(kThreads), (size_t)kSmemBytes, st, S.M, P));
   return RC_OK;
+}
+
+int alt_tc_run(const void *blob, const float *coords, float *out, float scale, void *plan_ws, size_t plan_bytes,
+               cudaStream_t st) {
+  using namespace alttc;
+  alignas(64) Setup S;
+  memcpy(&S, blob, sizeof(S));
+  if (S.magic != kSetupMagic) {
+    set_error("rc_alt_corr_pyramid_run: the setup blob was not initialised by rc_alt_corr_pyramid_setup");
+    return RC_ERR_INVALID;
+  }
+  const size_t need = alt_tc_plan_bytes(S.P.B, S.P.H1, S.P.W1, S.P.L);
+  if (plan_ws == nullptr || plan_bytes < need || (reinterpret_cast<uintptr_t>(plan_ws) & 15) != 0) {
+    set_error("rc_alt_corr_pyramid: plan scratch missing, misaligned or too small (%zu < %zu bytes)", plan_bytes, need);
+    return RC_ERR_WORKSPACE;
+  }
+  S.P.coords = coords;
+  S.P.out = out;
+  S.P.plan = static_cast<const int4 *>(plan_ws);
+  S.P.scale = scale;
+  return S.radius == 3 ? alt_tc_run_r<3>(S, st) : alt_tc_run_r<4>(S, st);
+}
+
+int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,
+                  const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius, int precision,
+                  float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st) {
+  alignas(64) unsigned char blob[sizeof(alttc::Setup)];
+  if (int rc = alt_tc_setup(blob, f1_hi, f1_lo, f2_hi, f2_lo, B, H1, W1, H1, W1, Cp, L, radius, precision)) return rc;
+  return alt_tc_run(blob, coords, out, scale, plan_ws, plan_bytes, st);
 }
 
 }  // namespace rc

@@ -325,6 +325,41 @@ int rc_alt_prep_fmap(const float *fmap, void *hi, void *lo, int B, int C, int H,
   return launch_alt_prep(fmap, hi, lo, B, C, H * W, static_cast<cudaStream_t>(stream));
 }
 
+int rc_alt_prep_fmap_level(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level, void *stream) {
+  RC_CHECK_ARG(fmap && hi, "rc_alt_prep_fmap_level: null pointer");
+  RC_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "rc_alt_prep_fmap_level: all sizes must be positive");
+  RC_CHECK_ARG(level >= 0 && level <= 3, "rc_alt_prep_fmap_level: level %d outside 0..3", level);
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(hi) & 15) == 0 && (reinterpret_cast<uintptr_t>(lo) & 15) == 0,
+               "rc_alt_prep_fmap_level: outputs must be 16-byte aligned");
+  return launch_alt_prep_pooled(fmap, hi, lo, B, C, H, W, level, static_cast<cudaStream_t>(stream));
+}
+
+size_t rc_alt_corr_pyramid_setup_bytes(void) { return alt_tc_setup_bytes(); }
+
+int rc_alt_corr_pyramid_setup(void *setup, const void *fmap1_hi, const void *fmap1_lo, const void *const *fmap2_hi,
+                              const void *const *fmap2_lo, int B, int H1, int W1, int H2, int W2, int C, int num_levels,
+                              int radius, int precision) {
+  if (int rc = check_geometry("rc_alt_corr_pyramid_setup", B, H2, W2, num_levels)) return rc;
+  RC_CHECK_ARG(setup && fmap1_hi && fmap2_hi, "rc_alt_corr_pyramid_setup: null pointer");
+  RC_CHECK_ARG(H1 > 0 && W1 > 0 && C > 0, "rc_alt_corr_pyramid_setup: sizes must be positive");
+  RC_CHECK_ARG(precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16,
+               "rc_alt_corr_pyramid_setup: precision must be RC_PREC_BF16X3 or RC_PREC_BF16");
+  RC_CHECK_ARG(precision == RC_PREC_BF16 || (fmap1_lo && fmap2_lo), "rc_alt_corr_pyramid_setup: BF16X3 needs the lo parts");
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(fmap2_hi[l] != nullptr, "rc_alt_corr_pyramid_setup: level %d pointer is null", l);
+    RC_CHECK_ARG(precision == RC_PREC_BF16 || fmap2_lo[l] != nullptr, "rc_alt_corr_pyramid_setup: level %d lo pointer is null", l);
+  }
+  return alt_tc_setup(setup, fmap1_hi, fmap1_lo, fmap2_hi, fmap2_lo, B, H1, W1, H2, W2, (C + 63) / 64 * 64, num_levels, radius,
+                      precision);
+}
+
+int rc_alt_corr_pyramid_run(const void *setup, const float *coords, float *out, float scale, void *plan, size_t plan_bytes,
+                            void *stream) {
+  RC_CHECK_ARG(setup && coords && out, "rc_alt_corr_pyramid_run: null pointer");
+  RC_CHECK_ARG(scale != 0.0f, "rc_alt_corr_pyramid_run: scale must be given (1/sqrt(C) for core/corr.py:91)");
+  return alt_tc_run(setup, coords, out, scale, plan, plan_bytes, static_cast<cudaStream_t>(stream));
+}
+
 size_t rc_alt_corr_pyramid_plan_bytes(int B, int H, int W, int num_levels) {
   if (B <= 0 || H <= 0 || W <= 0 || num_levels <= 0) return 0;
   return alt_tc_plan_bytes(B, H, W, num_levels);

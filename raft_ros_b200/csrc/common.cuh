@@ -104,7 +104,13 @@ int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const 
                    int r, cudaStream_t st);
 
 int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW, cudaStream_t st);
+int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level, cudaStream_t st);
 size_t alt_tc_plan_bytes(int B, int H1, int W1, int L);
+size_t alt_tc_setup_bytes();
+int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo, int B,
+                 int H1, int W1, int H2, int W2, int Cp, int L, int radius, int precision);
+int alt_tc_run(const void *blob, const float *coords, float *out, float scale, void *plan_ws, size_t plan_bytes,
+               cudaStream_t st);
 int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,
                   const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius,
                   int precision, float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st);

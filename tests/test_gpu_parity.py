@@ -370,6 +370,79 @@ def test_alternate_block_vs_oracle(rr, geom, kind, precision):
     assert torch.equal(blk(coords), b)  # deterministic
 
 
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("geom", [(2, 128, 24, 32, 4), (1, 128, 23, 39, 3), (1, 96, 46, 62, 4)])
+def test_alternate_block_radius3(rr, geom, precision):
+    """raft-small (core/raft.py:33: corr_radius = 3, 128 feature channels) on the tensor-core on-the-fly kernel,
+    against the oracle's CorrBlock restatement."""
+    B, D, h, w, L = geom
+    rng = np.random.default_rng(seed_of(geom, "r3"))
+    f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    blk = rr.AlternateCorrBlock(t(f1), t(f2), num_levels=L, radius=3, precision=precision)
+    assert blk._tc
+    pyr = O.corr_build(f1, f2, L)
+    tol = ALT_TOL[precision]
+    for kind in ("sigma4", "border", "oob", "grid"):
+        coords = make_coords(kind, B, h, w, rng)
+        want = O.corr_lookup(pyr, coords, 3)
+        got = n(blk(t(coords)))
+        assert got.shape == want.shape == (B, L * 49, h, w) and np.isfinite(got).all()
+        assert relmax(got, want) <= tol["rel"] + LOOKUP_TOL, (geom, kind, precision, relmax(got, want))
+        assert normwise(got, want) <= tol["norm"] + LOOKUP_TOL, (geom, kind, precision)
+
+
+@pytest.mark.parametrize("shape", [(2, 96, 27, 40), (1, 256, 55, 128), (1, 40, 8, 8)])
+def test_alt_prep_pools_like_avg_pool2d(rr, shape):
+    """rc_alt_prep_fmap_level forms pyramid level l of a feature map in registers; its hi / lo outputs are
+    bit-identical to converting the reference's avg_pool2d chain (core/corr.py:68-72)."""
+    from raft_ros_b200 import _lib
+    lib = _lib.lib()
+    B, C, H, W = shape
+    g = torch.Generator().manual_seed(H * W)
+    f = (torch.randn(B, C, H, W, generator=g) * 3).to(DEV)
+    Cp = (C + 63) // 64 * 64
+    st = torch.cuda.current_stream().cuda_stream
+    pooled = f
+    for level in range(4):
+        if level:
+            pooled = torch.nn.functional.avg_pool2d(pooled, 2, stride=2)
+        Hl, Wl = H >> level, W >> level
+        assert pooled.shape == (B, C, Hl, Wl)
+        outs = []
+        for src, fn, extra in ((f, lib.rc_alt_prep_fmap_level, (B, C, H, W, level)),
+                               (pooled.contiguous(), lib.rc_alt_prep_fmap, (B, C, Hl, Wl))):
+            hi = torch.full((B, Hl, Wl, Cp), float("nan"), dtype=torch.bfloat16, device=DEV)
+            lo = torch.full_like(hi, float("nan"))
+            assert fn(src.data_ptr(), hi.data_ptr(), lo.data_ptr(), *extra, st) == 0, lib.rc_last_error()
+            outs.append((hi, lo))
+        torch.cuda.synchronize()
+        assert torch.isfinite(outs[0][0].float()).all()
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), (shape, level)
+
+
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+def test_alternate_block_query_row_band(rr, precision):
+    """A band of query rows against the full fmap2 (how one large pair is split over GPUs):
+    bit-identical to the same rows of the whole-frame block when the band starts on a tile row, and within
+    rounding of it otherwise (the box of a query tile, and with it the summation split, depends on the tiling)."""
+    B, D, H, W, L = 1, 128, 43, 70, 4
+    rng = np.random.default_rng(43)
+    f1 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    coords = t(make_coords("sigma4", B, H, W, rng))
+    full = rr.AlternateCorrBlock(f1, f2, num_levels=L, radius=4, precision=precision)(coords)
+    for r0, r1 in ((0, 16), (16, 43), (11, 30)):
+        band = rr.AlternateCorrBlock(f1[:, :, r0:r1].contiguous(), f2, num_levels=L, radius=4, precision=precision)
+        got = band(coords[:, :, r0:r1].contiguous())
+        want = full[:, :, r0:r1]
+        assert got.shape == want.shape
+        if r0 % 8 == 0:
+            assert torch.equal(got, want), (r0, r1)
+        else:
+            assert relmax(n(got), n(want)) <= 2e-6, (r0, r1, relmax(n(got), n(want)))
+
+
 # ----------------------------------------------------------------------------- bilinear_sampler
 def test_bilinear_sampler_vs_grid_sample(rr):
     g = torch.Generator(device="cpu").manual_seed(3)
