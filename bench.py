@@ -427,6 +427,16 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
+    # host placement of the end-to-end arm: this rank's threads and the first touch of its pinned buffers go to
+    # the NUMA node its GPU hangs off (no effect on the device-timed numbers)
+    import contextlib
+
+    from raft_ros_b200 import hostbind
+    bind = hostbind.near_gpu(local, rank, world) if os.environ.get("RAFT_BENCH_NUMA_BIND", "1") != "0" else None
+
+    def pinned_alloc():
+        # `with pinned_alloc(): x = t.pin_memory()`: pages land on the GPU's NUMA node, then the thread is released
+        return bind if bind is not None else contextlib.nullcontext()
 
     if args.l2_fetch:
         _lib.check(_lib.lib().rc_set_l2_fetch_granularity(args.l2_fetch), "rc_set_l2_fetch_granularity")
@@ -440,11 +450,12 @@ def run_ours(args):
     N = h * w
     # every rank owns its own shard of frame pairs: no data-path collective
     g = torch.Generator().manual_seed(1234 + rank)
-    f1_host = torch.randn(B, D, h, w, generator=g).pin_memory()
-    f2_host = torch.randn(B, D, h, w, generator=g).pin_memory()
     base = rr.coords_grid(B, h, w, "cpu")
-    flows = torch.cumsum(0.5 * torch.randn(K, B, 2, h, w, generator=g), 0)
-    coords_host = (base[None] + flows).contiguous().pin_memory()  # (K,B,2,h,w)
+    with pinned_alloc():
+        f1_host = torch.randn(B, D, h, w, generator=g).pin_memory()
+        f2_host = torch.randn(B, D, h, w, generator=g).pin_memory()
+        flows = torch.cumsum(0.5 * torch.randn(K, B, 2, h, w, generator=g), 0)
+        coords_host = (base[None] + flows).contiguous().pin_memory()  # (K,B,2,h,w)
     f1, f2 = f1_host.to(dev), f2_host.to(dev)
     coords = coords_host.to(dev)
     torch.cuda.synchronize()
@@ -503,7 +514,10 @@ def run_ours(args):
         # Host side: pinned inputs, one pinned result buffer per lookup of a step.  Three streams so that
         # the PCIe directions and the kernels overlap: feature maps of the next pair go up on `s_up`
         # while the previous pair's lookups are still being read back on `s_down`.
-        out_host = [torch.empty((B, L * (2 * r + 1) ** 2, h, w), dtype=torch.float32).pin_memory() for _ in range(K)]
+        with pinned_alloc():
+            out_host = [torch.empty((B, L * (2 * r + 1) ** 2, h, w), dtype=torch.float32).pin_memory() for _ in range(K)]
+            for o_ in out_host:
+                o_.zero_()  # first touch
         s_main = torch.cuda.current_stream()
         s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
         ring = [[torch.empty_like(f1), torch.empty_like(f2), None] for _ in range(2)]  # device inputs, double-buffered
@@ -551,10 +565,21 @@ def run_ours(args):
             tt = torch.tensor([e_ms], device=dev, dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             e_ms = float(tt.item())
+        d2h_bytes = int(K * out_host[0].numel() * 4)
         e2e = {"value": world * B / (e_ms * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(2 * f1_host.numel() * 4 + K * coords_host[0].numel() * 4),
-               "d2h_bytes_per_step": int(K * out_host[0].numel() * 4), "ms_per_step": e_ms, "steps": n_e2e,
-               "overlap": "H2D, kernels and D2H on three streams; device inputs double-buffered"}
+               "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e_ms, "steps": n_e2e,
+               "overlap": "H2D, kernels and D2H on three streams; device inputs double-buffered",
+               "d2h_gbs": world * d2h_bytes / (e_ms * 1e-3) / 1e9, "host_binding": bind.info if bind is not None else {"bound": False}}
+        # ceiling measured on this box type by tools/probe_d2h.py (aggregate pinned D2H rate at this GPU count)
+        try:
+            probe = json.load(open(os.path.join(ROOT, "profiles", "r02_d2h_probe.json")))
+            ceil = probe.get(str(world), {}).get("bound_d2h", {}).get("aggregate_gbs")
+            if ceil:
+                e2e["probe_d2h_gbs"] = ceil
+                e2e["frac_of_probe"] = e2e["d2h_gbs"] / ceil
+        except Exception:
+            pass
 
     if rank != 0:
         if world > 1:

@@ -46,6 +46,34 @@ def gather_batch(local: torch.Tensor, num_pairs: int, group=None) -> torch.Tenso
     return torch.cat([bufs[r][: e - b] for r, (b, e) in enumerate(sizes)], dim=0)
 
 
+def shard_rows(num_rows: int, rank: int, world: int, align: int = 8) -> Tuple[int, int]:
+    """[begin, end) of the query ROWS of one large frame that `rank` owns: contiguous
+    bands whose starts are multiples of `align` (the on-the-fly kernel's query tile is 8 rows: aligned bands give
+    bit-identical results to the unsharded call), sizes as even as that allows; trailing ranks may own nothing when
+    the frame has fewer tile rows than ranks.  The band of fmap1 / coords goes with the FULL fmap2:
+    `AlternateCorrBlock(fmap1[:, :, b:e], fmap2)(coords[:, :, b:e])`."""
+    if world < 1 or not (0 <= rank < world) or num_rows < 0 or align < 1:
+        raise ValueError(f"bad shard request: num_rows={num_rows}, rank={rank}, world={world}, align={align}")
+    units = (num_rows + align - 1) // align
+    b, e = shard_bounds(units, rank, world)
+    return min(b * align, num_rows), min(e * align, num_rows)
+
+
+def gather_rows(local: torch.Tensor, num_rows: int, align: int = 8, group=None) -> torch.Tensor:
+    """Assemble (B, C, rows_r, W) bands into the (B, C, num_rows, W) result on every rank (all_gather on padded bands)."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    sizes = [shard_rows(num_rows, r, world, align) for r in range(world)]
+    cap = max(e - b for b, e in sizes)
+    B, C, _, W = local.shape
+    pad = torch.zeros((B, C, cap, W), dtype=local.dtype, device=local.device)
+    pad[:, :, : local.shape[2]] = local
+    bufs: List[torch.Tensor] = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(bufs, pad, group=group)
+    return torch.cat([bufs[r][:, :, : e - b] for r, (b, e) in enumerate(sizes)], dim=2)
+
+
 def max_over_ranks(value: float, device, group=None) -> float:
     """Device-side timing convention of bench.py: a step takes as long as its slowest rank."""
     import torch.distributed as dist
