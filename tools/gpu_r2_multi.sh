@@ -9,7 +9,7 @@ for N in $1; do port=$((port+1))
 done
 for N in $2; do port=$((port+1))
   timeout 600 $TR --nproc-per-node $N --master-port $port bench.py --gpus $N --steps 30 --warmup 3 > gpurun_out/r02_bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench N=$N rc=$?"
-  python -c "import json; d=json.load(open('gpurun_out/r02_bench_n$N.json')); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d.get('e2e'))"; tail -2 gpurun_out/bench_n$N.err
+  python -c "import json; d=json.loads(open('gpurun_out/r02_bench_n$N.json').read().strip().splitlines()[-1]); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d.get('e2e'))"; tail -2 gpurun_out/bench_n$N.err
 done
 for N in $3; do port=$((port+1))
   timeout 300 $TR --nproc-per-node $N --master-port $port tools/train_step_ddp.py --steps 20 > gpurun_out/r02_ddp_train_n$N.json 2> gpurun_out/ddp_n$N.err; echo "ddp N=$N rc=$?"; cat gpurun_out/r02_ddp_train_n$N.json; tail -2 gpurun_out/ddp_n$N.err

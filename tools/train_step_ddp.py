@@ -68,18 +68,15 @@ def main():
         model = nn.parallel.DistributedDataParallel(model, device_ids=[local])
     opt = torch.optim.AdamW(model.parameters(), lr=1e-5)
 
-    import contextlib
-
     def step(sync=True):
         opt.zero_grad(set_to_none=True)
-        ctx = contextlib.nullcontext() if (sync or world == 1) else model.no_sync()
-        with ctx:
-            f1, f2 = model(x1).float(), model(x2).float()
-            blk = rr.CorrBlock(f1, f2, radius=4, precision=a.precision)
-            loss = 0
-            for k in range(K):
-                loss = loss + (blk(coords[k]) * proj).sum()
-            loss.backward()
+        net = model if (sync or world == 1) else model.module  # the bare module: same step, no gradient exchange
+        f1, f2 = net(x1).float(), net(x2).float()
+        blk = rr.CorrBlock(f1, f2, radius=4, precision=a.precision)
+        loss = 0
+        for k in range(K):
+            loss = loss + (blk(coords[k]) * proj).sum()
+        loss.backward()
         opt.step()
         return loss
 
