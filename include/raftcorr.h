@@ -98,8 +98,13 @@ int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, 
  *   - a problem whose rc_corr_build_workspace_bytes(...) exceeds RC_STATIC_SCRATCH_BYTES is
  *     rejected with RC_ERR_WORKSPACE and nothing is launched (32 MiB covers two 440x1024 pairs in
  *     BF16X3, four in BF16);
- *   - the first call on a device looks up the array's device address; issue that first call
- *     before beginning any stream capture on that device;
+ *   - warm-up: the first call on a device looks up the array's device address, and -- because
+ *     the CUDA runtime loads kernels lazily -- the first launch of each kernel variant (one per
+ *     precision; one more for num_levels > 4) may itself make the driver allocate or synchronise
+ *     while it loads the code.  So make one call per device AND per precision you are going to use
+ *     (any small problem will do) before the phase in which nothing may allocate, and before
+ *     beginning any stream capture on that device.  The looked-up address is cached per device
+ *     for the life of the process: it does not survive cudaDeviceReset;
  *   - every call on a device uses the same array and finds the previous call's contents in it.
  *     Nothing must be cleared: each call rewrites all it reads.  Calls that overlap on the GPU
  *     race on the array; order them (same stream, or an event between streams).

@@ -23,7 +23,7 @@ _PRECISIONS = {"fp32": _lib.RC_PREC_FP32, "bf16x3": _lib.RC_PREC_BF16X3, "bf16":
 #: arithmetic of the all-pairs contraction when the caller does not say: "bf16x3" is the
 #: fp32-class tensor-core path (error-compensated bf16 operands, ~1e-5 normwise), "bf16" the
 #: single-pass fast path, "fp32" plain fp32 FMA on CUDA cores, "bf16_vol16" = "bf16" with the
-#: pyramid stored as fp16 (inference with radius 4 and <= 4 levels only; half the HBM traffic).
+#: pyramid stored as fp16 (inference with radius 3 or 4 and <= 4 levels only; half the HBM traffic).
 DEFAULT_PRECISION = os.environ.get("RAFT_CORR_PRECISION", "bf16x3")
 
 
@@ -103,8 +103,9 @@ def _tile_group() -> int:
 
 def tiled_level_elems(B: int, N: int, hl: int, wl: int, vol16: bool = False) -> int:
     """elements of one level in the tiled layout (include/raftcorr.h: rc_corr_tiled_level_elems /
-    rc_corr_tiled16_level_elems): [B][ceil(N/G)][hp/2][wp/cw][G][2][cw], G = rc_corr_tile_group(),
-    cw = 8 floats or 16 halves."""
+    rc_corr_tiled16_level_elems): [B][ceil(N/G)][hp/2][wp/cw][G pixels][4 chunks of 16 B], G = rc_corr_tile_group()
+    = 32, cw = 8 floats or 16 halves per tile row; chunk k = 2*(row & 1) + (column half) of pixel u sits at
+    position k ^ ((u >> 1) & 3).  Only the size is computed here; the addressing is in the header."""
     G = _tile_group()
     cw = 16 if vol16 else 8
     return B * ((N + G - 1) // G) * G * ((hl + 1) & ~1) * ((wl + cw - 1) & ~(cw - 1))
@@ -479,6 +480,9 @@ class CorrBlock:
         self._token = None
 
     def __call__(self, coords):
+        if coords.requires_grad and torch.is_grad_enabled():
+            # the reference's grid_sample would propagate to coords; its one caller detaches them first
+            raise RuntimeError("CorrBlock: gradients w.r.t. coords are not provided (detach them, as core/raft.py:123 does)")
         if self._token is not None:
             if torch.is_grad_enabled():
                 return _LookupTokenFn.apply(coords, self._token, self._state, self.radius)

@@ -81,12 +81,13 @@ struct Cfg {
 };
 
 // TILED: every row p of a level is cut into [hp/2][wp/8] tiles of 2 rows x 8 floats (hp = ceil2,
-// wp = ceil8 of the level's size, zeros in the padding that a lookup can touch) and the tiles of 8
-// consecutive query pixels are interleaved, [group][tile][pixel][2][8] -- the layout
-// lookup_tiled.cu reads.  It costs the epilogue nothing: a warp's row pair of the 8x32 patch IS
-// four whole tiles per query pixel, one store instruction writes one tile of 8 pixels = 512
-// contiguous bytes, and every tile is 64 B aligned whatever h and w are, so the stores are whole
-// 128 B lines for ragged sizes too.
+// wp = ceil8 of the level's size, zeros in the padding that a lookup can touch) and the tiles of
+// G = 32 consecutive query pixels are interleaved: [group][tile][pixel u][4 chunks of 16 B], chunk
+// k = 2*(row & 1) + (column half) of pixel u at position k ^ ((u >> 1) & 3) (include/raftcorr.h) --
+// the layout lookup_tiled.cu reads.  It costs the epilogue nothing: a warp (32 query pixels = one
+// group) holds, per row pair of the 8x32 patch, four whole tiles per pixel; two tiles of the group
+// are 4 KB of contiguous global memory, staged in that order (conflict-free thanks to the chunk
+// swizzle) and moved by one bulk copy; every tile is 64 B aligned whatever h and w are.
 // V16 (TILED only): the volume is stored as fp16 (saturating), tiles of 2 rows x 16 halves = the
 // same 64 B / 4 chunks per pixel, so the layout code is shared: the warp's row pair is two tiles.
 template <int NPASS, int NCTA, bool TILED, bool V16 = false>
@@ -254,7 +255,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     uint32_t acc_phase = 0;
     const int h = P.h, w = P.w, N = P.N, L = P.L;
     const int h1 = h >> 1, w1 = w >> 1, h2 = h >> 2, w2 = w >> 2, h3 = h >> 3, w3 = w >> 3;
-    // row layout: floats per volume row; tiled layout: floats per group of 8 query pixels
+    // row layout: floats per volume row; tiled layout: floats per group of G = 32 query pixels
     const size_t pitch0 = TILED ? (size_t)P.gstride[0] : (size_t)h * w, pitch1 = TILED ? (size_t)P.gstride[1] : (size_t)h1 * w1,
                  pitch2 = TILED ? (size_t)P.gstride[2] : (size_t)h2 * w2, pitch3 = TILED ? (size_t)P.gstride[3] : (size_t)h3 * w3;
     const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;

@@ -1,6 +1,6 @@
-// Pyramid lookup on the TILED volume layout (r = 4): warp-autonomous, persistent, cp.async-fed.
+// Pyramid lookup on the TILED volume layout (r = 3 or 4): warp-autonomous, persistent, cp.async-fed.
 //
-// Same result as lookup_fwd_kernel<4> (reference core/corr.py:29-50) on the TILED layout of
+// Same result as lookup_fwd_kernel<R> (reference core/corr.py:29-50) on the TILED layout of
 // include/raftcorr.h: every row p of a level is cut into tiles of 2 rows x 8 floats (64 B, the
 // plane padded with zeros to an even height and a multiple-of-8 width), the tiles of 32 consecutive
 // query pixels are interleaved, and each pixel's four 16 B chunks sit at swizzled positions:

@@ -903,3 +903,43 @@ def test_lookup_on_tiled_layout(rr, geom, kind, radius):
     rc = lib.rc_corr_lookup_tiled_fwd(_lib.ptr_array([x.data_ptr() for x in tiles]), coords.data_ptr(), out.data_ptr(),
                                       B, h, w, L, 5, torch.cuda.current_stream().cuda_stream)
     assert rc == 3 and b"radius" in lib.rc_last_error()
+
+
+# ----------------------------------------------------------------------------- documented build-time / run-time knobs
+def test_single_cta_build_variant_in_a_subprocess(rr):
+    """RAFT_CORR_TC_CTAS=1 selects the single-CTA (cta_group::1) instantiations of the tensor-core build: other
+    TMA boxes, barrier counts and commit paths than the default CTA pairs.  The variable is read once per process,
+    so the golden, ragged tiled and fp16-volume build / lookup cases are re-run in a child process with it set."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RAFT_CORR_TC_CTAS="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-x", "-q", "-m", "gpu",
+                        "-k", "golden_build or test_build_vs_oracle or tiled_build_equals_row_build or vol16_build_and_lookup",
+                        "-p", "no:cacheprovider"], capture_output=True, text=True, env=env, cwd=root, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout and "failed" not in r.stdout
+
+
+def test_pdl_off_gives_the_same_results(rr):
+    """RAFT_CORR_PDL=0 launches every kernel without programmatic dependent launch; a child process with it set
+    re-runs a build + lookup parity slice (the variable is read once per process)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RAFT_CORR_PDL="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-x", "-q", "-m", "gpu",
+                        "-k", "corrblock_random_geometries or lookup_on_tiled_layout", "-p", "no:cacheprovider"],
+                       capture_output=True, text=True, env=env, cwd=root, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_corrblock_refuses_coords_that_want_a_gradient(rr):
+    f = torch.randn(1, 32, 16, 16, device=DEV)
+    c = rr.coords_grid(1, 16, 16, DEV).requires_grad_(True)
+    for blk in (rr.CorrBlock(f, f), rr.CorrBlock(f.clone().requires_grad_(True), f)):
+        with pytest.raises(RuntimeError, match="coords"):
+            blk(c)
+        with torch.no_grad():
+            assert blk(c).shape == (1, 324, 16, 16)
+        assert blk(c.detach()).shape == (1, 324, 16, 16)

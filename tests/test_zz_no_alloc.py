@@ -77,17 +77,18 @@ def test_noalloc_matches_workspace_entry_point_twice_in_a_row(L):
         ((1, 256, 55, 128), 4, "bf16x3"),   # the 440x1024 geometry: 14.4 MB of the 32 MiB
         ((2, 96, 23, 39), 3, "bf16"),       # smaller, ragged, other precision, right after
     ]
-    first = True
+    # The documented warm-up (include/raftcorr.h): one small call per device and per precision before the phase in
+    # which nothing may allocate -- the first call resolves the scratch address, and the first launch of each
+    # kernel variant lets the runtime's lazy loader bring the code in.  Only this entry point is used for it, so a
+    # host that never calls the workspace entry point is what is being measured.
+    w1 = torch.randn(1, 64, 16, 16, generator=g).to(DEV)
+    for prec in ("bf16x3", "bf16"):
+        _build_noalloc(L, w1, w1, 2, prec)
     for shape, nl, prec in calls:
         f1 = torch.randn(*shape, generator=g).to(DEV)
         f2 = torch.randn(*shape, generator=g).to(DEV)
+        got, grew = _build_noalloc(L, f1, f2, nl, prec)  # measured before the workspace entry point runs at all
         want = _build_with_workspace(L, f1, f2, nl, prec)
-        if first:
-            # the first call on a device also resolves the scratch address (module data may be
-            # made resident then); memory is accounted from the calls after it
-            _build_noalloc(L, f1, f2, nl, prec)
-            first = False
-        got, grew = _build_noalloc(L, f1, f2, nl, prec)
         assert grew == 0, f"device memory in use grew by {grew} bytes across the call"
         for l in range(nl):
             assert torch.isfinite(got[l]).all(), (shape, l)
