@@ -167,6 +167,31 @@ int rc_corr_relayout_level(const float *src, float *dst, int B, int N, int hl, i
                            void *stream);
 
 /*
+ * Producer-side fusion: the feature encoder's output layer, the 1x1 convolution `conv2` of
+ * BasicEncoder / SmallEncoder (core/extractor.py:144,184 -- 128 -> 256; :217,256 -- 96 -> 128), writing
+ * its result directly as the K-major bf16 hi / lo operand maps the tensor-core build reads, so that
+ * the fp32 (B, 256, h, w) feature maps of core/raft.py:99-103 are never written and the build's own
+ * layout prepass never runs:
+ *     y[b, p, o] = bias[o] + sum_c weight[o, c] * x[b, c, p],   hi = bf16(y), lo = bf16(y - hi)
+ * (error-compensated bf16 products, fp32 accumulation: fp32-class, like RC_PREC_BF16X3).
+ *   x      : (Bt, Cin, H, W) fp32 NCHW, the input of conv2 (both images of the pairs: Bt = 2B when the
+ *            encoder runs them as one batch, core/raft.py:100); Cin a multiple of 16, <= 128
+ *   wprep  : weight (Cout, Cin) fp32 converted once per model by rc_fnet_conv1x1_prep_weight into
+ *            rc_fnet_conv1x1_weight_bytes() bytes; Cout a multiple of 64, <= 256
+ *   hi, lo : (Bt, H*W, Cout) bf16; lo may be NULL when only RC_PREC_BF16 / _VOL16 builds follow
+ * rc_corr_build_pyramid_tiled_prepared is rc_corr_build_pyramid_tiled on such maps (fmap1 = the first
+ * image's maps, fmap2 = the second's; D = Cout is also the channel pitch); no workspace is needed.
+ */
+size_t rc_fnet_conv1x1_weight_bytes(int Cout, int Cin);
+int rc_fnet_conv1x1_prep_weight(const float *weight, void *wprep, int Cout, int Cin, void *stream);
+int rc_fnet_conv1x1_prep(const float *x, const void *wprep, const float *bias, void *hi, void *lo, int Bt,
+                         int Cin, int Cout, int H, int W, void *stream);
+int rc_corr_build_pyramid_tiled_prepared(const void *fmap1_hi, const void *fmap1_lo, const void *fmap2_hi,
+                                         const void *fmap2_lo, int B, int D, int h, int w,
+                                         float *const *level_ptrs, int num_levels, int precision, float scale,
+                                         void *stream);
+
+/*
  * The 16-bit flavour of the tiled layout (RC_PREC_BF16_VOL16): the same structure with fp16
  * elements, tiles of 2 rows x 16 halves (still 64 B = 4 chunks of 16 B = 8 halves, chunk
  * k = 2*(y%2) + (x%16)/8), wp = w_l rounded up to 16:

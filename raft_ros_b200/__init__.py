@@ -4,10 +4,14 @@
     from raft_ros_b200 import alt_cuda_corr          # forward / backward, reference signatures
 
 Only the correlation path of the reference (core/corr.py, core/utils/utils.py:57-77,
-alt_cuda_corr/) lives here; everything else of RAFT stays the reference's own torch code.
+alt_cuda_corr/) lives here, plus the two fusions into its neighbours:
+`encoder_head` (the encoder's output 1x1 convolution emitting the build's operand maps) and
+`CorrBlock.lookup_convc1` (the lookup fused into the motion encoder's first convolution);
+everything else of RAFT stays the reference's own torch code.
 """
 from . import alt_cuda_corr  # noqa: F401
-from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION  # noqa: F401
+from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION, PreparedFeatures, encoder_head  # noqa: F401
 from .utils import bilinear_sampler, coords_grid  # noqa: F401
 
-__all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr"]
+__all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr", "encoder_head",
+           "PreparedFeatures"]

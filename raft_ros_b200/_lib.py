@@ -101,6 +101,10 @@ SIGNATURES = {
     "rc_corr_tile_group": (_i, []),
     "rc_corr_tiled_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
     "rc_corr_build_pyramid_tiled": (_i, [_vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp, _sz, _vp]),
+    "rc_corr_build_pyramid_tiled_prepared": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, ctypes.POINTER(_vp), _i, _i, _f, _vp]),
+    "rc_fnet_conv1x1_weight_bytes": (_sz, [_i, _i]),
+    "rc_fnet_conv1x1_prep_weight": (_i, [_vp, _vp, _i, _i, _vp]),
+    "rc_fnet_conv1x1_prep": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_relayout_level": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "rc_corr_tiled16_level_elems": (_i, [_i, _i, _i, _i, ctypes.POINTER(_sz)]),
     "rc_corr_lookup_tiled16_fwd": (_i, [ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -271,6 +271,74 @@ def build_bwd_raw(grad_levels: Sequence[torch.Tensor], fmap1: torch.Tensor, fmap
     return df1, df2
 
 
+class PreparedFeatures:
+    """Feature maps in the layout the tensor-core build reads: K-major bf16 `hi` (+ `lo` residual, x ~= hi + lo),
+    shaped (Bt, h, w, C) with C a multiple of 64.  Produced by `encoder_head`; consumed by `CorrBlock.from_prepared`."""
+
+    def __init__(self, hi, lo, h, w):
+        self.hi, self.lo, self.h, self.w = hi, lo, h, w
+
+    def __getitem__(self, sl):
+        return PreparedFeatures(self.hi[sl], None if self.lo is None else self.lo[sl], self.h, self.w)
+
+    @property
+    def batch(self):
+        return self.hi.shape[0]
+
+    @property
+    def channels(self):
+        return self.hi.shape[3]
+
+    def float(self):
+        """(Bt, C, h, w) fp32: hi + lo back in the reference's layout (tests, debugging)"""
+        v = self.hi.float() if self.lo is None else self.hi.float() + self.lo.float()
+        return v.permute(0, 3, 1, 2).contiguous()
+
+
+_HEAD_CACHE = {}
+
+
+def encoder_head(x, weight, bias, with_lo=True):
+    """The feature encoder's output layer -- `conv2`, a 1x1 convolution (reference core/extractor.py:144,184; small
+    :217,256) -- emitting the operand maps of the build directly (rc_fnet_conv1x1_prep): the fp32 (B, 256, h, w)
+    feature maps of core/raft.py:99-103 are never written and the build's layout prepass never runs.
+
+    x: (Bt, Cin, h, w) fp32, the input of conv2 (Bt = 2B when both images go through the encoder as one batch,
+    core/raft.py:100); weight: (Cout, Cin[, 1, 1]), bias: (Cout,).  Cin a multiple of 16 (<= 128), Cout a multiple of
+    64 (<= 256).  Error-compensated bf16 products with fp32 accumulation: fp32-class, like precision "bf16x3".
+    The converted weights are cached per (weight storage, version)."""
+    _require_cuda(x, "x")
+    _require_cuda(weight, "weight")
+    _require_cuda(bias, "bias")
+    if weight.dim() == 4 and weight.shape[2:] == (1, 1):
+        weight = weight[:, :, 0, 0]
+    if x.dim() != 4 or weight.dim() != 2 or weight.shape[1] != x.shape[1] or bias.shape != (weight.shape[0],):
+        raise RuntimeError(f"expected x (Bt,Cin,h,w), weight (Cout,Cin[,1,1]), bias (Cout,); got {tuple(x.shape)}, "
+                           f"{tuple(weight.shape)}, {tuple(bias.shape)}")
+    xs = _f32c(x)
+    Bt, Cin, h, w = xs.shape
+    Cout = weight.shape[0]
+    L = _lib.lib()
+    with torch.cuda.device(xs.device):
+        key = (weight.data_ptr(), weight._version, xs.device.index)
+        ent = _HEAD_CACHE.get(key)
+        if ent is None:
+            nbytes = int(L.rc_fnet_conv1x1_weight_bytes(Cout, Cin))
+            wp = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=xs.device)
+            w32 = _f32c(weight)
+            _lib.check(L.rc_fnet_conv1x1_prep_weight(w32.data_ptr(), wp.data_ptr(), Cout, Cin, _stream()), "rc_fnet_conv1x1_prep_weight")
+            if len(_HEAD_CACHE) > 8:
+                _HEAD_CACHE.clear()
+            ent = _HEAD_CACHE[key] = wp
+        b32 = _f32c(bias)
+        hi = torch.empty((Bt, h, w, Cout), dtype=torch.bfloat16, device=xs.device)
+        lo = torch.empty_like(hi) if with_lo else None
+        rc = L.rc_fnet_conv1x1_prep(xs.data_ptr(), ent.data_ptr(), b32.data_ptr(), hi.data_ptr(), lo.data_ptr() if with_lo else None,
+                                    Bt, Cin, Cout, h, w, _stream())
+        _lib.check(rc, "rc_fnet_conv1x1_prep")
+    return PreparedFeatures(hi, lo, h, w)
+
+
 # --------------------------------------------------------------------------- autograd
 class _GradState:
     """Per-CorrBlock bookkeeping of one backward pass.
@@ -496,6 +564,52 @@ class CorrBlock:
             # an assigned pyramid that is part of someone else's graph: generic differentiable path
             return _LookupFn.apply(coords, self.radius, *self._rows)
         return lookup_raw(self._rows, coords, self.radius)
+
+    @classmethod
+    def from_prepared(cls, prep1, prep2=None, num_levels=4, radius=4, precision=None):
+        """An inference CorrBlock from `encoder_head` output (rc_corr_build_pyramid_tiled_prepared): `prep1`, `prep2`
+        are the two images' PreparedFeatures; with `prep2` omitted, `prep1` holds both (first half = image 1, as the
+        encoder returns them for `fnet([image1, image2])`, core/raft.py:100).  Same object as CorrBlock(fmap1, fmap2)
+        otherwise; precision "bf16x3" needs the `lo` parts."""
+        if prep2 is None:
+            if prep1.batch % 2:
+                raise RuntimeError("from_prepared: one PreparedFeatures must hold an even number of images (2B)")
+            prep1, prep2 = prep1[:prep1.batch // 2], prep1[prep1.batch // 2:]
+        if prep1.hi.shape != prep2.hi.shape or prep1.hi.device != prep2.hi.device:
+            raise RuntimeError("from_prepared: the two images' maps must have one shape and device")
+        prec = _precision_code(precision)
+        if not _use_tiled(num_levels, radius, precision):
+            raise RuntimeError("from_prepared builds the tiled inference pyramid: radius 3 or 4, at most 4 levels, a tensor-core precision")
+        if prec == _lib.RC_PREC_BF16X3 and (prep1.lo is None or prep2.lo is None):
+            raise RuntimeError("precision 'bf16x3' needs the lo parts (encoder_head(..., with_lo=True))")
+        B, h, w, D = prep1.hi.shape
+        shapes = level_shapes(h, w, num_levels)
+        self = cls.__new__(cls)
+        self.num_levels, self.radius, self.precision = num_levels, radius, precision
+        self._state = self._token = self._rows = None
+        dev = prep1.hi.device
+        with torch.cuda.device(dev):
+            vol16 = prec == _lib.RC_PREC_BF16_VOL16
+            sizes = [tiled_level_elems(B, h * w, hl, wl, vol16) for hl, wl in shapes]
+            flat = torch.empty(sum(sizes), dtype=torch.float16 if vol16 else torch.float32, device=dev)
+            levels, o = [], 0
+            for s_ in sizes:
+                levels.append(flat[o:o + s_])
+                o += s_
+            ops = [prep1.hi, prep1.lo, prep2.hi, prep2.lo]
+            ops = [None if t is None else (t if t.is_contiguous() else t.contiguous()) for t in ops]
+            rc = _lib.lib().rc_corr_build_pyramid_tiled_prepared(
+                ops[0].data_ptr(), None if ops[1] is None else ops[1].data_ptr(), ops[2].data_ptr(),
+                None if ops[3] is None else ops[3].data_ptr(), B, D, h, w, _lib.ptr_array([lv.data_ptr() for lv in levels]),
+                num_levels, prec, 0.0, _stream())
+            _lib.check(rc, "rc_corr_build_pyramid_tiled_prepared")
+            for t in ops:
+                if t is not None:
+                    t.record_stream(torch.cuda.current_stream())
+        self._tiled = levels
+        self._geom = (B, h, w)
+        self._fast = _TiledLookup(self._tiled, B, h, w, radius)
+        return self
 
     def lookup_convc1(self, coords, weight, bias, operands="fp16"):
         """`F.relu(F.conv2d(self(coords), weight, bias))` in ONE launch (rc_corr_lookup_convc1_fwd): the lookup

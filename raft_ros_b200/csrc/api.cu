@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cmath>
 #include <cstdlib>
+#include <initializer_list>
 
 #include "common.cuh"
 
@@ -169,6 +170,59 @@ int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, i
   if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
   return launch_build_tc_tiled(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale, workspace,
                                workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int rc_corr_build_pyramid_tiled_prepared(const void *fmap1_hi, const void *fmap1_lo, const void *fmap2_hi,
+                                         const void *fmap2_lo, int B, int D, int h, int w, float *const *level_ptrs,
+                                         int num_levels, int precision, float scale, void *stream) {
+  const char *fn = "rc_corr_build_pyramid_tiled_prepared";
+  if (int rc = check_geometry(fn, B, h, w, num_levels)) return rc;
+  RC_CHECK_ARG(fmap1_hi && fmap2_hi && level_ptrs, "%s: null pointer", fn);
+  RC_CHECK_ARG(D > 0 && D % 64 == 0, "%s: the prepared maps have a channel pitch of D = %d, which must be a multiple of 64", fn, D);
+  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16 && precision != RC_PREC_BF16_VOL16) {
+    set_error("%s: only the tensor-core precisions write the tiled layout (got %d)", fn, precision);
+    return RC_ERR_UNSUPPORTED;
+  }
+  RC_CHECK_ARG(precision != RC_PREC_BF16X3 || (fmap1_lo && fmap2_lo), "%s: RC_PREC_BF16X3 needs the lo parts", fn);
+  for (const void *q : {fmap1_hi, fmap1_lo, fmap2_hi, fmap2_lo})
+    RC_CHECK_ARG((reinterpret_cast<uintptr_t>(q) & 127) == 0, "%s: operand maps must be 128-byte aligned", fn);
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; ++l) {
+    RC_CHECK_ARG(level_ptrs[l] != nullptr, "%s: level %d pointer is null", fn, l);
+    lv.p[l] = level_ptrs[l];
+  }
+  if (scale == 0.0f) scale = 1.0f / sqrtf((float)D);
+  return launch_build_tc_tiled_prepared(fmap1_hi, fmap1_lo, fmap2_hi, fmap2_lo, B, D, h, w, lv, num_levels, precision, scale,
+                                        static_cast<cudaStream_t>(stream));
+}
+
+size_t rc_fnet_conv1x1_weight_bytes(int Cout, int Cin) {
+  if (Cout <= 0 || Cin <= 0) return 0;
+  return conv1x1_weight_bytes(Cout, Cin);
+}
+
+static int check_conv1x1(const char *fn, int Cout, int Cin) {
+  RC_CHECK_ARG(Cout > 0 && Cout <= 256 && Cout % 64 == 0, "%s: Cout %d must be a multiple of 64, at most 256", fn, Cout);
+  RC_CHECK_ARG(Cin > 0 && Cin <= 128 && Cin % 16 == 0, "%s: Cin %d must be a multiple of 16, at most 128", fn, Cin);
+  return RC_OK;
+}
+
+int rc_fnet_conv1x1_prep_weight(const float *weight, void *wprep, int Cout, int Cin, void *stream) {
+  RC_CHECK_ARG(weight && wprep, "rc_fnet_conv1x1_prep_weight: null pointer");
+  if (int rc = check_conv1x1("rc_fnet_conv1x1_prep_weight", Cout, Cin)) return rc;
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_fnet_conv1x1_prep_weight: wprep must be 128-byte aligned");
+  return launch_conv1x1_prep_weight(weight, wprep, Cout, Cin, static_cast<cudaStream_t>(stream));
+}
+
+int rc_fnet_conv1x1_prep(const float *x, const void *wprep, const float *bias, void *hi, void *lo, int Bt, int Cin, int Cout,
+                         int H, int W, void *stream) {
+  RC_CHECK_ARG(x && wprep && bias && hi, "rc_fnet_conv1x1_prep: null pointer");
+  RC_CHECK_ARG(Bt > 0 && H > 0 && W > 0 && (long long)Bt * ((long long)H * W / 128 + 1) < 0x7fffffffLL, "rc_fnet_conv1x1_prep: bad sizes");
+  if (int rc = check_conv1x1("rc_fnet_conv1x1_prep", Cout, Cin)) return rc;
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0 && (reinterpret_cast<uintptr_t>(hi) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(lo) & 15) == 0,
+               "rc_fnet_conv1x1_prep: wprep must be 128-byte aligned, hi / lo 16-byte aligned");
+  return launch_conv1x1_prep(x, wprep, bias, hi, lo, Bt, Cin, Cout, H * W, static_cast<cudaStream_t>(stream));
 }
 
 int rc_corr_tiled16_level_elems(int B, int h, int w, int level, size_t *elems) {

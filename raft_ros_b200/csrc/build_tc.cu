@@ -665,6 +665,10 @@ size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision) {
   return aligned * 2 * (precision == RC_PREC_BF16X3 ? 2 : 1);
 }
 
+static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
+                               int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
+                               bool tiled);
+
 static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv,
                                 int L, int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st,
                                 bool tiled) {
@@ -697,6 +701,19 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
     dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
     RC_CUDA(launch_pdl(prep_kernel, grid, dim3(256), 0, st, f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0));
   }
+  return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled);
+}
+
+// The tensor-core build proper, on operands already in the K-major bf16 hi (/ lo) layout (B, h*w, Dp): what the
+// layout prepass above writes, and what rc_fnet_conv1x1_prep (fnet_head.cu) emits straight from the encoder.
+static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
+                               int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
+                               bool tiled) {
+  using namespace tc;
+  const int N = h * w;
+  const bool x3 = precision == RC_PREC_BF16X3;
+  const bool v16 = precision == RC_PREC_BF16_VOL16;
+  const int ncta = tc::ctas_per_tile();
 
   CUtensorMap tmAh, tmAl, tmBh, tmBl;
   {
@@ -767,6 +784,14 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   if (rc) return rc;
   if (L > 4) return launch_pool_tail(lv, B, h, w, 4, L, st);
   return RC_OK;
+}
+
+int launch_build_tc_tiled_prepared(const void *a_hi, const void *a_lo, const void *b_hi, const void *b_lo, int B, int Dp, int h,
+                                   int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st) {
+  auto p = [](const void *q) { return static_cast<__nv_bfloat16 *>(const_cast<void *>(q)); };
+  const bool x3 = precision == RC_PREC_BF16X3;
+  return build_from_operands(p(a_hi), x3 ? p(a_lo) : p(a_hi), p(b_hi), x3 ? p(b_lo) : p(b_hi), B, Dp, h, w, lv, L, precision, scale,
+                             st, true);
 }
 
 int launch_build_tc(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv, int L,

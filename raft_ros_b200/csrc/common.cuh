@@ -73,6 +73,12 @@ int launch_build_tc_noalloc(const float *f1, const float *f2, int B, int D, int 
 int launch_build_tc_tiled(const float *f1, const float *f2, int B, int D, int h, int w,
                           const LevelPtrs &lv, int L, int precision, float scale, void *ws,
                           size_t ws_bytes, cudaStream_t st);
+int launch_build_tc_tiled_prepared(const void *a_hi, const void *a_lo, const void *b_hi, const void *b_lo, int B, int Dp, int h,
+                                   int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st);
+size_t conv1x1_weight_bytes(int Cout, int Cin);
+int launch_conv1x1_prep_weight(const float *w, void *wp, int Cout, int Cin, cudaStream_t st);
+int launch_conv1x1_prep(const float *x, const void *wp, const float *bias, void *hi, void *lo, int Bt, int Cin, int Cout, int HW,
+                        cudaStream_t st);
 int launch_relayout(const float *src, float *dst, int B, int N, int hl, int wl, bool to_tiled,
                     cudaStream_t st);
 int launch_relayout16(const void *src, void *dst, int B, int N, int hl, int wl, bool to_tiled,

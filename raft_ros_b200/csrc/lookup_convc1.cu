@@ -16,14 +16,19 @@
 // no tensor-core equivalent in one pass; this entry point is a stated-bounds fast path next to
 // rc_corr_lookup_tiled_fwd, not a replacement for it.
 //
-// One CTA per SM, persistent over tiles of 128 consecutive query pixels of one frame pair, 14 warps:
-//   warps 0-7   gather: warp g owns pixels 16g .. 16g+15 of the tile, as two work items of 8 pixels per
-//               level (lane = pixel x quarter, cp.async ring of two patch buffers, separable bilinear
-//               taps from registers -- the lookup kernel's item), taps -> A[level parity] in shared memory
-//   warps 8-11  epilogue: thread <-> pixel, tcgen05.ld 32 output channels at a time, bias, ReLU,
+// One CTA per SM, persistent over tiles of 128 consecutive query pixels of one frame pair, 22 warps:
+//   warps 0-15  gather: warp g owns pixels 8g .. 8g+7 of the tile, one work item per level (lane = pixel x
+//               quarter, cp.async patch buffer, separable bilinear taps from registers -- the lookup kernel's
+//               item), taps -> A[level parity] in shared memory.  Sixteen warps with one buffer each rather
+//               than eight with two: the item is bound by instruction latency, which more warps hide.
+//   warps 16-19 epilogue: thread <-> pixel, tcgen05.ld 32 output channels at a time, bias, ReLU,
 //               one coalesced 128 B store per channel and warp
-//   warp 12     TMA producer of the weight blocks ([Cout][64] 16-bit, SWIZZLE_128B, from L2)
-//   warp 13     MMA issuer (tcgen05.mma kind::f16, 128 x Cout x 16), TMEM owner
+//   warp 20     TMA producer of the weight blocks ([Cout][64] 16-bit, SWIZZLE_128B, from L2)
+//   warp 21     MMA issuer (tcgen05.mma kind::f16, 128 x Cout x 16), TMEM owner
+// K order inside a level: the quarter-lane that forms a tap also fixes its K index (slot t of quarter q sits
+// in chunk (SLOTS/8)*q + t/8, SLOTS = 24 for r = 4, 16 for r = 3; rc_corr_convc1_prep_weight lays the weights
+// out the same way), so a tap's shared-memory address is the sum of two per-lane registers and two neighbouring
+// taps leave as one packed 32-bit store.
 // TMEM holds two accumulators (2 x 256 columns): the epilogue of tile t overlaps tile t+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -39,14 +44,14 @@ namespace fc {
 
 using namespace tc;
 
-constexpr int kGatherWarps = 8, kEpiWarps = 4;
-constexpr int kProducerWarp = 12, kMmaWarp = 13, kThreads = 14 * 32;
+constexpr int kGatherWarps = 16, kEpiWarps = 4;
+constexpr int kProducerWarp = 20, kMmaWarp = 21, kThreads = 22 * 32;
 constexpr int TMPIX = 128;                         // query pixels per tile (TMEM lanes)
 constexpr int kPix = 8;                            // query pixels per gather item
 constexpr int PS = 16;                             // patch row stride (floats): the 16 fetched columns
 constexpr int kPatch = 10 * PS + 12;               // per-pixel patch (floats); the pad spreads the banks
 constexpr int kStageFloats = kPix * kPatch;
-constexpr int kStages = 2;
+constexpr int kStages = 1;
 constexpr int A_KBLOCK = TMPIX * 64 * 2;           // one 64-wide K block of the tap operand: 16 KB
 constexpr int A_BYTES = 2 * A_KBLOCK;              // taps of one level: K padded to 128
 constexpr int W_BLOCK = 256 * 64 * 2;              // one weight block: up to 256 rows x 64 K
@@ -123,162 +128,155 @@ lookup_convc1_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < kGatherWarps) {
-    // ===================== gather: taps of 16 pixels per level -> A =====================
+    // ===================== gather: taps of this warp's 8 pixels, level by level -> A =====================
     const int tu = lane >> 2, tc = lane & 3;
-    float *ring = gather + warp * (kStages * kStageFloats);
-    const uint32_t ring_u32 = smem_u32(ring);
+    float *patchbuf = gather + warp * kStageFloats;
+    const uint32_t patch_u32 = smem_u32(patchbuf);
     const uint32_t dst_lane = (uint32_t)(tu * kPatch + tc * 4) * 4u;
-
-    // fetch stream (runs one item ahead of the consume stream): tile, level, sub-item
-    int f_tile = blockIdx.x, f_l = 0, f_s = 0;
-    float cx[2] = {0.f, 0.f}, cy[2] = {0.f, 0.f};
-    auto load_coords = [&](int tile) {
-      if (tile < P.total_tiles) {
-        const int b = tile / P.tiles_per_b, p0 = (tile - b * P.tiles_per_b) * TMPIX + warp * 16;
+    // operand row of this lane's pixel: K-major, 128 B rows, 16 B chunk c at position c ^ (row & 7).  This lane's
+    // taps are slots 0 .. SLOTS-1 of quarter tc, i.e. K = SLOTS*tc + t: chunk (SLOTS/8)*tc + (t >> 3), a constant
+    // offset (t & 7) inside it.
+    constexpr int SLOTS = KSTEPS * 4;  // 24 (r = 4), 16 (r = 3)
+    constexpr int NCH = SLOTS / 8;     // chunks per quarter: 3, 2
+    const int row = warp * 8 + tu, rx = row & 7;
+    uint32_t chunk_off[NCH];           // byte offset of this lane's chunks inside an A buffer
 #pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          const int p = p0 + 8 * s + tu;
-          cx[s] = p < N ? __ldg(P.coords + ((size_t)b * 2 + 0) * N + p) : 0.f;
-          cy[s] = p < N ? __ldg(P.coords + ((size_t)b * 2 + 1) * N + p) : 0.f;
-        }
-      }
-    };
-    auto next_ctx = [&]() {
-      Ctx c{f_l, 0, 0, f_tile < P.total_tiles ? 1 : 0, 0, -(1 << 28), 0.f, 0.f};
-      if (c.valid) {
-        c.b = f_tile / P.tiles_per_b;
-        c.p0 = (f_tile - c.b * P.tiles_per_b) * TMPIX + warp * 16 + 8 * f_s;
-        if (c.p0 + tu < N) {
-          const float inv = 1.0f / (float)(1 << f_l);
-          c.x0 = safe_floor_int((f_s ? cx[1] : cx[0]) * inv, &c.fx) - R;
-          c.y0 = safe_floor_int((f_s ? cy[1] : cy[0]) * inv, &c.fy) - R;
-        }
-      }
-      if (++f_s == 2) {
-        f_s = 0;
-        if (++f_l == L) {
-          f_l = 0;
-          f_tile += gridDim.x;
-          load_coords(f_tile);
-        }
-      }
-      return c;
+    for (int m = 0; m < NCH; ++m) {
+      const int ch = NCH * tc + m;
+      chunk_off[m] = (uint32_t)((ch >> 3) * A_KBLOCK + (row >> 3) * 1024 + rx * 128 + (((ch & 7) ^ rx) << 4));
+    }
+    // inside its chunk, quarter tc keeps slot t at element (t + 2 tc) & 7: the four quarters of a pixel then hit
+    // four different 32-bit words with the same store instruction, and the 32 lanes 32 different banks
+    uint32_t word_off[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) word_off[q] = (uint32_t)(((q + tc) & 3) << 2);
+    auto pack2 = [](float a, float b) -> uint32_t {  // a -> low half (K even), b -> high half
+      uint32_t r;
+      if constexpr (BF16OPS) asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+      else asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+      return r;
     };
     auto copy16 = [&](uint32_t dst, const float *src, bool ok) {
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
     };
     // the lookup kernel's copy issue (lookup_tiled.cu): lane (u, k) fetches the k-th 16 B piece of the PN
     // window rows of pixel u, zero-filled outside the level
-    auto issue = [&](const Ctx &c, int stage) {
-      if (c.valid) {
-        const int hl = P.h >> c.lvl, wl = P.w >> c.lvl;
-        constexpr int CW = V16 ? 16 : 8, PC = V16 ? 8 : 4;
-        const int hp = (hl + 1) & ~1, wp = (wl + CW - 1) & ~(CW - 1), tpr = wp / CW;
-        const int wb = (wl + PC - 1) & ~(PC - 1);
-        const int cg = (c.x0 & ~(PC - 1)) + PC * tc;
-        const bool want = PC * tc < (c.x0 & (PC - 1)) + PN;
-        const bool okx = want && (unsigned)cg < (unsigned)wb;
-        constexpr int G = kTileGroup;
-        const int ng = (N + G - 1) / G;
-        const size_t grp = (size_t)c.b * ng + c.p0 / G;
-        const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg / PC) & 1;
-        const size_t gwords = (size_t)(hp * wp) * G / (V16 ? 2 : 1);
-        const float *base = pick_level(P.lv, c.lvl) + grp * gwords + ((cg / CW) * (16 * G) + u * 16);
-        const int trs = tpr * 16 * G;
-        const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);
-        constexpr uint32_t RB = V16 ? 48u : (uint32_t)PS * 4u;
-        const uint32_t dst = ring_u32 + (uint32_t)(stage * kStageFloats) * 4u + dst_lane;
+    auto issue = [&](const Ctx &c) {
+      const int hl = P.h >> c.lvl, wl = P.w >> c.lvl;
+      constexpr int CW = V16 ? 16 : 8, PC = V16 ? 8 : 4;
+      const int hp = (hl + 1) & ~1, wp = (wl + CW - 1) & ~(CW - 1), tpr = wp / CW;
+      const int wb = (wl + PC - 1) & ~(PC - 1);
+      const int cg = (c.x0 & ~(PC - 1)) + PC * tc;
+      const bool want = PC * tc < (c.x0 & (PC - 1)) + PN;
+      const bool okx = want && (unsigned)cg < (unsigned)wb;
+      constexpr int G = kTileGroup;
+      const int ng = (N + G - 1) / G;
+      const size_t grp = (size_t)c.b * ng + c.p0 / G;
+      const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg / PC) & 1;
+      const size_t gwords = (size_t)(hp * wp) * G / (V16 ? 2 : 1);
+      const float *base = pick_level(P.lv, c.lvl) + grp * gwords + ((cg / CW) * (16 * G) + u * 16);
+      const int trs = tpr * 16 * G;
+      const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);
+      constexpr uint32_t RB = V16 ? 48u : (uint32_t)PS * 4u;
+      const uint32_t dst = patch_u32 + dst_lane;
 #pragma unroll
-        for (int r = 0; r < PN; ++r) {
-          const int ya = c.y0 + r;
-          const bool ok = okx && (unsigned)ya < (unsigned)hl;
-          const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
-          if (!V16 || tc < 3) copy16(dst + (uint32_t)r * RB, ok ? base + off : pick_level(P.lv, 0), ok);
-        }
+      for (int r = 0; r < PN; ++r) {
+        const int ya = c.y0 + r;
+        const bool ok = okx && (unsigned)ya < (unsigned)hl;
+        const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
+        if (!V16 || tc < 3) copy16(dst + (uint32_t)r * RB, ok ? base + off : pick_level(P.lv, 0), ok);
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    auto cvt16 = [](float v) -> unsigned short {
-      if constexpr (BF16OPS) return __bfloat16_as_ushort(__float2bfloat16_rn(v));
-      else {
-        unsigned short r;
-        asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
-        return r;
+
+    uint32_t cnt = 0;  // levels done: A buffer = cnt & 1
+    float ncx = 0.f, ncy = 0.f;  // coordinates of the next tile's pixel, loaded a tile ahead
+    auto load_coords = [&](int tile, float &x, float &y) {
+      x = 0.f;
+      y = 0.f;
+      if (tile < P.total_tiles) {
+        const int b = tile / P.tiles_per_b, p = (tile - b * P.tiles_per_b) * TMPIX + warp * 8 + tu;
+        if (p < N) {
+          x = __ldg(P.coords + ((size_t)b * 2 + 0) * N + p);
+          y = __ldg(P.coords + ((size_t)b * 2 + 1) * N + p);
+        }
       }
     };
-
-    load_coords(f_tile);
-    Ctx cur = next_ctx();
-    issue(cur, 0);
-    int stage = 0;
-    uint32_t cnt = 0;  // levels done: A buffer = cnt & 1
+    load_coords(blockIdx.x, ncx, ncy);
     for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+      const float cx = ncx, cy = ncy;
+      load_coords(tile + gridDim.x, ncx, ncy);
+      const int b = tile / P.tiles_per_b, p0 = (tile - b * P.tiles_per_b) * TMPIX + warp * 8;
+      const bool pv = p0 + tu < N;
       for (int l = 0; l < L; ++l, ++cnt) {
+        Ctx cur{l, b, p0, 1, 0, -(1 << 28), 0.f, 0.f};
+        if (pv) {
+          const float inv = 1.0f / (float)(1 << l);
+          cur.x0 = safe_floor_int(cx * inv, &cur.fx) - R;
+          cur.y0 = safe_floor_int(cy * inv, &cur.fy) - R;
+        }
+        issue(cur);
         const uint32_t buf = cnt & 1;
         mbar_wait(&a_empty[buf], ((cnt >> 1) & 1) ^ 1);  // the MMAs that read this buffer two levels ago are done
         const uint32_t a_buf = a_u32 + buf * A_BYTES;
-#pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
-          const Ctx nn = next_ctx();
-          issue(nn, stage ^ 1);
-          asm volatile("cp.async.wait_group 1;" ::: "memory");
-          __syncwarp();
-          const float dx = cur.fx, dy = cur.fy, ex = 1.0f - dx, ey = 1.0f - dy;
-          const float *pbase = ring + stage * kStageFloats + tu * kPatch;
-          auto at = [&](int j, int i) -> float {
-            if constexpr (V16) return __half2float(reinterpret_cast<const __half *>(pbase)[j * 24 + (cur.x0 & 7) + i]);
-            else return pbase[j * PS + (cur.x0 & 3) + i];
-          };
-          // operand row of this lane's pixel: K-major, 128 B rows, 16 B chunk c at position c ^ (row & 7)
-          const int row = warp * 16 + 8 * s + tu;
-          const uint32_t rbase = a_buf + (uint32_t)((row >> 3) * 1024 + (row & 7) * 128);
-          const int rx = row & 7;
-          auto put = [&](int k, float v) {
-            sts16(rbase + (uint32_t)((k >> 6) * A_KBLOCK + (((((k & 63) >> 3) ^ rx)) << 4) + ((k & 7) << 1)), cvt16(v));
-          };
-          if (tc < RD / 2) {
-            float h0[PN], h1[PN];
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        const float dx = cur.fx, dy = cur.fy, ex = 1.0f - dx, ey = 1.0f - dy;
+        const float *pbase = patchbuf + tu * kPatch;
+        auto at = [&](int j, int i) -> float {
+          if constexpr (V16) return __half2float(reinterpret_cast<const __half *>(pbase)[j * 24 + (cur.x0 & 7) + i]);
+          else return pbase[j * PS + (cur.x0 & 3) + i];
+        };
+        float tap[SLOTS];  // this lane's taps in slot order; unused slots stay zero
 #pragma unroll
-            for (int j = 0; j < PN; ++j) {
-              const float a = at(j, 2 * tc), b = at(j, 2 * tc + 1), d = at(j, 2 * tc + 2);
-              h0[j] = fmaf(b, dx, a * ex);
-              h1[j] = fmaf(d, dx, b * ex);
-            }
-            const int k0 = 2 * tc * RD;
+        for (int t = 0; t < SLOTS; ++t) tap[t] = 0.0f;
+        if (tc < RD / 2) {
+          // slots 0 .. RD-1: window column 2tc, slots RD .. 2RD-1: column 2tc+1 (both with j = 0 .. RD-1)
+          float h0[PN], h1[PN];
 #pragma unroll
-            for (int j = 0; j < RD; ++j) {
-              put(k0 + j, fmaf(h0[j + 1], dy, h0[j] * ey));
-              put(k0 + RD + j, fmaf(h1[j + 1], dy, h1[j] * ey));
-            }
+          for (int j = 0; j < PN; ++j) {
+            const float a = at(j, 2 * tc), bb = at(j, 2 * tc + 1), d = at(j, 2 * tc + 2);
+            h0[j] = fmaf(bb, dx, a * ex);
+            h1[j] = fmaf(d, dx, bb * ex);
           }
-          if constexpr (R == 4) {
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-              const int j = tc + 4 * k;
-              if (j < RD && (k < 2 || tc == 0)) {
-                const float a = at(j, 8), b = at(j, 9), c2 = at(j + 1, 8), d2 = at(j + 1, 9);
-                const float top = fmaf(b, dx, a * ex), bot = fmaf(d2, dx, c2 * ex);
-                put(8 * RD + j, fmaf(bot, dy, top * ey));
-              }
-            }
-          } else if (tc == RD / 2) {
-            float hc[PN];
-#pragma unroll
-            for (int j = 0; j < PN; ++j) hc[j] = fmaf(at(j, RD), dx, at(j, RD - 1) * ex);
-#pragma unroll
-            for (int j = 0; j < RD; ++j) put((RD - 1) * RD + j, fmaf(hc[j + 1], dy, hc[j] * ey));
+          for (int j = 0; j < RD; ++j) {
+            tap[j] = fmaf(h0[j + 1], dy, h0[j] * ey);
+            tap[RD + j] = fmaf(h1[j + 1], dy, h1[j] * ey);
           }
-          __syncwarp();
-          stage ^= 1;
-          cur = nn;
         }
-        // this warp's 16 rows of the level are in place: make them visible to the tensor-core (async) proxy
+        if constexpr (R == 4) {
+          // window column 8, rows shared out over the quarters: quarter tc takes j = tc, tc+4 (and 8 for tc = 0) as
+          // slots 18, 19, 20
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            const int j = tc + 4 * k;
+            if (j < RD && (k < 2 || tc == 0)) {
+              const float a = at(j, 8), bb = at(j, 9), c2 = at(j + 1, 8), d2 = at(j + 1, 9);
+              const float top = fmaf(bb, dx, a * ex), bot = fmaf(d2, dx, c2 * ex);
+              tap[2 * RD + k] = fmaf(bot, dy, top * ey);
+            }
+          }
+        } else if (tc == RD / 2) {
+          // r = 3: the fourth quarter owns the last column (6) on its own: slots 0 .. 6
+          float hc[PN];
+#pragma unroll
+          for (int j = 0; j < PN; ++j) hc[j] = fmaf(at(j, RD), dx, at(j, RD - 1) * ex);
+#pragma unroll
+          for (int j = 0; j < RD; ++j) tap[j] = fmaf(hc[j + 1], dy, hc[j] * ey);
+        }
+        // pairs of slots leave as one 32-bit store; slots a quarter never fills are left alone (they are zero)
+        constexpr int USED = (R == 4) ? 22 : 14;  // rounded up to even
+#pragma unroll
+        for (int t = 0; t < USED; t += 2)
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a_buf + chunk_off[t >> 3] + word_off[(t & 7) >> 1]), "r"(pack2(tap[t], tap[t + 1]))
+                       : "memory");
+        // this warp's 8 rows of the level are in place: make them visible to the tensor-core (async) proxy
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_full[buf]);
       }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
   } else if (warp < kGatherWarps + kEpiWarps) {
     // ===================== epilogue: bias + ReLU, thread <-> pixel =====================
     const int e = warp - kGatherWarps;  // = warp % 4: the TMEM lane quarter this warp may read
@@ -372,18 +370,45 @@ lookup_convc1_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 }
 
-// weights (Cout, L*(2r+1)^2) fp32 -> (Cout, L*KP) 16-bit, K of every level padded with zeros to KP
+// weights (Cout, L*(2r+1)^2) fp32 -> (Cout, L*KP) 16-bit in the kernel's K order: inside a level, slot t of quarter q
+// (K = SLOTS*q + 8*(t/8) + (t + 2q) % 8) holds the tap that quarter-lane q forms as its t-th (see the gather above);
+// unused slots are zero.
+//   r = 4 (SLOTS 24): q = 0..3: t < 9 -> tap (i = 2q, j = t); t < 18 -> (2q+1, t-9); t = 18, 19 -> (8, q), (8, q+4);
+//                     q = 0 also t = 20 -> (8, 8)
+//   r = 3 (SLOTS 16): q = 0..2: t < 7 -> (2q, t); t < 14 -> (2q+1, t-7); q = 3: t < 7 -> (6, t)
+// tap (i, j) is input channel i*(2r+1) + j of the level (i = x offset, j = y offset).
+__device__ __forceinline__ int slot_tap(int r, int q, int t) {
+  const int rd = 2 * r + 1;
+  if (r == 4) {
+    if (t < 9) return (2 * q) * rd + t;
+    if (t < 18) return (2 * q + 1) * rd + (t - 9);
+    if (t == 18) return 8 * rd + q;
+    if (t == 19) return 8 * rd + q + 4;
+    if (t == 20 && q == 0) return 8 * rd + 8;
+    return -1;
+  }
+  if (q < 3) {
+    if (t < 7) return (2 * q) * rd + t;
+    if (t < 14) return (2 * q + 1) * rd + (t - 7);
+    return -1;
+  }
+  return t < 7 ? 6 * rd + t : -1;
+}
+
 template <bool BF16OPS>
 __global__ void convc1_prep_weight_kernel(const float *__restrict__ w, unsigned short *__restrict__ wp, int Cout, int L,
-                                          int ntap, int KP) {
-  const int total = Cout * L * KP;
+                                          int r, int KP) {
+  const int total = Cout * L * KP, ntap = (2 * r + 1) * (2 * r + 1), slots = (r == 4) ? 24 : 16;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int o = i / (L * KP), rem = i - o * (L * KP), l = rem / KP, t = rem - l * KP;
-    const float v = t < ntap ? __ldg(w + (size_t)o * (L * ntap) + l * ntap + t) : 0.0f;
-    unsigned short r;
-    if (BF16OPS) r = __bfloat16_as_ushort(__float2bfloat16_rn(v));
-    else asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
-    wp[i] = r;
+    const int o = i / (L * KP), rem = i - o * (L * KP), l = rem / KP, k = rem - l * KP;
+    const int q = k / slots, kk = k - q * slots;
+    const int t = (kk & ~7) | ((kk - 2 * q) & 7);  // element (t + 2q) & 7 of its chunk holds slot t (bank spreading, see the gather)
+    const int tap = q < 4 ? slot_tap(r, q, t) : -1;
+    const float v = tap >= 0 ? __ldg(w + (size_t)o * (L * ntap) + l * ntap + tap) : 0.0f;
+    unsigned short rr;
+    if (BF16OPS) rr = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+    else asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(rr) : "f"(v));
+    wp[i] = rr;
   }
 }
 
@@ -422,11 +447,11 @@ static int launch_t(const CUtensorMap &tm, const Params &P, cudaStream_t st) {
 size_t convc1_weight_bytes(int Cout, int L, int r) { return (size_t)Cout * L * fc::kp_of(r) * 2; }
 
 int launch_convc1_prep_weight(const float *w, void *wp, int Cout, int L, int r, int bf16_ops, cudaStream_t st) {
-  const int ntap = (2 * r + 1) * (2 * r + 1), KP = fc::kp_of(r);
+  const int KP = fc::kp_of(r);
   const int total = Cout * L * KP;
   const int blocks = (total + 255) / 256;
-  if (bf16_ops) fc::convc1_prep_weight_kernel<true><<<blocks, 256, 0, st>>>(w, static_cast<unsigned short *>(wp), Cout, L, ntap, KP);
-  else fc::convc1_prep_weight_kernel<false><<<blocks, 256, 0, st>>>(w, static_cast<unsigned short *>(wp), Cout, L, ntap, KP);
+  if (bf16_ops) fc::convc1_prep_weight_kernel<true><<<blocks, 256, 0, st>>>(w, static_cast<unsigned short *>(wp), Cout, L, r, KP);
+  else fc::convc1_prep_weight_kernel<false><<<blocks, 256, 0, st>>>(w, static_cast<unsigned short *>(wp), Cout, L, r, KP);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
 }
