@@ -295,7 +295,27 @@ class PreparedFeatures:
         return v.permute(0, 3, 1, 2).contiguous()
 
 
-_HEAD_CACHE = {}
+class _WeightCache:
+    """Converted weights per weight TENSOR OBJECT (weak: the entry dies with the tensor) and variant; an in-place
+    update of the tensor (its `_version` moves) re-converts.  Never keyed on data_ptr: a freed tensor's address is
+    handed out again."""
+
+    def __init__(self):
+        import weakref
+        self._d = weakref.WeakKeyDictionary()
+
+    def get(self, weight, variant, make):
+        per = self._d.get(weight)
+        if per is None:
+            per = self._d[weight] = {}
+        ent = per.get(variant)
+        if ent is None or ent[0] != weight._version:
+            ent = per[variant] = (weight._version, make())
+        return ent[1]
+
+
+_HEAD_CACHE = _WeightCache()
+_CONVC1_CACHE = _WeightCache()
 
 
 def encoder_head(x, weight, bias, with_lo=True):
@@ -306,10 +326,11 @@ def encoder_head(x, weight, bias, with_lo=True):
     x: (Bt, Cin, h, w) fp32, the input of conv2 (Bt = 2B when both images go through the encoder as one batch,
     core/raft.py:100); weight: (Cout, Cin[, 1, 1]), bias: (Cout,).  Cin a multiple of 16 (<= 128), Cout a multiple of
     64 (<= 256).  Error-compensated bf16 products with fp32 accumulation: fp32-class, like precision "bf16x3".
-    The converted weights are cached per (weight storage, version)."""
+    The converted weights are cached per weight tensor object (and its version)."""
     _require_cuda(x, "x")
     _require_cuda(weight, "weight")
     _require_cuda(bias, "bias")
+    weight_obj = weight
     if weight.dim() == 4 and weight.shape[2:] == (1, 1):
         weight = weight[:, :, 0, 0]
     if x.dim() != 4 or weight.dim() != 2 or weight.shape[1] != x.shape[1] or bias.shape != (weight.shape[0],):
@@ -320,16 +341,14 @@ def encoder_head(x, weight, bias, with_lo=True):
     Cout = weight.shape[0]
     L = _lib.lib()
     with torch.cuda.device(xs.device):
-        key = (weight.data_ptr(), weight._version, xs.device.index)
-        ent = _HEAD_CACHE.get(key)
-        if ent is None:
+        def make():
             nbytes = int(L.rc_fnet_conv1x1_weight_bytes(Cout, Cin))
             wp = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=xs.device)
             w32 = _f32c(weight)
             _lib.check(L.rc_fnet_conv1x1_prep_weight(w32.data_ptr(), wp.data_ptr(), Cout, Cin, _stream()), "rc_fnet_conv1x1_prep_weight")
-            if len(_HEAD_CACHE) > 8:
-                _HEAD_CACHE.clear()
-            ent = _HEAD_CACHE[key] = wp
+            return wp
+
+        ent = _HEAD_CACHE.get(weight_obj, ("head", xs.device.index), make)
         b32 = _f32c(bias)
         hi = torch.empty((Bt, h, w, Cout), dtype=torch.bfloat16, device=xs.device)
         lo = torch.empty_like(hi) if with_lo else None
@@ -621,7 +640,7 @@ class CorrBlock:
         operands: "fp16" (taps and weights rounded to fp16, fp32 accumulate -- what the reference's
         --mixed_precision autocast does to this convolution) or "bf16".  Returns (B, Cout, h, w) fp32.
         Inference blocks on the tiled layout only (radius 3 or 4, <= 4 levels, a tensor-core precision).
-        The converted weights are cached on the block per (weight storage, version, operands)."""
+        The converted weights are cached per weight tensor object (and its version) and operand type."""
         if self._tiled is None:
             raise RuntimeError("lookup_convc1 needs an inference CorrBlock on the tiled layout "
                                "(radius 3 or 4, at most 4 levels, precision bf16x3 / bf16 / bf16_vol16, no gradient)")
@@ -633,6 +652,7 @@ class CorrBlock:
         B, h, w = self._geom
         nl, r = self.num_levels, self.radius
         K = nl * (2 * r + 1) ** 2
+        weight_obj = weight
         if weight.dim() == 4 and weight.shape[2:] == (1, 1):
             weight = weight[:, :, 0, 0]
         if weight.dim() != 2 or weight.shape[1] != K or bias.shape != (weight.shape[0],):
@@ -644,19 +664,18 @@ class CorrBlock:
         L = _lib.lib()
         bf = 1 if operands == "bf16" else 0
         with torch.cuda.device(c.device):
-            key = (weight.data_ptr(), weight._version, bias.data_ptr(), bias._version, bf)
-            cache = self.__dict__.setdefault("_convc1_cache", {})
-            if key not in cache:
-                cache.clear()
+            def make():
                 nbytes = int(L.rc_corr_convc1_weight_bytes(Cout, nl, r))
                 if nbytes == 0:
                     raise RuntimeError(f"lookup_convc1: unsupported Cout={Cout}, levels={nl}, radius={r}")
-                wp = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
+                wp_ = torch.empty(nbytes, dtype=torch.uint8, device=c.device)
                 w32 = _f32c(weight)
-                _lib.check(L.rc_corr_convc1_prep_weight(w32.data_ptr(), wp.data_ptr(), Cout, nl, r, bf, _stream()),
+                _lib.check(L.rc_corr_convc1_prep_weight(w32.data_ptr(), wp_.data_ptr(), Cout, nl, r, bf, _stream()),
                            "rc_corr_convc1_prep_weight")
-                cache[key] = (wp, _f32c(bias))
-            wp, b32 = cache[key]
+                return wp_
+
+            wp = _CONVC1_CACHE.get(weight_obj, (bf, nl, r, c.device.index), make)
+            b32 = _f32c(bias)
             out = torch.empty((B, Cout, h, w), dtype=torch.float32, device=c.device)
             vol16 = 1 if self._tiled[0].dtype == torch.float16 else 0
             rc = L.rc_corr_lookup_convc1_fwd(self._fast.ptrs, vol16, c.data_ptr(), wp.data_ptr(), b32.data_ptr(), out.data_ptr(),
