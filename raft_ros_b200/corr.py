@@ -301,13 +301,16 @@ class _WeightCache:
     handed out again."""
 
     def __init__(self):
-        import weakref
-        self._d = weakref.WeakKeyDictionary()
+        self._d = {}  # id(tensor) -> (weak reference to the tensor, {variant: (version, converted)})
 
     def get(self, weight, variant, make):
-        per = self._d.get(weight)
-        if per is None:
-            per = self._d[weight] = {}
+        import weakref
+        key = id(weight)
+        slot = self._d.get(key)
+        if slot is None or slot[0]() is not weight:  # (an id can be reused once its tensor is gone)
+            d = self._d
+            slot = d[key] = (weakref.ref(weight, lambda _r, k=key: d.pop(k, None)), {})
+        per = slot[1]
         ent = per.get(variant)
         if ent is None or ent[0] != weight._version:
             ent = per[variant] = (weight._version, make())
