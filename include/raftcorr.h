@@ -335,6 +335,15 @@ int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
                     int H1, int W1, int H2, int W2, int C, int radius, void *stream);
 
 /*
+ * RAFT.upsample_flow (core/raft.py:72-83): convex 8x upsampling of the flow field, one launch instead of
+ * view / softmax / unfold / mul / sum / permute / reshape with their temporaries:
+ *     out[n, c, 8y+i, 8x+j] = sum_k softmax_k(mask[n, k*64 + i*8 + j, y, x]) * 8 * flow[n, c, y + k/3 - 1, x + k%3 - 1]
+ *   flow : (N, 2, H, W) fp32      mask : (N, 576, H, W) fp32 (the mask head's output, already scaled by 0.25,
+ *   core/update.py:134-135)       out  : (N, 2, 8H, 8W) fp32, 16 B aligned.  Forward only.
+ */
+int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int N, int H, int W, void *stream);
+
+/*
  * bilinear_sampler: pixel-coordinate bilinear sampling with zeros outside.
  * Replaces: core/utils/utils.py:57-71 (normalise to [-1,1], F.grid_sample(..., align_corners=True),
  * optional in-bounds mask at :67-69).

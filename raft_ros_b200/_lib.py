@@ -126,6 +126,7 @@ SIGNATURES = {
     "rc_alt_corr_pyramid_fwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i,
                                      _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_convex_upsample_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "rc_bilinear_sampler_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_bilinear_sampler_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
 }

@@ -448,6 +448,13 @@ int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
                         W2, C, radius, static_cast<cudaStream_t>(stream));
 }
 
+int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int N, int H, int W, void *stream) {
+  RC_CHECK_ARG(flow && mask && out, "rc_convex_upsample_fwd: null pointer");
+  RC_CHECK_ARG(N > 0 && H > 0 && W > 0 && (long long)N * H * W < 0x7fffffffLL / 64, "rc_convex_upsample_fwd: bad sizes");
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 15) == 0, "rc_convex_upsample_fwd: out must be 16-byte aligned");
+  return launch_convex_upsample(flow, mask, out, N, H, W, static_cast<cudaStream_t>(stream));
+}
+
 int rc_bilinear_sampler_fwd(const float *img, const float *coords, float *out, float *mask, int M,
                             int C, int H, int W, int Ho, int Wo, void *stream) {
   RC_CHECK_ARG(img && coords && out, "rc_bilinear_sampler_fwd: null pointer");

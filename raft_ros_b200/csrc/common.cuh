@@ -121,6 +121,7 @@ int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi
                   const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius,
                   int precision, float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st);
 int launch_pool_tail(const LevelPtrs &lv, int B, int h, int w, int first, int L, cudaStream_t st);
+int launch_convex_upsample(const float *flow, const float *mask, float *out, int N, int H, int W, cudaStream_t st);
 int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
                         int H, int W, int Ho, int Wo, cudaStream_t st);
 int launch_bilinear_bwd(const float *gout, const float *coords, float *gimg, int M, int C, int H,

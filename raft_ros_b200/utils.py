@@ -66,3 +66,25 @@ def coords_grid(batch, ht, wd, device):
     ys = torch.arange(ht, device=device, dtype=torch.float32).view(1, 1, ht, 1).expand(batch, 1, ht, wd)
     xs = torch.arange(wd, device=device, dtype=torch.float32).view(1, 1, 1, wd).expand(batch, 1, ht, wd)
     return torch.cat([xs, ys], dim=1).contiguous()
+
+
+def upsample_flow(flow, mask):
+    """Upsample flow field [H/8, W/8, 2] -> [H, W, 2] using convex combination: `RAFT.upsample_flow` (reference
+    core/raft.py:72-83) as one kernel (rc_convex_upsample_fwd).  flow (N,2,H,W), mask (N,576,H,W) -> (N,2,8H,8W) fp32.
+    Inference only: tensors that require a gradient are refused."""
+    if not flow.is_cuda or not mask.is_cuda:
+        raise RuntimeError("flow and mask must be CUDA tensors")
+    if flow.dim() != 4 or flow.shape[1] != 2 or mask.dim() != 4 or mask.shape[1] != 576 or mask.shape[0] != flow.shape[0] \
+            or mask.shape[2:] != flow.shape[2:]:
+        raise RuntimeError(f"expected flow (N,2,H,W) and mask (N,576,H,W); got {tuple(flow.shape)}, {tuple(mask.shape)}")
+    if torch.is_grad_enabled() and (flow.requires_grad or mask.requires_grad):
+        raise RuntimeError("upsample_flow: inference only (no gradient); use the reference's torch ops for training")
+    f = flow.detach().float().contiguous()
+    m = mask.detach().float().contiguous()
+    N, _, H, W = f.shape
+    with torch.cuda.device(f.device):
+        out = torch.empty((N, 2, 8 * H, 8 * W), dtype=torch.float32, device=f.device)
+        rc = _lib.lib().rc_convex_upsample_fwd(f.data_ptr(), m.data_ptr(), out.data_ptr(), N, H, W,
+                                               torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "rc_convex_upsample_fwd")
+    return out
