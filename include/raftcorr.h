@@ -335,6 +335,20 @@ int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
                     int H1, int W1, int H2, int W2, int C, int radius, void *stream);
 
 /*
+ * rc_alt_corr_bwd with a DETERMINISTIC fmap2_grad.  The reference scatters fmap2_grad with float atomicAdd
+ * (correlation_kernel.cu:229-238), so its low bits change from run to run; here the contributions are
+ * accumulated as 64-bit fixed-point integers (scale chosen on the device from max|corr_grad| * max|fmap1| and
+ * the number of contributions so that no sum can overflow; resolution far below fp32), whose sum does not depend
+ * on the order of the atomics, and converted to fp32 once.  Same arguments and results (to fp32 rounding) as
+ * rc_alt_corr_bwd, except: fmap2_grad need NOT be zeroed by the caller, inputs must be finite, and
+ *   workspace : rc_alt_corr_bwd_det_workspace_bytes(B, H2, W2, C) bytes of device scratch, 256 B aligned.
+ */
+size_t rc_alt_corr_bwd_det_workspace_bytes(int B, int H2, int W2, int C);
+int rc_alt_corr_bwd_det(const float *fmap1, const float *fmap2, const float *coords, const float *corr_grad,
+                        float *fmap1_grad, float *fmap2_grad, int B, int N, int H1, int W1, int H2, int W2, int C,
+                        int radius, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
  * RAFT.upsample_flow (core/raft.py:72-83): convex 8x upsampling of the flow field, one launch instead of
  * view / softmax / unfold / mul / sum / permute / reshape with their temporaries:
  *     out[n, c, 8y+i, 8x+j] = sum_k softmax_k(mask[n, k*64 + i*8 + j, y, x]) * 8 * flow[n, c, y + k/3 - 1, x + k%3 - 1]

@@ -127,6 +127,8 @@ SIGNATURES = {
                                      _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_convex_upsample_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "rc_alt_corr_bwd_det_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "rc_alt_corr_bwd_det": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "rc_bilinear_sampler_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_bilinear_sampler_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
 }

@@ -13,6 +13,7 @@ module, see INTEGRATION.md.
 """
 from __future__ import annotations
 
+import os
 from typing import List
 
 import torch
@@ -70,10 +71,22 @@ def backward(fmap1: torch.Tensor, fmap2: torch.Tensor, coords: torch.Tensor, cor
         raise RuntimeError(f"corr_grad must be {(B, N, rd * rd, H1, W1)}, got {tuple(corr_grad.shape)}")
     with torch.cuda.device(fmap1.device):
         fmap1_grad = torch.empty_like(fmap1)
-        fmap2_grad = torch.zeros_like(fmap2)
         coords_grad = torch.zeros_like(coords)  # never written by the reference either (:307)
-        rc = _lib.lib().rc_alt_corr_bwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(), corr_grad.data_ptr(),
-                                        fmap1_grad.data_ptr(), fmap2_grad.data_ptr(), B, N, H1, W1, H2, W2, C,
-                                        int(radius), torch.cuda.current_stream().cuda_stream)
+        L = _lib.lib()
+        st = torch.cuda.current_stream().cuda_stream
+        if os.environ.get("RAFT_ALT_BWD_ATOMICS") == "1":
+            # the reference's scheme: float atomics into a zeroed buffer (run-to-run differences in the low bits)
+            fmap2_grad = torch.zeros_like(fmap2)
+            rc = L.rc_alt_corr_bwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(), corr_grad.data_ptr(),
+                                   fmap1_grad.data_ptr(), fmap2_grad.data_ptr(), B, N, H1, W1, H2, W2, C, int(radius), st)
+        else:
+            # default: bit-reproducible fmap2_grad (fixed-point accumulation, rc_alt_corr_bwd_det)
+            fmap2_grad = torch.empty_like(fmap2)
+            nbytes = int(L.rc_alt_corr_bwd_det_workspace_bytes(B, H2, W2, C))
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=fmap1.device)
+            rc = L.rc_alt_corr_bwd_det(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(), corr_grad.data_ptr(),
+                                       fmap1_grad.data_ptr(), fmap2_grad.data_ptr(), B, N, H1, W1, H2, W2, C, int(radius),
+                                       ws.data_ptr(), nbytes, st)
+            ws.record_stream(torch.cuda.current_stream())
         _lib.check(rc, "alt_cuda_corr.backward")
     return [fmap1_grad, fmap2_grad, coords_grad]

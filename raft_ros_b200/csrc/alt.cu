@@ -100,15 +100,56 @@ alt_fwd_kernel(const float *__restrict__ f1, const float *__restrict__ f2,
   }
 }
 
+// ---- deterministic fmap2_grad: fixed-point scale and helper kernels
+// maxima[0] = max |corr_grad|, maxima[1] = max |fmap1| (as float bit patterns, non-negative: integer max = float max).
+// One contribution is g * f1 with |g| <= max|corr_grad| (a convex combination of taps), at most `count` of them meet
+// in one accumulator: scale = 2^floor(61 - log2(count * bound)) keeps every partial sum below 2^62.
+__device__ __forceinline__ double det_scale(const float *maxima, double count) {
+  const double bound = (double)maxima[0] * (double)maxima[1] * count;
+  if (!(bound > 0.0) || !isfinite(bound)) return 1.0;
+  int e;
+  frexp(bound, &e);  // bound < 2^e
+  return ldexp(1.0, 61 - e);
+}
+
+__global__ void alt_absmax_kernel(const float *__restrict__ a, long long na, const float *__restrict__ b, long long nb,
+                                  unsigned int *__restrict__ maxima) {
+  float ma = 0.0f, mb = 0.0f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < na; i += (long long)gridDim.x * blockDim.x)
+    ma = fmaxf(ma, fabsf(__ldg(a + i)));
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nb; i += (long long)gridDim.x * blockDim.x)
+    mb = fmaxf(mb, fabsf(__ldg(b + i)));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ma = fmaxf(ma, __shfl_xor_sync(0xffffffffu, ma, o));
+    mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(maxima + 0, __float_as_uint(ma));  // non-negative floats order like their bit patterns
+    atomicMax(maxima + 1, __float_as_uint(mb));
+  }
+}
+
+__global__ void alt_det_finish_kernel(const long long *__restrict__ acc, float *__restrict__ g2, long long n,
+                                      const float *__restrict__ maxima, double count) {
+  const double inv = 1.0 / det_scale(maxima, count);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    g2[i] = (float)((double)acc[i] * inv);
+}
+
 // Backward: a warp owns one query pixel (all N coordinate sets), lanes <-> channels.
 // fmap1_grad is accumulated in registers and written once; fmap2_grad is a scatter into a
 // caller-zeroed buffer (float atomics, as in the reference :237).
-template <int R>
+// DET: fmap2_grad is accumulated as 64-bit FIXED-POINT integers (integer addition is associative, so the
+// result does not depend on the order in which the atomics land: bit-reproducible) into `acc`, scaled by a
+// power of two chosen from the data so that no sum can overflow; alt_det_finish_kernel converts back.
+template <int R, bool DET>
 __global__ void __launch_bounds__(kAltThreads)
 alt_bwd_kernel(const float *__restrict__ f1, const float *__restrict__ f2,
                const float *__restrict__ coords, const float *__restrict__ cg,
                float *__restrict__ g1, float *__restrict__ g2, int Nn, int H1, int W1, int H2,
-               int W2, int C, int B) {
+               int W2, int C, int B, unsigned long long *__restrict__ acc64 = nullptr,
+               const float *__restrict__ maxima = nullptr) {
   constexpr int RD = 2 * R + 1, PN = RD + 1, NPATCH = PN * PN, NTAP = RD * RD;
   constexpr int NE = (NPATCH + 31) / 32;
   __shared__ float gs_all[kAltWarps][NPATCH];
@@ -122,6 +163,8 @@ alt_bwd_kernel(const float *__restrict__ f1, const float *__restrict__ f2,
   const float4 *a4 = reinterpret_cast<const float4 *>(f1 + ((size_t)b * HW1 + p) * C);
   const float4 *b4 = reinterpret_cast<const float4 *>(f2 + (size_t)b * H2 * W2 * C);
   float *g2b = g2 + (size_t)b * H2 * W2 * C;
+  unsigned long long *accb = DET ? acc64 + (size_t)b * H2 * W2 * C : nullptr;
+  const double fx_scale = DET ? det_scale(maxima, (double)Nn * HW1) : 0.0;
 
   for (int c0 = 0; c0 < C4; c0 += 32) {
     const int c = c0 + lane;
@@ -163,11 +206,19 @@ alt_bwd_kernel(const float *__restrict__ f1, const float *__restrict__ f2,
           acc.y = fmaf(g, bv.y, acc.y);
           acc.z = fmaf(g, bv.z, acc.z);
           acc.w = fmaf(g, bv.w, acc.w);
-          float *dst = g2b + off * 4;
-          atomicAdd(dst + 0, g * av.x);
-          atomicAdd(dst + 1, g * av.y);
-          atomicAdd(dst + 2, g * av.z);
-          atomicAdd(dst + 3, g * av.w);
+          if constexpr (DET) {
+            unsigned long long *dst = accb + off * 4;
+            atomicAdd(dst + 0, (unsigned long long)__double2ll_rn((double)(g * av.x) * fx_scale));
+            atomicAdd(dst + 1, (unsigned long long)__double2ll_rn((double)(g * av.y) * fx_scale));
+            atomicAdd(dst + 2, (unsigned long long)__double2ll_rn((double)(g * av.z) * fx_scale));
+            atomicAdd(dst + 3, (unsigned long long)__double2ll_rn((double)(g * av.w) * fx_scale));
+          } else {
+            float *dst = g2b + off * 4;
+            atomicAdd(dst + 0, g * av.x);
+            atomicAdd(dst + 1, g * av.y);
+            atomicAdd(dst + 2, g * av.z);
+            atomicAdd(dst + 3, g * av.w);
+          }
         }
       }
     }
@@ -198,7 +249,29 @@ static int alt_bwd_r(const float *f1, const float *f2, const float *coords, cons
   const long long pixels = (long long)B * H1 * W1;
   const long long blocks = (pixels + kAltWarps - 1) / kAltWarps;
   if (blocks > 2147483647LL) { set_error("alt_corr_bwd: grid too large"); return RC_ERR_UNSUPPORTED; }
-  alt_bwd_kernel<R><<<(unsigned)blocks, kAltThreads, 0, st>>>(f1, f2, coords, cg, g1, g2, Nn, H1, W1, H2, W2, C, B);
+  alt_bwd_kernel<R, false><<<(unsigned)blocks, kAltThreads, 0, st>>>(f1, f2, coords, cg, g1, g2, Nn, H1, W1, H2, W2, C, B);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+template <int R>
+static int alt_bwd_det_r(const float *f1, const float *f2, const float *coords, const float *cg, float *g1, float *g2, int B,
+                         int Nn, int H1, int W1, int H2, int W2, int C, void *ws, cudaStream_t st) {
+  constexpr int RD = 2 * R + 1;
+  const long long pixels = (long long)B * H1 * W1;
+  const long long blocks = (pixels + kAltWarps - 1) / kAltWarps;
+  if (blocks > 2147483647LL) { set_error("alt_corr_bwd: grid too large"); return RC_ERR_UNSUPPORTED; }
+  const long long n2 = (long long)B * H2 * W2 * C;
+  unsigned int *maxima = static_cast<unsigned int *>(ws);               // 2 words (in a 256 B header)
+  unsigned long long *acc = reinterpret_cast<unsigned long long *>(static_cast<unsigned char *>(ws) + 256);
+  RC_CUDA(cudaMemsetAsync(ws, 0, 256 + (size_t)n2 * 8, st));
+  alt_absmax_kernel<<<148 * 8, 256, 0, st>>>(cg, (long long)B * Nn * RD * RD * H1 * W1, f1, pixels * C, maxima);
+  RC_CUDA(cudaGetLastError());
+  alt_bwd_kernel<R, true><<<(unsigned)blocks, kAltThreads, 0, st>>>(f1, f2, coords, cg, g1, g2, Nn, H1, W1, H2, W2, C, B, acc,
+                                                                  reinterpret_cast<const float *>(maxima));
+  RC_CUDA(cudaGetLastError());
+  alt_det_finish_kernel<<<148 * 8, 256, 0, st>>>(reinterpret_cast<const long long *>(acc), g2, n2,
+                                                reinterpret_cast<const float *>(maxima), (double)Nn * H1 * W1);
   RC_CUDA(cudaGetLastError());
   return RC_OK;
 }
@@ -229,6 +302,19 @@ int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const 
                    float *g1, float *g2, int B, int N, int H1, int W1, int H2, int W2, int C,
                    int r, cudaStream_t st) {
 #define CALL(R) alt_bwd_r<R>(f1, f2, coords, cg, g1, g2, B, N, H1, W1, H2, W2, C, st)
+  RC_RADIUS_SWITCH(r, CALL)
+#undef CALL
+}
+
+}  // namespace rc
+
+namespace rc {
+
+size_t alt_bwd_det_workspace_bytes(int B, int H2, int W2, int C) { return 256 + (size_t)B * H2 * W2 * C * 8; }
+
+int launch_alt_bwd_det(const float *f1, const float *f2, const float *coords, const float *cg, float *g1, float *g2, int B, int N,
+                       int H1, int W1, int H2, int W2, int C, int r, void *ws, cudaStream_t st) {
+#define CALL(R) alt_bwd_det_r<R>(f1, f2, coords, cg, g1, g2, B, N, H1, W1, H2, W2, C, ws, st)
   RC_RADIUS_SWITCH(r, CALL)
 #undef CALL
 }

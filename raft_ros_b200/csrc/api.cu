@@ -455,6 +455,25 @@ int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int
   return launch_convex_upsample(flow, mask, out, N, H, W, static_cast<cudaStream_t>(stream));
 }
 
+size_t rc_alt_corr_bwd_det_workspace_bytes(int B, int H2, int W2, int C) {
+  if (B <= 0 || H2 <= 0 || W2 <= 0 || C <= 0) return 0;
+  return alt_bwd_det_workspace_bytes(B, H2, W2, C);
+}
+
+int rc_alt_corr_bwd_det(const float *fmap1, const float *fmap2, const float *coords, const float *corr_grad,
+                        float *fmap1_grad, float *fmap2_grad, int B, int N, int H1, int W1, int H2, int W2, int C, int radius,
+                        void *workspace, size_t workspace_bytes, void *stream) {
+  if (int rc = check_alt("rc_alt_corr_bwd_det", B, N, H1, W1, H2, W2, C, radius)) return rc;
+  RC_CHECK_ARG(fmap1 && fmap2 && coords && corr_grad && fmap1_grad && fmap2_grad, "rc_alt_corr_bwd_det: null pointer");
+  const size_t need = alt_bwd_det_workspace_bytes(B, H2, W2, C);
+  if (workspace == nullptr || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255) != 0) {
+    set_error("rc_alt_corr_bwd_det: workspace missing, not 256-byte aligned or too small (%zu < %zu bytes)", workspace_bytes, need);
+    return RC_ERR_WORKSPACE;
+  }
+  return launch_alt_bwd_det(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, N, H1, W1, H2, W2, C, radius, workspace,
+                            static_cast<cudaStream_t>(stream));
+}
+
 int rc_bilinear_sampler_fwd(const float *img, const float *coords, float *out, float *mask, int M,
                             int C, int H, int W, int Ho, int Wo, void *stream) {
   RC_CHECK_ARG(img && coords && out, "rc_bilinear_sampler_fwd: null pointer");

@@ -109,6 +109,9 @@ int launch_alt_bwd(const float *f1, const float *f2, const float *coords, const 
                    float *g1, float *g2, int B, int N, int H1, int W1, int H2, int W2, int C,
                    int r, cudaStream_t st);
 
+size_t alt_bwd_det_workspace_bytes(int B, int H2, int W2, int C);
+int launch_alt_bwd_det(const float *f1, const float *f2, const float *coords, const float *cg, float *g1, float *g2, int B, int N,
+                       int H1, int W1, int H2, int W2, int C, int r, void *ws, cudaStream_t st);
 int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW, cudaStream_t st);
 int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level, cudaStream_t st);
 size_t alt_tc_plan_bytes(int B, int H1, int W1, int L);

@@ -317,6 +317,39 @@ def test_alt_fwd_bwd_vs_oracle(rr, shape):
     assert tuple(gc.shape) == coords.shape and not bool(gc.any())
 
 
+def test_alt_backward_fmap2_grad_is_bit_reproducible(rr, monkeypatch):
+    """alt_cuda_corr.backward: thousands of query pixels whose windows all land on the same few fmap2 pixels -- the
+    case in which a float atomicAdd scatter (the reference's, correlation_kernel.cu:229-238) gives different low bits
+    from run to run.  The default path (rc_alt_corr_bwd_det, fixed-point accumulation) must give the same bits every
+    time and agree with the oracle; the float-atomics path stays available and agrees to rounding."""
+    B, N, H1, W1, H2, W2, C, r = 2, 1, 48, 64, 20, 24, 64, 4
+    rng = np.random.default_rng(2025)
+    f1 = rng.standard_normal((B, H1, W1, C)).astype(np.float32)
+    f2 = rng.standard_normal((B, H2, W2, C)).astype(np.float32)
+    coords = np.empty((B, N, H1, W1, 2), np.float32)
+    coords[..., 0] = 9.3 + 0.5 * rng.standard_normal((B, N, H1, W1))
+    coords[..., 1] = 7.7 + 0.5 * rng.standard_normal((B, N, H1, W1))
+    g = rng.standard_normal((B, N, 81, H1, W1)).astype(np.float32)
+    w1, w2, _ = O.alt_bwd(f1, f2, coords, g, r)
+    runs = [rr.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(g), r) for _ in range(3)]
+    torch.cuda.synchronize()
+    for g1, g2, gc in runs:
+        assert relmax(n(g1), w1) <= 3e-6 and relmax(n(g2), w2) <= 3e-6, (relmax(n(g1), w1), relmax(n(g2), w2))
+    assert all(torch.equal(runs[0][0], x[0]) and torch.equal(runs[0][1], x[1]) for x in runs[1:])
+    monkeypatch.setenv("RAFT_ALT_BWD_ATOMICS", "1")
+    a1, a2, _ = rr.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(g), r)
+    assert torch.equal(a1, runs[0][0]) and relmax(n(a2), w2) <= 1e-5
+    # all-zero gradients (scale undefined) and a workspace that is too small
+    z = rr.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(np.zeros_like(g)), r)
+    assert not bool(z[1].any())
+    from raft_ros_b200 import _lib
+    L = _lib.lib()
+    x = torch.zeros(1024, device=DEV)
+    rc = L.rc_alt_corr_bwd_det(x.data_ptr(), x.data_ptr(), x.data_ptr(), x.data_ptr(), x.data_ptr(), x.data_ptr(), B, N, H1, W1,
+                               H2, W2, C, r, x.data_ptr(), 1024, None)
+    assert rc == 4 and b"workspace" in L.rc_last_error()
+
+
 ALT_TOL = {"fp32": dict(rel=5e-6, norm=3e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
 
 
