@@ -263,17 +263,35 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
             // its patch slot under a predicate (no bounce through a row buffer; the epilogue has issue
             // slots to spare, shared-memory round trips it has not)
             const int cbase = x0 - ox;
+            if (shape == 0) {
+              // 32 x 8 chunk: one chunk row per load; rows that no window of the warp touches are skipped
 #pragma unroll 1
-            for (int rr = 0; rr < 8; ++rr) {
-              // 32 accumulator columns per load: one chunk row (32 x 8 chunks) or two (16 x 16 chunks)
-              const int py0 = oy + (shape ? 2 * rr : rr) - y0;
-              const bool need0 = xhit && (unsigned)py0 < (unsigned)PN;
-              const bool need1 = shape && xhit && (unsigned)(py0 + 1) < (unsigned)PN;
-              if (__any_sync(0xffffffffu, need0 || need1)) {  // tcgen05.ld is warp-collective
-                float v[32];
-                tmem_ld32(taddr + rr * 32, v);
-                tmem_ld_wait();
-                if (shape) {
+              for (int rr = 0; rr < CH0; ++rr) {
+                const int py = oy + rr - y0;
+                const bool need = xhit && (unsigned)py < (unsigned)PN;
+                if (__any_sync(0xffffffffu, need)) {  // tcgen05.ld is warp-collective
+                  float v[32];
+                  tmem_ld32(taddr + rr * CW0, v);
+                  tmem_ld_wait();
+                  if (need) {
+                    const uint32_t prow = patch + (uint32_t)((py * PN - cbase) * 4);
+#pragma unroll
+                    for (int c = 0; c < CW0; ++c)
+                      if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[c]);
+                  }
+                }
+              }
+            } else {
+              // 16 x 16 chunk: two chunk rows per load
+#pragma unroll 1
+              for (int rr = 0; rr < CH1 / 2; ++rr) {
+                const int py0 = oy + 2 * rr - y0;
+                const bool need0 = xhit && (unsigned)py0 < (unsigned)PN;
+                const bool need1 = xhit && (unsigned)(py0 + 1) < (unsigned)PN;
+                if (__any_sync(0xffffffffu, need0 || need1)) {
+                  float v[32];
+                  tmem_ld32(taddr + rr * 32, v);
+                  tmem_ld_wait();
                   if (need0) {
                     const uint32_t prow = patch + (uint32_t)((py0 * PN - cbase) * 4);
 #pragma unroll
@@ -286,11 +304,6 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
                     for (int c = 0; c < CW1; ++c)
                       if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[CW1 + c]);
                   }
-                } else if (need0) {
-                  const uint32_t prow = patch + (uint32_t)((py0 * PN - cbase) * 4);
-#pragma unroll
-                  for (int c = 0; c < CW0; ++c)
-                    if ((unsigned)(c - cbase) < (unsigned)PN) sts32(prow + c * 4, v[c]);
                 }
               }
             }
