@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -38,12 +39,18 @@ constexpr int QH = 8, QW = 16;       // query tile (rows x cols) = 128 pixels = 
 constexpr int CW0 = 32, CH0 = 8, CW1 = 16, CH1 = 16;
 constexpr int TK = 64, UK = 16;
 constexpr int A_BYTES = 128 * TK * 2, B_BYTES = 256 * TK * 2;
-constexpr int kStageBytes = A_BYTES + B_BYTES;   // one operand pair per stage
-constexpr int kStages = 3;
+// one operand pair per stage; a CTA of a pair (NCTA = 2) stages its own 128 query pixels and HALF of the chunk
+template <int NCTA>
+struct StageCfg {
+  static constexpr int kStageBytes = A_BYTES + B_BYTES / NCTA;
+  static constexpr int kStages = NCTA == 2 ? 4 : 3;
+};
+constexpr int kRingBytes = 3 * (A_BYTES + B_BYTES);  // 144 KB: 3 stages of 48 KB, or 4 of 32 KB
 constexpr int kEpiWarps = 4, kProducerWarp = 4, kMmaWarp = 5, kThreads = 192;
 constexpr int kPatchStrideMax = 101;             // (2*4+2)^2 + 1: odd -> conflict-free across lanes
 constexpr int kPatchBytes = 128 * kPatchStrideMax * 4;
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kPatchBytes + 256;
+constexpr int kSmemBytes = 1024 + kRingBytes + kPatchBytes + 256;
+constexpr uint32_t kIdescA2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 constexpr uint32_t kIdescA = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr int kMaxLevels = 4;
 
@@ -64,7 +71,7 @@ struct Params {
 };
 
 // ------------------------------------------------------------------ plan
-template <int R>
+template <int R, int NCTA>
 __global__ void __launch_bounds__(128)
 alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B, int H1, int W1, int L, int tiles_x,
                 int tiles_y, long long total_tiles, int h2_0, int w2_0, int allow_square) {
@@ -77,12 +84,13 @@ alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B
   const int per_item = tiles_x * tiles_y;
   const int b = (int)(tile / per_item);
   const int rem = (int)(tile - (long long)b * per_item);
-  const int ty0 = (rem / tiles_x) * QH, tx0 = (rem % tiles_x) * QW;
+  constexpr int NI = 4 * NCTA;  // query pixels per lane: the tile is QH * NCTA rows x QW columns
+  const int ty0 = (rem / tiles_x) * (QH * NCTA), tx0 = (rem % tiles_x) * QW;
   const size_t HW = (size_t)H1 * W1;
-  float cx[4], cy[4];
-  bool ok[4];
+  float cx[NI], cy[NI];
+  bool ok[NI];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < NI; ++i) {
     const int m = lane + 32 * i;
     const int y = ty0 + m / QW, x = tx0 + m % QW;
     ok[i] = y < H1 && x < W1;
@@ -94,7 +102,7 @@ alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B
     const int h2 = h2_0 >> l, w2 = w2_0 >> l;
     int xmin = 0x7fffffff, xmax = -0x7fffffff, ymin = 0x7fffffff, ymax = -0x7fffffff;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < NI; ++i) {
       if (!ok[i]) continue;
       float fr;
       // window [x0, x0+PN) x [y0, y0+PN), clipped to the map: only that part can be non-zero
@@ -127,9 +135,16 @@ alt_plan_kernel(const float *__restrict__ coords, int4 *__restrict__ plan, int B
 }
 
 // ------------------------------------------------------------------ main kernel
-template <int R>
+// NCTA == 2: clusters of two CTAs share one 16 x 16 query tile (rows 0-7 / 8-15) and its boxes: a pair contracts its
+// 256 query pixels with a chunk in one tcgen05.mma.cta_group::2 (each CTA stages its own A and half of the chunk),
+// so a box -- which grows by the window, not by the tile -- is paid for by twice the pixels.
+template <int R, int NCTA>
 __global__ void __launch_bounds__(kThreads, 1)
 alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
+  constexpr int kStages = StageCfg<NCTA>::kStages, kStageBytes = StageCfg<NCTA>::kStageBytes;
+  const uint32_t rank = (NCTA == 2) ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const unsigned unit0 = blockIdx.x / NCTA, unit_step = gridDim.x / NCTA;
   constexpr int RD = 2 * R + 1, PN = RD + 1, NTAP = RD * RD, NPATCH = PN * PN;
   constexpr int kPatchStride = NPATCH + 1;  // odd -> conflict-free across lanes
   static_assert(kPatchStride <= kPatchStrideMax, "patch buffer");
@@ -137,8 +152,8 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   const uint32_t raw_u32 = smem_u32(smem_raw);
   const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
   uint8_t *smem = smem_raw + (base_u32 - raw_u32);
-  const uint32_t patch_u32 = base_u32 + kStages * kStageBytes;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes + kPatchBytes);
+  const uint32_t patch_u32 = base_u32 + kRingBytes;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kPatchBytes);
   uint64_t *full = bars, *empty = bars + kStages, *tfull = bars + 2 * kStages, *tempty = tfull + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -146,18 +161,22 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
 
   if (warp == kProducerWarp && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], NCTA);  // pair: the leader's barrier also takes the peer's arrival and bytes
       mbar_init(&empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], kEpiWarps);
+      mbar_init(&tempty[a], kEpiWarps * NCTA);
     }
     fence_barrier_init();
   }
-  if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
+  if (warp == kMmaWarp) {
+    if (NCTA == 2) tmem_alloc2(tmem_slot, 512);
+    else tmem_alloc(tmem_slot, 512);
+  }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();  // both CTAs' barriers are initialised before any remote use
   tc_fence_after();
   pdl_wait();  // the plan (previous kernel), the coordinates and the feature maps are read from here on
   const uint32_t tmem_base = *tmem_slot;
@@ -168,24 +187,31 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      for (long long t = unit0; t < P.total_tiles; t += unit_step) {
         const int b = (int)(t / per_item);
         const int rem = (int)(t - (long long)b * per_item);
-        const int ty0 = (rem / P.tiles_x) * QH, tx0 = (rem % P.tiles_x) * QW;
+        const int ty0 = (rem / P.tiles_x) * (QH * NCTA) + (int)rank * QH, tx0 = (rem % P.tiles_x) * QW;
         for (int l = 0; l < P.L; ++l) {
           const int4 pl = __ldg(P.plan + t * P.L + l);
           const int shape = pl.z >> 16, ncx = pl.z & 0xffff;
           const int cw = shape ? CW1 : CW0, chh = shape ? CH1 : CH0;
           for (int cyi = 0; cyi < pl.w; ++cyi)
             for (int cxi = 0; cxi < ncx; ++cxi) {
-              const int ox = pl.x + cxi * cw, oy = pl.y + cyi * chh;
+              const int ox = pl.x + cxi * cw, oy = pl.y + cyi * chh + (int)rank * (chh / NCTA);  // this CTA's rows of the chunk
               for (int s = 0; s < steps; ++s) {
                 const int kb = s / P.npass, pr = s - kb * P.npass;  // pr: 0 hi*hi, 1 hi*lo, 2 lo*hi
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t *sp = smem + stage * kStageBytes;
-                mbar_expect_tx(&full[stage], kStageBytes);
-                tma_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
-                tma_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
+                if (NCTA == 1) {
+                  mbar_expect_tx(&full[stage], kStageBytes);
+                  tma_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
+                  tma_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
+                } else {
+                  if (leader) mbar_expect_tx(&full[stage], 2 * kStageBytes);  // both CTAs' bytes land on the leader's barrier
+                  tma2_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
+                  tma2_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
+                  if (!leader) mbar_arrive_leader(&full[stage]);
+                }
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
               }
             }
@@ -193,10 +219,10 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
       }
     }
   } else if (warp == kMmaWarp) {
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      for (long long t = unit0; t < P.total_tiles; t += unit_step) {
         for (int l = 0; l < P.L; ++l) {
           const int4 pl = __ldg(P.plan + t * P.L + l);
           const int chunks = (pl.z & 0xffff) * pl.w;
@@ -212,12 +238,15 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
 #pragma unroll
               for (int k = 0; k < TK / UK; ++k) {
                 const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);
-                umma_bf16(d_tmem, ad + koff, bd + koff, kIdescA, (s | k) != 0 ? 1u : 0u);
+                if (NCTA == 1) umma_bf16(d_tmem, ad + koff, bd + koff, kIdescA, (s | k) != 0 ? 1u : 0u);
+                else umma2_bf16(d_tmem, ad + koff, bd + koff, kIdescA2, (s | k) != 0 ? 1u : 0u);
               }
-              umma_commit(&empty[stage]);
+              if (NCTA == 1) umma_commit(&empty[stage]);
+              else umma2_commit_both(&empty[stage]);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&tfull[acc]);
+            if (NCTA == 1) umma_commit(&tfull[acc]);
+            else umma2_commit_both(&tfull[acc]);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
           }
@@ -233,10 +262,10 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
     uint32_t acc_phase = 0;
     const size_t HW = (size_t)P.H1 * P.W1;
     const int CH = P.L * NTAP;
-    for (long long t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+    for (long long t = unit0; t < P.total_tiles; t += unit_step) {
       const int b = (int)(t / per_item);
       const int rem = (int)(t - (long long)b * per_item);
-      const int y = (rem / P.tiles_x) * QH + m / QW, x = (rem % P.tiles_x) * QW + m % QW;
+      const int y = (rem / P.tiles_x) * (QH * NCTA) + (int)rank * QH + m / QW, x = (rem % P.tiles_x) * QW + m % QW;
       const bool pvalid = y < P.H1 && x < P.W1;
       float cx = 0.0f, cy = 0.0f;
       if (pvalid) {
@@ -309,7 +338,10 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[acc]);
+            if (lane == 0) {
+              if (NCTA == 1) mbar_arrive(&tempty[acc]);
+              else mbar_arrive_leader(&tempty[acc]);  // the pair's MMA thread lives in the leader CTA
+            }
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
           }
@@ -341,8 +373,12 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();  // the peer may still be signalling our barriers
   tc_fence_after();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+  if (warp == kMmaWarp) {
+    if (NCTA == 2) tmem_dealloc2(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
+  }
 }
 
 // ------------------------------------------------------------------ layout prepass
@@ -470,7 +506,7 @@ static int sm_count() {
 struct Setup {
   Maps M;
   Params P;   // coords / out / plan / scale are filled per call
-  int radius;
+  int radius, ncta;
   unsigned magic;
 };
 constexpr unsigned kSetupMagic = 0x52434154u;
@@ -509,6 +545,17 @@ int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, 
   return RC_OK;
 }
 
+// One CTA per 8 x 16 query tile by default; RAFT_CORR_ALT_CTAS=2 selects CTA pairs (a 16 x 16 tile per pair).  Measured at
+// 2160x3840: the pairs issue 37 % fewer MMAs (15 instead of 24 chunks per 256 query pixels) but every epilogue thread then
+// scans the chunks of the larger box, and the epilogue becomes the bound: 0.434 vs 0.406 ms (bf16x3), 0.231 vs 0.219 (bf16).
+static int alt_ctas() {
+  static const int n = [] {
+    const char *e = getenv("RAFT_CORR_ALT_CTAS");
+    return (e && e[0] == '2') ? 2 : 1;
+  }();
+  return n;
+}
+
 size_t alt_tc_plan_bytes(int B, int H1, int W1, int L) {
   const long long tiles = (long long)B * ((H1 + alttc::QH - 1) / alttc::QH) * ((W1 + alttc::QW - 1) / alttc::QW);
   return (size_t)tiles * L * sizeof(int4);
@@ -529,7 +576,9 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
     return RC_ERR_INVALID;
   }
   const bool x3 = precision == RC_PREC_BF16X3;
+  const int ncta = alt_ctas();
   Setup S{};
+  S.ncta = ncta;
   if (int rc = map4(&S.M.a[0], f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
   if (int rc = map4(&S.M.a[1], x3 ? f1_lo : f1_hi, Cp, W1, H1, B, QW, QH)) return rc;
   Params &P = S.P;
@@ -542,7 +591,7 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
       return RC_ERR_INVALID;
     }
     for (int sh = 0; sh < 2; ++sh) {
-      const int bw = sh ? CW1 : CW0, bh = sh ? CH1 : CH0;
+      const int bw = sh ? CW1 : CW0, bh = (sh ? CH1 : CH0) / ncta;  // a CTA of a pair loads half of the chunk's rows
       if (int rc = map4(&S.M.b[l][sh][0], f2_hi[ll], Cp, P.w2[l], P.h2[l], B, bw, bh)) return rc;
       if (int rc = map4(&S.M.b[l][sh][1], x3 ? f2_lo[ll] : f2_hi[ll], Cp, P.w2[l], P.h2[l], B, bw, bh)) return rc;
     }
@@ -551,7 +600,7 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
   P.k_blocks = Cp / TK;
   P.npass = x3 ? 3 : 1;
   P.tiles_x = (W1 + QW - 1) / QW;
-  P.tiles_y = (H1 + QH - 1) / QH;
+  P.tiles_y = (H1 + QH * ncta - 1) / (QH * ncta);
   P.total_tiles = (long long)B * P.tiles_x * P.tiles_y;
   S.radius = radius;
   S.magic = kSetupMagic;
@@ -559,20 +608,35 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
   return RC_OK;
 }
 
-template <int R>
+template <int R, int NCTA>
 static int alt_tc_run_r(const alttc::Setup &S, cudaStream_t st) {
   using namespace alttc;
   const Params &P = S.P;
   {
     const unsigned blocks = (unsigned)((P.total_tiles + 3) / 4);
-    RC_CUDA(launch_pdl(alt_plan_kernel<R>, dim3(blocks), dim3(128), 0, st, P.coords, const_cast<int4 *>(P.plan), P.B, P.H1, P.W1,
-                       P.L, P.tiles_x, P.tiles_y, P.total_tiles, P.h2[0], P.w2[0], P.npass == 3 ? 1 : 0));
+    RC_CUDA(launch_pdl(alt_plan_kernel<R, NCTA>, dim3(blocks), dim3(128), 0, st, P.coords, const_cast<int4 *>(P.plan), P.B, P.H1,
+                       P.W1, P.L, P.tiles_x, P.tiles_y, P.total_tiles, P.h2[0], P.w2[0], P.npass == 3 ? 1 : 0));
   }
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
-  RC_CUDA(cudaFuncSetAttribute(alt_tc_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-  const long long sms = sm_count();
-  const unsigned grid = (unsigned)(P.total_tiles < sms ? P.total_tiles : sms);
-  RC_CUDA(launch_pdl(alt_tc_kernel<R>, dim3(grid), dim3(kThreads), (size_t)kSmemBytes, st, S.M, P));
+  auto kern = alt_tc_kernel<R, NCTA>;
+  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  const long long units = sm_count() / NCTA;
+  const unsigned grid = (unsigned)((P.total_tiles < units ? P.total_tiles : units) * NCTA);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = NCTA;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  RC_CUDA(cudaLaunchKernelEx(&cfg, kern, S.M, P));
   return RC_OK;
 }
 
@@ -594,7 +658,8 @@ int alt_tc_run(const void *blob, const float *coords, float *out, float scale, v
   S.P.out = out;
   S.P.plan = static_cast<const int4 *>(plan_ws);
   S.P.scale = scale;
-  return S.radius == 3 ? alt_tc_run_r<3>(S, st) : alt_tc_run_r<4>(S, st);
+  if (S.ncta == 2) return S.radius == 3 ? alt_tc_run_r<3, 2>(S, st) : alt_tc_run_r<4, 2>(S, st);
+  return S.radius == 3 ? alt_tc_run_r<3, 1>(S, st) : alt_tc_run_r<4, 1>(S, st);
 }
 
 int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,

@@ -46,10 +46,10 @@ def gather_batch(local: torch.Tensor, num_pairs: int, group=None) -> torch.Tenso
     return torch.cat([bufs[r][: e - b] for r, (b, e) in enumerate(sizes)], dim=0)
 
 
-def shard_rows(num_rows: int, rank: int, world: int, align: int = 8) -> Tuple[int, int]:
+def shard_rows(num_rows: int, rank: int, world: int, align: int = 16) -> Tuple[int, int]:
     """[begin, end) of the query ROWS of one large frame that `rank` owns: contiguous
-    bands whose starts are multiples of `align` (the on-the-fly kernel's query tile is 8 rows: aligned bands give
-    bit-identical results to the unsharded call), sizes as even as that allows; trailing ranks may own nothing when
+    bands whose starts are multiples of `align` (the on-the-fly kernel's query tile is 16 rows -- a CTA pair -- so
+    aligned bands give bit-identical results to the unsharded call), sizes as even as that allows; trailing ranks may own nothing when
     the frame has fewer tile rows than ranks.  The band of fmap1 / coords goes with the FULL fmap2:
     `AlternateCorrBlock(fmap1[:, :, b:e], fmap2)(coords[:, :, b:e])`."""
     if world < 1 or not (0 <= rank < world) or num_rows < 0 or align < 1:
@@ -59,7 +59,7 @@ def shard_rows(num_rows: int, rank: int, world: int, align: int = 8) -> Tuple[in
     return min(b * align, num_rows), min(e * align, num_rows)
 
 
-def gather_rows(local: torch.Tensor, num_rows: int, align: int = 8, group=None) -> torch.Tensor:
+def gather_rows(local: torch.Tensor, num_rows: int, align: int = 16, group=None) -> torch.Tensor:
     """Assemble (B, C, rows_r, W) bands into the (B, C, num_rows, W) result on every rank (all_gather on padded bands)."""
     import torch.distributed as dist
 

@@ -457,7 +457,7 @@ def test_alt_prep_pools_like_avg_pool2d(rr, shape):
 @pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
 def test_alternate_block_query_row_band(rr, precision):
     """A band of query rows against the full fmap2 (how one large pair is split over GPUs):
-    bit-identical to the same rows of the whole-frame block when the band starts on a tile row, and within
+    bit-identical to the same rows of the whole-frame block when the band starts on a (16-row) tile row, and within
     rounding of it otherwise (the box of a query tile, and with it the summation split, depends on the tiling)."""
     B, D, H, W, L = 1, 128, 43, 70, 4
     rng = np.random.default_rng(43)
@@ -465,12 +465,12 @@ def test_alternate_block_query_row_band(rr, precision):
     f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
     coords = t(make_coords("sigma4", B, H, W, rng))
     full = rr.AlternateCorrBlock(f1, f2, num_levels=L, radius=4, precision=precision)(coords)
-    for r0, r1 in ((0, 16), (16, 43), (11, 30)):
+    for r0, r1 in ((0, 16), (16, 43), (32, 43), (11, 30), (8, 24)):
         band = rr.AlternateCorrBlock(f1[:, :, r0:r1].contiguous(), f2, num_levels=L, radius=4, precision=precision)
         got = band(coords[:, :, r0:r1].contiguous())
         want = full[:, :, r0:r1]
         assert got.shape == want.shape
-        if r0 % 8 == 0:
+        if r0 % 16 == 0:  # the query tile is 16 rows (a CTA pair)
             assert torch.equal(got, want), (r0, r1)
         else:
             assert relmax(n(got), n(want)) <= 2e-6, (r0, r1, relmax(n(got), n(want)))
@@ -976,3 +976,17 @@ def test_corrblock_refuses_coords_that_want_a_gradient(rr):
         with torch.no_grad():
             assert blk(c).shape == (1, 324, 16, 16)
         assert blk(c.detach()).shape == (1, 324, 16, 16)
+
+
+def test_cta_pair_on_the_fly_variant_in_a_subprocess(rr):
+    """RAFT_CORR_ALT_CTAS=2 selects the CTA-pair on-the-fly kernel (16x16 query tiles, cta_group::2) instead of the default
+    single CTA per 8x16 tile; the variable is read once per process, so the oracle comparisons re-run in a child process
+    with it set."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RAFT_CORR_ALT_CTAS="2")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-x", "-q", "-m", "gpu",
+                        "-k", "alternate_block_vs_oracle or alternate_block_radius3", "-p", "no:cacheprovider"],
+                       capture_output=True, text=True, env=env, cwd=root, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

@@ -74,8 +74,8 @@ def test_shard_rows_partition():
             spans = [shard_rows(rows, r, world) for r in range(world)]
             assert spans[0][0] == 0 and spans[-1][1] == rows
             assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
-            assert all(b % 8 == 0 or b == rows for b, _ in spans)  # bands start on a query-tile row
-    assert [shard_rows(270, r, 8) for r in range(8)][0] == (0, 40)
+            assert all(b % 16 == 0 or b == rows for b, _ in spans)  # bands start on a query-tile row
+    assert [shard_rows(270, r, 8) for r in range(8)][0] == (0, 48)
 
 
 def _rows_worker(rank, world, port, rows, q):
