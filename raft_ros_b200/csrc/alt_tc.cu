@@ -458,40 +458,11 @@ alt_prep_pool_kernel(const float *__restrict__ f, __nv_bfloat16 *__restrict__ hi
 }
 
 // ------------------------------------------------------------------ host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
 static int map4(CUtensorMap *tm, const void *base, int Cp, int W, int H, int B, int bw, int bh) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) {
-    set_error("cuTensorMapEncodeTiled is not available from the driver");
-    return RC_ERR_CUDA;
-  }
-  const cuuint64_t dims[4] = {(cuuint64_t)Cp, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-  const cuuint64_t strides[3] = {(cuuint64_t)Cp * 2, (cuuint64_t)W * Cp * 2, (cuuint64_t)H * W * Cp * 2};
-  const cuuint32_t box[4] = {TK, (cuuint32_t)bw, (cuuint32_t)bh, 1};
-  const cuuint32_t ones[4] = {1, 1, 1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, strides, box, ones,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    return RC_ERR_CUDA;
-  }
-  return RC_OK;
+  const unsigned long long dims[4] = {(unsigned long long)Cp, (unsigned long long)W, (unsigned long long)H, (unsigned long long)B};
+  const unsigned long long strides[3] = {(unsigned long long)Cp * 2, (unsigned long long)W * Cp * 2, (unsigned long long)H * W * Cp * 2};
+  const unsigned int box[4] = {TK, (unsigned int)bw, (unsigned int)bh, 1};
+  return encode_tmap_sw128(tm, base, 4, dims, strides, box, "rc_alt_corr_pyramid");
 }
 
 static int sm_count() {

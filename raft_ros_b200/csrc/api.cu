@@ -2,7 +2,10 @@
 // Argument validation + dispatch only; kernels live in the other translation units.
 #include <cstdarg>
 #include <cstdio>
+#include <cuda.h>
+
 #include <cmath>
+#include <mutex>
 #include <cstdlib>
 #include <initializer_list>
 
@@ -22,6 +25,42 @@ void set_error(const char *fmt, ...) {
 int cuda_fail(cudaError_t e, const char *what) {
   set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
   return RC_ERR_CUDA;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_tmap_sw128(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                      const unsigned long long *strides_bytes, const unsigned int *box, const char *who) {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  if (!fn) {
+    set_error("%s: cuTensorMapEncodeTiled is not available from the driver", who);
+    return RC_ERR_CUDA;
+  }
+  cuuint64_t d[5], st[4];
+  cuuint32_t b[5], ones[5] = {1, 1, 1, 1, 1};
+  for (int i = 0; i < rank; ++i) {
+    d[i] = dims[i];
+    b[i] = box[i];
+    if (i + 1 < rank) st[i] = strides_bytes[i];
+  }
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void *>(base), d, st, b, ones,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("%s: cuTensorMapEncodeTiled failed with CUresult %d", who, (int)r);
+    return RC_ERR_CUDA;
+  }
+  return RC_OK;
 }
 
 bool pdl_enabled() {

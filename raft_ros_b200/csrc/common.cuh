@@ -6,6 +6,8 @@
 
 #include "../../include/raftcorr.h"
 
+struct CUtensorMap_st;  // <cuda.h>'s tensor-map descriptor (CUtensorMap), forward-declared: not every file includes cuda.h
+
 namespace rc {
 
 // thread-local last-error string (set by the host entry points)
@@ -48,6 +50,12 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 #endif
+
+// cuTensorMapEncodeTiled fetched through the runtime (the library links no driver stub: it loads on a machine without a
+// driver); bf16 / 16-bit elements, SWIZZLE_128B, no interleave, zero fill outside the tensor.  `rank` entries of dims / box,
+// rank-1 of strides (bytes).  One definition for every tensor-core kernel of the library (api.cu).
+int encode_tmap_sw128(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                      const unsigned long long *strides_bytes, const unsigned int *box, const char *who);
 
 struct LevelPtrs {
   float *p[RC_MAX_LEVELS];

@@ -237,22 +237,6 @@ __global__ void conv1x1_prep_weight_kernel(const float *__restrict__ w, __nv_bfl
   }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
 }  // namespace fh
 
 size_t conv1x1_weight_bytes(int Cout, int Cin) { return (size_t)2 * Cout * ((Cin + 63) / 64 * 64) * 2; }
@@ -267,25 +251,13 @@ int launch_conv1x1_prep_weight(const float *w, void *wp, int Cout, int Cin, cuda
 int launch_conv1x1_prep(const float *x, const void *wp, const float *bias, void *hi, void *lo, int Bt, int Cin, int Cout, int HW,
                         cudaStream_t st) {
   using namespace fh;
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) {
-    set_error("cuTensorMapEncodeTiled is not available from the driver");
-    return RC_ERR_CUDA;
-  }
   const int Kp = (Cin + 63) / 64 * 64;
   CUtensorMap tm;
   {
-    const cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)Cout, 2};
-    const cuuint64_t strides[2] = {(cuuint64_t)Kp * 2, (cuuint64_t)Kp * 2 * Cout};
-    const cuuint32_t box[3] = {64, (cuuint32_t)Cout, 1};
-    const cuuint32_t ones[3] = {1, 1, 1};
-    CUresult cr = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(wp), dims, strides, box, ones,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (cr != CUDA_SUCCESS) {
-      set_error("rc_fnet_conv1x1_prep: cuTensorMapEncodeTiled failed with CUresult %d", (int)cr);
-      return RC_ERR_CUDA;
-    }
+    const unsigned long long dims[3] = {(unsigned long long)Kp, (unsigned long long)Cout, 2};
+    const unsigned long long strides[2] = {(unsigned long long)Kp * 2, (unsigned long long)Kp * 2 * Cout};
+    const unsigned int box[3] = {64, (unsigned int)Cout, 1};
+    if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_fnet_conv1x1_prep")) return rc;
   }
   Params P{};
   P.x = x;

@@ -297,40 +297,12 @@ fold_split_kernel(ConstLevelPtrs glv, __nv_bfloat16 *__restrict__ c_hi, __nv_bfl
 }
 
 // ---------------------------------------------------------------- host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
 static int map3(CUtensorMap *tm, void *base, cuuint64_t k, cuuint64_t rows, cuuint64_t batch, cuuint64_t pitch_elems,
                 cuuint64_t batch_stride_elems, cuuint32_t box_rows) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) {
-    set_error("cuTensorMapEncodeTiled is not available from the driver");
-    return RC_ERR_CUDA;
-  }
-  const cuuint64_t dims[3] = {k, rows, batch};
-  const cuuint64_t strides[2] = {pitch_elems * 2, batch_stride_elems * 2};
-  const cuuint32_t box[3] = {GK, box_rows, 1};
-  const cuuint32_t ones[3] = {1, 1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    return RC_ERR_CUDA;
-  }
-  return RC_OK;
+  const unsigned long long dims[3] = {k, rows, batch};
+  const unsigned long long strides[2] = {pitch_elems * 2, batch_stride_elems * 2};
+  const unsigned int box[3] = {GK, box_rows, 1};
+  return encode_tmap_sw128(tm, base, 3, dims, strides, box, "rc_corr_build_bwd");
 }
 
 static int sm_count() {

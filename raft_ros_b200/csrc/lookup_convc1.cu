@@ -412,22 +412,6 @@ __global__ void convc1_prep_weight_kernel(const float *__restrict__ w, unsigned 
   }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
 static int kp_of(int r) { return ((((2 * r + 1) * (2 * r + 1) + 15) / 16 + 3) / 4) * 64; }
 
 template <bool V16, int RR, bool BF16OPS>
@@ -459,25 +443,13 @@ int launch_convc1_prep_weight(const float *w, void *wp, int Cout, int L, int r, 
 int launch_lookup_convc1(const ConstLevelPtrs &lv, bool vol16, const float *coords, const void *wp, const float *bias,
                          float *out, int B, int h, int w, int L, int r, int Cout, int bf16_ops, cudaStream_t st) {
   using namespace fc;
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) {
-    set_error("cuTensorMapEncodeTiled is not available from the driver");
-    return RC_ERR_CUDA;
-  }
   const int KP = kp_of(r);
   CUtensorMap tm;
   {
-    const cuuint64_t dims[3] = {(cuuint64_t)L * KP, (cuuint64_t)Cout, 1};
-    const cuuint64_t strides[2] = {(cuuint64_t)L * KP * 2, (cuuint64_t)L * KP * 2 * Cout};
-    const cuuint32_t box[3] = {64, (cuuint32_t)Cout, 1};
-    const cuuint32_t ones[3] = {1, 1, 1};
-    CUresult cr = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(wp), dims, strides, box, ones,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (cr != CUDA_SUCCESS) {
-      set_error("rc_corr_lookup_convc1_fwd: cuTensorMapEncodeTiled failed with CUresult %d", (int)cr);
-      return RC_ERR_CUDA;
-    }
+    const unsigned long long dims[3] = {(unsigned long long)L * KP, (unsigned long long)Cout, 1};
+    const unsigned long long strides[2] = {(unsigned long long)L * KP * 2, (unsigned long long)L * KP * 2 * Cout};
+    const unsigned int box[3] = {64, (unsigned int)Cout, 1};
+    if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_corr_lookup_convc1_fwd")) return rc;
   }
   Params P{};
   P.lv = lv;
