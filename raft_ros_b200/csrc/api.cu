@@ -258,9 +258,9 @@ int rc_fnet_conv1x1_prep(const float *x, const void *wprep, const float *bias, v
   RC_CHECK_ARG(x && wprep && bias && hi, "rc_fnet_conv1x1_prep: null pointer");
   RC_CHECK_ARG(Bt > 0 && H > 0 && W > 0 && (long long)Bt * ((long long)H * W / 128 + 1) < 0x7fffffffLL, "rc_fnet_conv1x1_prep: bad sizes");
   if (int rc = check_conv1x1("rc_fnet_conv1x1_prep", Cout, Cin)) return rc;
-  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0 && (reinterpret_cast<uintptr_t>(hi) & 15) == 0 &&
-                   (reinterpret_cast<uintptr_t>(lo) & 15) == 0,
-               "rc_fnet_conv1x1_prep: wprep must be 128-byte aligned, hi / lo 16-byte aligned");
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0 && (reinterpret_cast<uintptr_t>(hi) & 127) == 0 &&
+                   (reinterpret_cast<uintptr_t>(lo) & 127) == 0,
+               "rc_fnet_conv1x1_prep: wprep, hi and lo must be 128-byte aligned");
   return launch_conv1x1_prep(x, wprep, bias, hi, lo, Bt, Cin, Cout, H * W, static_cast<cudaStream_t>(stream));
 }
 

@@ -53,8 +53,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ void sts128u(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
-__device__ __forceinline__ void stg128u(void *p, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
-  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+// one whole 32 B sector per thread (16 B pieces make the L1 send every sector twice, half masked)
+__device__ __forceinline__ void stg256u(void *p, const uint32_t (&a)[4], const uint32_t (&b)[4]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]),
+               "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3])
+               : "memory");
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -109,28 +112,27 @@ conv1x1_prep_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
       const int b = tile / P.tiles_per_b, pix = (tile - b * P.tiles_per_b) * TMPIX + prow;
       const bool pv = pix < P.HW;
       const float *xp = P.x + (size_t)b * P.Cin * P.HW + pix;
+      // all of this thread's channels are requested before it waits for the operand buffer, so the loads of tile
+      // t+1 are in flight while the MMAs of tile t run
+      float v[64];
+#pragma unroll
+      for (int i = 0; i < 64; ++i) v[i] = (pv && cbeg + i < cend) ? __ldg(xp + (size_t)(cbeg + i) * P.HW) : 0.0f;
       mbar_wait(a_empty, (it & 1) ^ 1);  // the MMAs of the previous tile have read the operand buffer
-#pragma unroll 1
-      for (int c0 = cbeg; c0 < cend; c0 += 32) {
-        float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = (pv && c0 + i < cend) ? __ldg(xp + (size_t)(c0 + i) * P.HW) : 0.0f;
+      for (int g = 0; g < 8; ++g) {
+        const int c = cbeg + 8 * g;
+        if (c < cend) {
+          uint32_t h[4], l[4];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int c = c0 + 8 * g;
-          if (c < cend) {
-            uint32_t h[4], l[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float a0 = v[8 * g + 2 * j], a1 = v[8 * g + 2 * j + 1];
-              const __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-              h[j] = *reinterpret_cast<const uint32_t *>(&hh);
-              l[j] = pack_bf16(a0 - __bfloat162float(hh.x), a1 - __bfloat162float(hh.y));
-            }
-            const uint32_t off = (uint32_t)((c >> 6) * A_KBLOCK) + rbase + (uint32_t)(((((c & 63) >> 3) ^ rx)) << 4);
-            sts128u(a_u32 + off, h[0], h[1], h[2], h[3]);
-            sts128u(a_u32 + kMaxKB * A_KBLOCK + off, l[0], l[1], l[2], l[3]);
+          for (int j = 0; j < 4; ++j) {
+            const float a0 = v[8 * g + 2 * j], a1 = v[8 * g + 2 * j + 1];
+            const __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+            h[j] = *reinterpret_cast<const uint32_t *>(&hh);
+            l[j] = pack_bf16(a0 - __bfloat162float(hh.x), a1 - __bfloat162float(hh.y));
           }
+          const uint32_t off = (uint32_t)((c >> 6) * A_KBLOCK) + rbase + (uint32_t)(((((c & 63) >> 3) ^ rx)) << 4);
+          sts128u(a_u32 + off, h[0], h[1], h[2], h[3]);
+          sts128u(a_u32 + kMaxKB * A_KBLOCK + off, l[0], l[1], l[2], l[3]);
         }
       }
       fence_proxy_async_smem();
@@ -155,17 +157,20 @@ conv1x1_prep_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
         tmem_ld_wait();
         if (pv) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint32_t h[4], l[4];
+          for (int g2 = 0; g2 < 2; ++g2) {  // 16 channels = one 32 B sector of the hi row and one of the lo row
+            uint32_t h[2][4], l[2][4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float a0 = v[8 * g + 2 * j] + bias_s[c0 + 8 * g + 2 * j], a1 = v[8 * g + 2 * j + 1] + bias_s[c0 + 8 * g + 2 * j + 1];
-              const __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
-              h[j] = *reinterpret_cast<const uint32_t *>(&hh);
-              l[j] = pack_bf16(a0 - __bfloat162float(hh.x), a1 - __bfloat162float(hh.y));
-            }
-            stg128u(P.hi + orow + c0 + 8 * g, h[0], h[1], h[2], h[3]);
-            if (P.lo) stg128u(P.lo + orow + c0 + 8 * g, l[0], l[1], l[2], l[3]);
+            for (int g = 0; g < 2; ++g)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int c = 16 * g2 + 8 * g + 2 * j;
+                const float a0 = v[c] + bias_s[c0 + c], a1 = v[c + 1] + bias_s[c0 + c + 1];
+                const __nv_bfloat162 hh = __floats2bfloat162_rn(a0, a1);
+                h[g][j] = *reinterpret_cast<const uint32_t *>(&hh);
+                l[g][j] = pack_bf16(a0 - __bfloat162float(hh.x), a1 - __bfloat162float(hh.y));
+              }
+            stg256u(P.hi + orow + c0 + 16 * g2, h[0], h[1]);
+            if (P.lo) stg256u(P.lo + orow + c0 + 16 * g2, l[0], l[1]);
           }
         }
       }
