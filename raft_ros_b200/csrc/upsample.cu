@@ -55,7 +55,7 @@ convex_upsample_kernel(const float *__restrict__ flow, const float *__restrict__
         float s = 0.0f, u0 = 0.0f, u1 = 0.0f;
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
-          const float e = expf(m[k] - mx);
+          const float e = __expf(m[k] - mx);  // ex2.approx: 2^-22 relative, far inside the 2e-6 bound; the kernel is issue-bound on this
           s += e;
           u0 = fmaf(e, f0[k], u0);
           u1 = fmaf(e, f1[k], u1);
