@@ -990,3 +990,27 @@ def test_cta_pair_on_the_fly_variant_in_a_subprocess(rr):
                         "-k", "alternate_block_vs_oracle or alternate_block_radius3", "-p", "no:cacheprovider"],
                        capture_output=True, text=True, env=env, cwd=root, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_alt_pyramid_one_call_entry_point(rr):
+    """rc_alt_corr_pyramid_fwd (maps described and kernel launched in one call) gives what the setup-once / run pair behind
+    AlternateCorrBlock gives, through the C ABI with raw pointers."""
+    from raft_ros_b200 import _lib
+    L_ = _lib.lib()
+    B, D, H, W, nl = 1, 128, 27, 40, 4
+    rng = np.random.default_rng(27)
+    f1 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    coords = t(make_coords("sigma4", B, H, W, rng))
+    blk = rr.AlternateCorrBlock(f1, f2, num_levels=nl, radius=4, precision="bf16x3")
+    want = blk(coords)
+    out = torch.full_like(want, float("nan"))
+    nbytes = int(L_.rc_alt_corr_pyramid_plan_bytes(B, H, W, nl))
+    plan = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    rc = L_.rc_alt_corr_pyramid_fwd(blk._f1_tc[0].data_ptr(), blk._f1_tc[1].data_ptr(),
+                                    _lib.ptr_array([x[0].data_ptr() for x in blk._f2_tc]),
+                                    _lib.ptr_array([x[1].data_ptr() for x in blk._f2_tc]), coords.data_ptr(), out.data_ptr(),
+                                    B, H, W, D, nl, 4, 1, 0.0, plan.data_ptr(), nbytes, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L_.rc_last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
