@@ -86,7 +86,7 @@ using namespace rc;
 
 extern "C" {
 
-int rc_version(void) { return 100; }
+int rc_version(void) { return 200; }
 
 const char *rc_last_error(void) { return g_err; }
 
