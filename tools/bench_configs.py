@@ -72,6 +72,9 @@ def fwd_case(name, B, D, h, w, K, precisions=("bf16x3", "bf16", "bf16_vol16")):
         out["torch_ops_on_gpu_pairs_per_s"] = B / (ms * 1e-3)
     except torch.cuda.OutOfMemoryError:
         out["torch_ops_on_gpu_ms"] = None
+    except RuntimeError as e:  # e.g. cuDNN's grid_sample refuses the (B*h*w = 469 248)-image batch of config 3 at batch 64
+        out["torch_ops_on_gpu_ms"] = None
+        out["torch_ops_on_gpu_error"] = str(e).splitlines()[0][:160]
     print(json.dumps(out), flush=True)
 
 
@@ -156,6 +159,8 @@ if __name__ == "__main__":
         fwd_case("sintel_440x1024_b8_k32", 8, 256, 55, 128, 32)
     if "kitti" in which:
         fwd_case("kitti_376x1248_b8_k24", 8, 256, 47, 156, 24)
+    if "kitti64" in which:  # config 3 as BASELINE.json states it: 64 pairs on ONE GPU (18 GB pyramid)
+        fwd_case("kitti_376x1248_b64_k24", 64, 256, 47, 156, 24, precisions=("bf16x3", "bf16_vol16"))
     if "train" in which:
         train_case()
     if "altsmall" in which:
