@@ -45,6 +45,33 @@ def case(name, D, radius, h, w, K=20):
     with torch.cuda.graph(graph):
         step()
     out["cuda_graph_ms"] = wall(graph.replay)
+    # per-call device time of the per-iteration pieces at this size (CUDA events around 50 back-to-back calls)
+    blk = rr.CorrBlock(f1, f2, radius=radius)
+    cout = 256 if radius == 4 else 96
+    cin = 4 * (2 * radius + 1) ** 2
+    W = (torch.randn(cout, cin, generator=g) / cin ** 0.5).to(DEV)
+    bias = torch.zeros(cout, device=DEV)
+
+    def dev_us(fn, reps=50):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for _ in range(reps):
+                fn()
+        gr.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(True), torch.cuda.Event(True)
+        a.record()
+        gr.replay()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps * 1e3
+
+    out["lookup_us"] = dev_us(lambda: blk(coords[0]))
+    out["lookup_convc1_fused_us"] = dev_us(lambda: blk.lookup_convc1(coords[0], W, bias))
+    out["build_us"] = dev_us(lambda: rr.CorrBlock(f1, f2, radius=radius), reps=10)
     try:
         from oracle import build_ref_core
         core = build_ref_core.load()
