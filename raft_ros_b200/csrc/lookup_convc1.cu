@@ -174,17 +174,19 @@ lookup_convc1_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
       const size_t grp = (size_t)c.b * ng + c.p0 / G;
       const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg / PC) & 1;
       const size_t gwords = (size_t)(hp * wp) * G / (V16 ? 2 : 1);
-      const float *base = pick_level(P.lv, c.lvl) + grp * gwords + ((cg / CW) * (16 * G) + u * 16);
+      const float *ibase = pick_level(P.lv, c.lvl) + grp * gwords + u * 16;  // always inside the level
       const int trs = tpr * 16 * G;
       const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);
+      // two arithmetic sequences of offsets (r even / r odd), as in lookup_tiled.cu
+      const int par = c.y0 & 1, t0 = (c.y0 >> 1) * trs + (cg / CW) * (16 * G);
+      const int tA = t0 + (par ? pos1 : pos0), tB = t0 + (par ? trs + pos0 : pos1);
       constexpr uint32_t RB = V16 ? 48u : (uint32_t)PS * 4u;
       const uint32_t dst = patch_u32 + dst_lane;
 #pragma unroll
       for (int r = 0; r < PN; ++r) {
-        const int ya = c.y0 + r;
-        const bool ok = okx && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
-        if (!V16 || tc < 3) copy16(dst + (uint32_t)r * RB, ok ? base + off : pick_level(P.lv, 0), ok);
+        const bool ok = okx && (unsigned)(c.y0 + r) < (unsigned)hl;
+        const int rel = ((r & 1) ? tB : tA) + (r >> 1) * trs;
+        if (!V16 || tc < 3) copy16(dst + (uint32_t)r * RB, ibase + (ok ? rel : 0), ok);
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };

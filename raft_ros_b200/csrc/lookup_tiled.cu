@@ -161,18 +161,22 @@ lookup_tiled_fwd_kernel(ConstLevelPtrs lv, const float *__restrict__ coords, flo
       const size_t grp = (size_t)c.b * ng + c.p0 / G;
       const int u = c.p0 % G + tu, sw = (u >> 1) & 3, half = (cg / PC) & 1;
       const size_t gwords = (size_t)(hp * wp) * G / (V16 ? 2 : 1);
-      const float *base = pick_level(lv, c.lvl) + grp * gwords + ((cg / CW) * (16 * G) + u * 16);
+      // this pixel's slot in its group: always inside the level, so it doubles as the (unread) source of zero fills
+      const float *ibase = pick_level(lv, c.lvl) + grp * gwords + u * 16;
       const int trs = tpr * 16 * G;  // words per tile-row of a group
       const int pos0 = ((half ^ sw) << 2), pos1 = (((2 | half) ^ sw) << 2);  // chunk position for even / odd rows
+      // window row r is level row y0 + r: rows alternate between the two chunk positions and advance one tile-row
+      // every second row, so the offsets are two arithmetic sequences (A: r even, B: r odd)
+      const int par = c.y0 & 1, t0 = (c.y0 >> 1) * trs + (cg / CW) * (16 * G);
+      const int tA = t0 + (par ? pos1 : pos0), tB = t0 + (par ? trs + pos0 : pos1);
       constexpr unsigned RB = V16 ? 48u : (unsigned)PS * 4u;  // bytes per patch row in shared memory
       const unsigned dst = ring_u32 + (unsigned)(stage * kTlStageFloats) * 4u + dst_lane;
 #pragma unroll
       for (int r = 0; r < PN; ++r) {
-        const int ya = c.y0 + r;
-        const bool ok = okx && (unsigned)ya < (unsigned)hl;
-        const int off = ok ? (ya >> 1) * trs + ((ya & 1) ? pos1 : pos0) : 0;
+        const bool ok = okx && (unsigned)(c.y0 + r) < (unsigned)hl;
+        const int rel = ((r & 1) ? tB : tA) + (r >> 1) * trs;
         // (fp16 rows hold three pieces: the 4th lane of a pixel has nothing to write)
-        if (!V16 || tc < 3) copy16(dst + (unsigned)r * RB, ok ? base + off : pick_level(lv, 0), ok);
+        if (!V16 || tc < 3) copy16(dst + (unsigned)r * RB, ibase + (ok ? rel : 0), ok);
       }
     }
     cp_async_commit();  // always commit (possibly empty) so that the wait counts stay uniform
