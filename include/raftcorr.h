@@ -349,6 +349,29 @@ int rc_alt_corr_bwd_det(const float *fmap1, const float *fmap2, const float *coo
                         int radius, void *workspace, size_t workspace_bytes, void *stream);
 
 /*
+ * Stride-1 "same" convolution + bias + activation on tensor cores: the convolutions of the per-iteration update
+ * (core/update.py: convc2 / convf2 / conv of the motion encoder :84-97, the 1x5 / 5x1 gates of SepConvGRU :33-60, the
+ * flow head :6-14 and the mask head :122-125), i.e. what follows rc_corr_lookup_convc1_fwd in an iteration.
+ *     out[b, o, y, x] = act(bias[o] + sum_{c, ky, kx} weight[o, c, ky, kx] * in[b, c, y + ky - KH/2, x + kx - KW/2])
+ *   x1, C1, x2 : the input is the channel concatenation of x1 (B, C1, H, W) and x2 (B, Cin - C1, H, W), both fp32
+ *                NCHW, read in place (the reference's torch.cat copies); x2 = NULL and C1 = Cin for one tensor
+ *   wprep      : weight (Cout, Cin, KH, KW) fp32 converted once per model by rc_conv_prep_weight into
+ *                rc_conv_weight_bytes() bytes (fp16, [channel block][tap][Cout][64])
+ *   bias       : (Cout) fp32 or NULL;   act : RC_ACT_*;   out : (B, Cout, H, W) fp32
+ * Cout a multiple of 16, <= 256 (wider layers: call per slice of output channels); KH, KW odd with a halo tile of at
+ * most 640 pixels: KH * (128 + KW - 1) for KW > 1, (8 + KH - 1) * 16 for KW = 1 (1x1, 3x3, 1x5, 5x1, 3x1, 1x3, ...).  Operands are rounded to fp16 (saturating), one pass,
+ * fp32 accumulation: the class of TF32, which is what cuDNN runs these layers in by torch's default.  Forward only.
+ */
+#define RC_ACT_NONE 0
+#define RC_ACT_RELU 1
+#define RC_ACT_SIGMOID 2
+#define RC_ACT_TANH 3
+size_t rc_conv_weight_bytes(int Cout, int Cin, int KH, int KW);
+int rc_conv_prep_weight(const float *weight, void *wprep, int Cout, int Cin, int KH, int KW, void *stream);
+int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, const float *bias, float *out, int B,
+                  int Cin, int Cout, int H, int W, int KH, int KW, int act, void *stream);
+
+/*
  * RAFT.upsample_flow (core/raft.py:72-83): convex 8x upsampling of the flow field, one launch instead of
  * view / softmax / unfold / mul / sum / permute / reshape with their temporaries:
  *     out[n, c, 8y+i, 8x+j] = sum_k softmax_k(mask[n, k*64 + i*8 + j, y, x]) * 8 * flow[n, c, y + k/3 - 1, x + k%3 - 1]

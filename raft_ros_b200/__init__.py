@@ -11,7 +11,7 @@ everything else of RAFT stays the reference's own torch code.
 """
 from . import alt_cuda_corr  # noqa: F401
 from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION, PreparedFeatures, encoder_head  # noqa: F401
-from .utils import bilinear_sampler, coords_grid, upsample_flow  # noqa: F401
+from .utils import bilinear_sampler, conv2d_act, coords_grid, upsample_flow  # noqa: F401
 
 __all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr", "encoder_head",
-           "PreparedFeatures", "upsample_flow"]
+           "PreparedFeatures", "upsample_flow", "conv2d_act"]

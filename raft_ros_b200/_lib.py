@@ -126,6 +126,9 @@ SIGNATURES = {
     "rc_alt_corr_pyramid_fwd": (_i, [_vp, _vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i,
                                      _i, _f, _vp, _sz, _vp]),
     "rc_alt_corr_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_conv_weight_bytes": (_sz, [_i, _i, _i, _i]),
+    "rc_conv_prep_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "rc_conv2d_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_convex_upsample_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "rc_alt_corr_bwd_det_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "rc_alt_corr_bwd_det": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),

@@ -487,6 +487,37 @@ int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
                         W2, C, radius, static_cast<cudaStream_t>(stream));
 }
 
+static int check_conv(const char *fn, int Cout, int Cin, int KH, int KW) {
+  RC_CHECK_ARG(Cout > 0 && Cout <= 256 && Cout % 16 == 0, "%s: Cout %d must be a multiple of 16, at most 256", fn, Cout);
+  RC_CHECK_ARG(Cin > 0 && Cin <= 4096, "%s: Cin %d out of range", fn, Cin);
+  RC_CHECK_ARG(KH > 0 && KW > 0 && (KH & 1) && (KW & 1) && (KW == 1 ? (8 + KH - 1) * 16 : KH * (128 + KW - 1)) <= 640,
+               "%s: %dx%d filters unsupported (odd sizes whose halo tile fits 640 pixels: 1x1, 3x3, 1x5, KHx1 up to 33x1, ...)", fn, KH, KW);
+  return RC_OK;
+}
+
+size_t rc_conv_weight_bytes(int Cout, int Cin, int KH, int KW) {
+  if (Cout <= 0 || Cin <= 0 || KH <= 0 || KW <= 0) return 0;
+  return conv_weight_bytes(Cout, Cin, KH, KW);
+}
+
+int rc_conv_prep_weight(const float *weight, void *wprep, int Cout, int Cin, int KH, int KW, void *stream) {
+  RC_CHECK_ARG(weight && wprep, "rc_conv_prep_weight: null pointer");
+  if (int rc = check_conv("rc_conv_prep_weight", Cout, Cin, KH, KW)) return rc;
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_conv_prep_weight: wprep must be 128-byte aligned");
+  return launch_conv_prep_weight(weight, wprep, Cout, Cin, KH, KW, static_cast<cudaStream_t>(stream));
+}
+
+int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, const float *bias, float *out, int B, int Cin,
+                  int Cout, int H, int W, int KH, int KW, int act, void *stream) {
+  RC_CHECK_ARG(x1 && wprep && out, "rc_conv2d_fwd: null pointer");
+  RC_CHECK_ARG(B > 0 && H > 0 && W > 0 && (long long)B * H * ((W + 127) / 128) < 0x7fffffffLL, "rc_conv2d_fwd: bad sizes");
+  if (int rc = check_conv("rc_conv2d_fwd", Cout, Cin, KH, KW)) return rc;
+  RC_CHECK_ARG(C1 > 0 && C1 <= Cin && (C1 == Cin || x2 != nullptr), "rc_conv2d_fwd: C1 = %d of Cin = %d needs a second input", C1, Cin);
+  RC_CHECK_ARG(act >= RC_ACT_NONE && act <= RC_ACT_TANH, "rc_conv2d_fwd: unknown activation %d", act);
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_conv2d_fwd: wprep must be 128-byte aligned");
+  return launch_conv_tc(x1, C1, x2, wprep, bias, out, B, Cin, Cout, H, W, KH, KW, act, static_cast<cudaStream_t>(stream));
+}
+
 int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int N, int H, int W, void *stream) {
   RC_CHECK_ARG(flow && mask && out, "rc_convex_upsample_fwd: null pointer");
   RC_CHECK_ARG(N > 0 && H > 0 && W > 0 && (long long)N * H * W < 0x7fffffffLL / 64, "rc_convex_upsample_fwd: bad sizes");

@@ -132,6 +132,10 @@ int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi
                   const float *coords, float *out, int B, int H1, int W1, int Cp, int L, int radius,
                   int precision, float scale, void *plan_ws, size_t plan_bytes, cudaStream_t st);
 int launch_pool_tail(const LevelPtrs &lv, int B, int h, int w, int first, int L, cudaStream_t st);
+size_t conv_weight_bytes(int Cout, int Cin, int KH, int KW);
+int launch_conv_prep_weight(const float *w, void *wp, int Cout, int Cin, int KH, int KW, cudaStream_t st);
+int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, const float *bias, float *out, int B, int Cin, int Cout,
+                   int H, int W, int KH, int KW, int act, cudaStream_t st);
 int launch_convex_upsample(const float *flow, const float *mask, float *out, int N, int H, int W, cudaStream_t st);
 int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
                         int H, int W, int Ho, int Wo, cudaStream_t st);

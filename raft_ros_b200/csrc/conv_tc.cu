@@ -1,0 +1,288 @@
+// Stride-1 "same" convolutions of the per-iteration update (reference core/update.py: the motion encoder's convc2 /
+// convf2 / conv, SepConvGRU's 1x5 and 5x1 gates, the flow and mask heads) as an implicit GEMM on tcgen05 whose filter
+// taps cost no copies:
+//
+//     out[b, o, y, x] = act( bias[o] + sum_{c, ky, kx} W[o, c, ky, kx] * in[b, c, y + ky - KH/2, x + kx - KW/2] )
+//
+// A tile is 128 output pixels: one row segment (or 8 rows x 16 columns when the filter is one column wide).  Converter warps read the input once per 64-channel block
+// (NCHW fp32, coalesced along x), round it to fp16 and lay the tile WITH ITS HALO -- KH rows of 128 + KW - 1 pixels --
+// out in shared memory as K-major SWIZZLE_128B operand rows (one 128 B row per halo pixel).  Filter tap (ky, kx) then
+// is the SAME buffer read from row ky * (128 + KW - 1) + kx on: the A descriptor of each tap's MMAs just starts that
+// many rows (x 128 B) later -- the 128 B swizzle is a function of the shared-memory address alone, so a start that is
+// not on a 1024 B boundary reads the rows exactly as they were written (base-offset field 0; measured: setting it to the
+// start row's phase gives wrong results) -- and the KH * KW taps re-use one conversion.  Weights ([tap][Cout][64] fp16 blocks, prepared once per model) stream from L2 through a TMA ring;
+// the accumulator (128 pixels x Cout <= 256, fp32) lives in TMEM, double-buffered; the epilogue (thread <-> pixel) adds
+// the bias, applies the activation and writes NCHW fp32, one coalesced 128 B store per channel and warp.  The input
+// may be the channel concatenation of two tensors (core/update.py:41,47,52,58,95,134 `torch.cat([...], dim=1)`), read in
+// place.  Operands are fp16 (11-bit mantissa: the class of TF32, which is what cuDNN runs these convolutions in by
+// torch's default, and of the reference's --mixed_precision autocast), one pass, fp32 accumulation.
+//
+// One CTA per SM, persistent, 14 warps: 0-7 converters, 8-11 epilogue, 12 weight TMA, 13 MMA issue.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace rc {
+namespace cv {
+
+using namespace tc;
+
+constexpr int kConvWarps = 8, kEpiWarps = 4, kProducerWarp = 12, kMmaWarp = 13, kThreads = 14 * 32;
+constexpr int TMPIX = 128;
+constexpr int kMaxHaloPix = 640;                    // 5 rows x 128 (5x1), 3 x 130 (3x3), 1 x 132 (1x5)
+constexpr int kHaloBytes = kMaxHaloPix * 128;       // one 64-channel block of the halo tile: 80 KB
+constexpr int W_BLOCK = 256 * 64 * 2;               // one weight block: up to 256 rows x 64 K
+constexpr int kSmemBytes = 1024 + 2 * kHaloBytes + 2 * W_BLOCK + 1024 /*bias*/ + 256;
+static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+
+struct Params {
+  const float *x1, *x2;  // input = channels [0, C1) of x1 followed by [0, Cin - C1) of x2 (x2 may be null)
+  const float *bias;
+  float *out;
+  int B, C1, Cin, Cout, H, W, KH, KW, act;
+  int TH, TW;  // output tile: TH rows x TW columns = 128 pixels (1 x 128, or 8 x 16 for filters one column wide)
+  int ncb, tiles_x, tiles_y, total_tiles;
+};
+
+__device__ __forceinline__ float activate(float v, int act) {
+  switch (act) {
+    case RC_ACT_RELU: return fmaxf(v, 0.0f);
+    case RC_ACT_SIGMOID: return 1.0f / (1.0f + __expf(-v));
+    case RC_ACT_TANH: return tanhf(v);
+    default: return v;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = smem_u32(smem_raw);
+  const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
+  uint8_t *smem = smem_raw + (base_u32 - raw_u32);
+  const uint32_t halo_u32 = base_u32, w_u32 = base_u32 + 2 * kHaloBytes;
+  float *bias_s = reinterpret_cast<float *>(smem + 2 * kHaloBytes + 2 * W_BLOCK);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(bias_s + 256);
+  uint64_t *h_full = bars, *h_empty = bars + 2, *w_full = bars + 4, *w_empty = bars + 6, *acc_full = bars + 8,
+           *acc_empty = bars + 10;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 12);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int KH = P.KH, KW = P.KW, T = KH * KW, ph = KH >> 1, pw = KW >> 1;
+  const int TH = P.TH, TW = P.TW;
+  const int RW = TW + 2 * pw, HP = (TH + 2 * ph) * RW;  // halo tile: TH + KH - 1 rows of RW pixels
+  const int Cout = P.Cout, H = P.H, W = P.W;
+  const size_t HW = (size_t)H * W;
+  pdl_launch_dependents();
+
+  if (warp == kProducerWarp && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&h_full[i], kConvWarps);
+      mbar_init(&h_empty[i], 1);
+      mbar_init(&w_full[i], 1);
+      mbar_init(&w_empty[i], 1);
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], kEpiWarps);
+    }
+    fence_barrier_init();
+    prefetch_tmap(&tmW);
+  }
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
+  pdl_wait();
+  for (int i = threadIdx.x; i < 256; i += kThreads) bias_s[i] = (i < Cout && P.bias) ? __ldg(P.bias + i) : 0.0f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < kConvWarps) {
+    // ===================== converters: input tile with halo -> fp16 operand rows, one 64-channel block at a time =====================
+    const int tid = threadIdx.x;
+    uint32_t n = 0;  // channel blocks done (over all tiles): buffer n & 1
+    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+      const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
+      const int x0 = txi * TW, y = tyi * TH;
+      for (int cb = 0; cb < P.ncb; ++cb, ++n) {
+        const uint32_t buf = n & 1;
+        mbar_wait(&h_empty[buf], ((n >> 1) & 1) ^ 1);  // the MMAs that read this buffer two blocks ago are done
+        const uint32_t hb = halo_u32 + buf * kHaloBytes;
+        for (int it = tid; it < HP * 8; it += kConvWarps * 32) {
+          const int c8 = it / HP, hi = it - c8 * HP;       // 8-channel chunk, halo pixel (consecutive threads: consecutive pixels)
+          const int r = hi / RW, xx = hi - r * RW;
+          const int iy = y - ph + r, ix = x0 - pw + xx;
+          const bool inside = (unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W;
+          const int c0 = cb * 64 + c8 * 8;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int c = c0 + j;
+            const float *src = c < P.C1 ? P.x1 + ((size_t)b * P.C1 + c) * HW : P.x2 + ((size_t)b * (P.Cin - P.C1) + (c - P.C1)) * HW;
+            v[j] = (inside && c < P.Cin) ? __ldg(src + (size_t)iy * W + ix) : 0.0f;
+          }
+          uint32_t w4[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w4[j]) : "f"(v[2 * j + 1]), "f"(v[2 * j]));
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + (uint32_t)hi * 128u + (uint32_t)((c8 ^ (hi & 7)) << 4)),
+                       "r"(w4[0]), "r"(w4[1]), "r"(w4[2]), "r"(w4[3])
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&h_full[buf]);
+      }
+    }
+  } else if (warp < kConvWarps + kEpiWarps) {
+    // ===================== epilogue: bias + activation, thread <-> pixel =====================
+    const int e = warp - kConvWarps;
+    int acc = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+      const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
+      const int m = e * 32 + lane;  // output pixel of the tile, row-major
+      const int y = tyi * TH + m / TW, x = txi * TW + m % TW;
+      const bool pv = x < W && y < H;
+      mbar_wait(&acc_full[acc], phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(acc * 256);
+      float *o = P.out + (size_t)b * Cout * HW + (size_t)y * W + x;
+      int c0 = 0;
+      for (; c0 + 32 <= Cout; c0 += 32) {
+        float v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        if (pv) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bias_s[c0 + i], P.act));
+        }
+      }
+      if (c0 < Cout) {  // Cout is a multiple of 16
+        float v[16];
+        tmem_ld16(taddr + c0, v);
+        tmem_ld_wait();
+        if (pv) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bias_s[c0 + i], P.act));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      acc ^= 1;
+      if (acc == 0) phase ^= 1;
+    }
+  } else if (warp == kProducerWarp) {
+    // ===================== weight blocks [Cout][64] of (channel block, tap): L2 -> shared memory =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+        for (int cb = 0; cb < P.ncb; ++cb)
+          for (int t = 0; t < T; ++t) {
+            mbar_wait(&w_empty[stage], phase ^ 1);
+            mbar_expect_tx(&w_full[stage], (uint32_t)Cout * 128u);
+            tma_load_3d(smem + 2 * kHaloBytes + stage * W_BLOCK, &tmW, &w_full[stage], 0, 0, cb * T + t);
+            if (++stage == 2) { stage = 0; phase ^= 1; }
+          }
+    }
+  } else {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      // kind::f16: D = f32, A = B = f16, K-major, M = 128, N = Cout
+      const uint32_t idesc = (1u << 4) | ((uint32_t)(Cout >> 3) << 17) | ((uint32_t)(TMPIX >> 4) << 24);
+      int ws = 0, acc = 0;
+      uint32_t wphase = 0, accphase = 0, n = 0;
+      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+        mbar_wait(&acc_empty[acc], accphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+        uint32_t first = 1;
+        for (int cb = 0; cb < P.ncb; ++cb, ++n) {
+          const uint32_t buf = n & 1;
+          mbar_wait(&h_full[buf], (n >> 1) & 1);
+          tc_fence_after();
+          const uint32_t hb = halo_u32 + buf * kHaloBytes;
+          for (int t = 0; t < T; ++t) {
+            const int ky = t / KW, kx = t - ky * KW;
+            mbar_wait(&w_full[ws], wphase);
+            tc_fence_after();
+            // tap (ky, kx): the tile's 128 output pixels (row-major) see halo pixels ky * RW + kx .. + 127 -- consecutive
+            // because the tile is a single row (RW = TW + KW - 1 only matters within it) or the filter a single column (RW = TW)
+            const uint64_t adesc = make_sw128_desc(hb + (uint32_t)(ky * RW + kx) * 128u);
+            const uint64_t bdesc = make_sw128_desc(w_u32 + ws * W_BLOCK);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, first ? 0u : 1u);
+              first = 0;
+            }
+            umma_commit(&w_empty[ws]);
+            if (++ws == 2) { ws = 0; wphase ^= 1; }
+          }
+          umma_commit(&h_empty[buf]);
+        }
+        umma_commit(&acc_full[acc]);
+        acc ^= 1;
+        if (acc == 0) accphase ^= 1;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+}
+
+// weights (Cout, Cin, KH, KW) fp32 -> [channel block][tap][Cout][64] fp16, channels beyond Cin zero
+__global__ void conv_prep_weight_kernel(const float *__restrict__ w, unsigned short *__restrict__ wp, int Cout, int Cin, int T, int ncb) {
+  const int total = ncb * T * Cout * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c64 = i & 63, o = (i >> 6) % Cout, bt = (i >> 6) / Cout, t = bt % T, cb = bt / T;
+    const int c = cb * 64 + c64;
+    const float v = c < Cin ? __ldg(w + ((size_t)o * Cin + c) * T + t) : 0.0f;
+    unsigned short r;
+    asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
+    wp[i] = r;
+  }
+}
+
+}  // namespace cv
+
+size_t conv_weight_bytes(int Cout, int Cin, int KH, int KW) { return (size_t)((Cin + 63) / 64) * KH * KW * Cout * 64 * 2; }
+
+int launch_conv_prep_weight(const float *w, void *wp, int Cout, int Cin, int KH, int KW, cudaStream_t st) {
+  const int ncb = (Cin + 63) / 64, T = KH * KW;
+  const int total = ncb * T * Cout * 64;
+  cv::conv_prep_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, static_cast<unsigned short *>(wp), Cout, Cin, T, ncb);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, const float *bias, float *out, int B, int Cin, int Cout,
+                   int H, int W, int KH, int KW, int act, cudaStream_t st) {
+  using namespace cv;
+  const int ncb = (Cin + 63) / 64, T = KH * KW;
+  CUtensorMap tm;
+  {
+    const unsigned long long dims[3] = {64, (unsigned long long)Cout, (unsigned long long)ncb * T};
+    const unsigned long long strides[2] = {128, 128ull * Cout};
+    const unsigned int box[3] = {64, (unsigned int)Cout, 1};
+    if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_conv2d_fwd")) return rc;
+  }
+  Params P{};
+  P.x1 = x1; P.x2 = x2; P.bias = bias; P.out = out;
+  P.B = B; P.C1 = C1; P.Cin = Cin; P.Cout = Cout; P.H = H; P.W = W; P.KH = KH; P.KW = KW; P.act = act;
+  P.ncb = ncb;
+  if (KW == 1 && KH > 1) { P.TH = 8; P.TW = 16; }  // vertical filters: a square-ish tile keeps the halo at 1.5x instead of KH x
+  else { P.TH = 1; P.TW = TMPIX; }
+  P.tiles_x = (W + P.TW - 1) / P.TW;
+  P.tiles_y = (H + P.TH - 1) / P.TH;
+  P.total_tiles = B * P.tiles_y * P.tiles_x;
+  RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  int dev = 0, sms = 148;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = P.total_tiles < sms ? P.total_tiles : sms;
+  RC_CUDA(launch_pdl(conv_tc_kernel, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, P));
+  return RC_OK;
+}
+
+}  // namespace rc

@@ -88,3 +88,57 @@ def upsample_flow(flow, mask):
                                                torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "rc_convex_upsample_fwd")
     return out
+
+
+_ACTS = {None: 0, "none": 0, "relu": 1, "sigmoid": 2, "tanh": 3}
+_CONV_CACHE = None
+
+
+def conv2d_act(x, weight, bias=None, act=None):
+    """`act(F.conv2d(x, weight, bias, padding="same"))` for the stride-1 convolutions of the per-iteration update
+    (reference core/update.py:6-14,33-60,84-97,122-125) on tensor cores (rc_conv2d_fwd): filter taps re-use one fp16
+    conversion of the input tile, bias and activation are fused, and `x` may be a tuple (a, b) standing for
+    `torch.cat([a, b], dim=1)` without the copy.  weight (Cout, Cin, KH, KW) with KH x KW in 1x1, 3x3, 1x5, 5x1;
+    act in None / "relu" / "sigmoid" / "tanh".  fp16 operands (TF32-class), fp32 accumulate and output.  Inference only."""
+    global _CONV_CACHE
+    from .corr import _WeightCache
+    if _CONV_CACHE is None:
+        _CONV_CACHE = _WeightCache()
+    xs = x if isinstance(x, (tuple, list)) else (x,)
+    if len(xs) not in (1, 2) or any((not t.is_cuda) or t.dim() != 4 for t in xs) or not weight.is_cuda:
+        raise RuntimeError("conv2d_act: x must be one or two (B,C,H,W) CUDA tensors and weight a CUDA tensor")
+    if torch.is_grad_enabled() and (any(t.requires_grad for t in xs) or weight.requires_grad):
+        raise RuntimeError("conv2d_act: inference only (no gradient); use torch's convolution for training")
+    if act not in _ACTS:
+        raise ValueError(f"act must be one of {sorted(k for k in _ACTS if k)}, got {act!r}")
+    xs = [t.detach().float().contiguous() for t in xs]
+    B, C1, H, W = xs[0].shape
+    Cin = C1 + (xs[1].shape[1] if len(xs) == 2 else 0)
+    if len(xs) == 2 and (xs[1].shape[0] != B or xs[1].shape[2:] != xs[0].shape[2:]):
+        raise RuntimeError("conv2d_act: the two inputs must agree in batch and spatial size")
+    if weight.dim() != 4 or weight.shape[1] != Cin:
+        raise RuntimeError(f"conv2d_act: weight must be (Cout, {Cin}, KH, KW), got {tuple(weight.shape)}")
+    Cout, _, KH, KW = weight.shape
+    L = _lib.lib()
+    dev = xs[0].device
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        outs = []
+        for o0 in range(0, Cout, 256):  # wider layers (the mask head's 576 channels) go slice by slice
+            o1 = min(Cout, o0 + 256)
+
+            def make(o0=o0, o1=o1):
+                nbytes = int(L.rc_conv_weight_bytes(o1 - o0, Cin, KH, KW))
+                wp_ = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+                w32 = weight.detach()[o0:o1].float().contiguous()
+                _lib.check(L.rc_conv_prep_weight(w32.data_ptr(), wp_.data_ptr(), o1 - o0, Cin, KH, KW, st), "rc_conv_prep_weight")
+                return wp_
+
+            wp = _CONV_CACHE.get(weight, ("conv", o0, dev.index), make)
+            b32 = None if bias is None else bias.detach()[o0:o1].float().contiguous()
+            out = torch.empty((B, o1 - o0, H, W), dtype=torch.float32, device=dev)
+            rc = L.rc_conv2d_fwd(xs[0].data_ptr(), C1, xs[1].data_ptr() if len(xs) == 2 else None, wp.data_ptr(),
+                                 None if b32 is None else b32.data_ptr(), out.data_ptr(), B, Cin, o1 - o0, H, W, KH, KW, _ACTS[act], st)
+            _lib.check(rc, "rc_conv2d_fwd")
+            outs.append(out)
+    return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
