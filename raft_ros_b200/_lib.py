@@ -22,6 +22,7 @@ RC_PREC_FP32 = 0
 RC_PREC_BF16X3 = 1
 RC_PREC_BF16 = 2
 RC_PREC_BF16_VOL16 = 3
+RC_PREC_FP16_FP8 = 4
 RC_MAX_LEVELS = 8
 RC_MAX_RADIUS = 8
 

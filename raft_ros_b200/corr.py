@@ -18,7 +18,7 @@ import torch
 from . import _lib
 
 _PRECISIONS = {"fp32": _lib.RC_PREC_FP32, "bf16x3": _lib.RC_PREC_BF16X3, "bf16": _lib.RC_PREC_BF16,
-               "bf16_vol16": _lib.RC_PREC_BF16_VOL16}
+               "bf16_vol16": _lib.RC_PREC_BF16_VOL16, "fp16_fp8": _lib.RC_PREC_FP16_FP8}
 
 #: arithmetic of the all-pairs contraction when the caller does not say: "bf16x3" is the
 #: fp32-class tensor-core path (error-compensated bf16 operands, ~1e-5 normwise), "bf16" the
@@ -540,6 +540,8 @@ class CorrBlock:
             if not tiled or (torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)):
                 raise RuntimeError("precision 'bf16_vol16' is an inference mode for radius 3 or 4 and at most 4 levels "
                                    "(tiled layout); use 'bf16' or 'bf16x3' here")
+        if _precision_code(precision) == _lib.RC_PREC_FP16_FP8 and torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            raise RuntimeError("precision 'fp16_fp8' is a forward-only mode; train with 'bf16x3' or 'bf16'")
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
             self._state = _GradState()
             out = _BuildPyramidFn.apply(fmap1, fmap2, num_levels, precision, self._state, tiled)
@@ -602,6 +604,8 @@ class CorrBlock:
         prec = _precision_code(precision)
         if not _use_tiled(num_levels, radius, precision):
             raise RuntimeError("from_prepared builds the tiled inference pyramid: radius 3 or 4, at most 4 levels, a tensor-core precision")
+        if prec == _lib.RC_PREC_FP16_FP8:
+            raise RuntimeError("from_prepared: the prepared maps are bf16 hi/lo; precision 'fp16_fp8' converts the fp32 maps itself (CorrBlock(fmap1, fmap2, precision='fp16_fp8'))")
         if prec == _lib.RC_PREC_BF16X3 and (prep1.lo is None or prep2.lo is None):
             raise RuntimeError("precision 'bf16x3' needs the lo parts (encoder_head(..., with_lo=True))")
         B, h, w, D = prep1.hi.shape

@@ -136,6 +136,7 @@ int rc_corr_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, 
       return launch_build_simt(fmap1, fmap2, B, D, h, w, lv, num_levels, scale, st);
     case RC_PREC_BF16X3:
     case RC_PREC_BF16:
+    case RC_PREC_FP16_FP8:
       return launch_build_tc(fmap1, fmap2, B, D, h, w, lv, num_levels, precision, scale, workspace,
                              workspace_bytes, st);
     default:
@@ -196,7 +197,7 @@ int rc_corr_build_pyramid_tiled(const float *fmap1, const float *fmap2, int B, i
   if (int rc = check_geometry("rc_corr_build_pyramid_tiled", B, h, w, num_levels)) return rc;
   RC_CHECK_ARG(fmap1 && fmap2 && level_ptrs, "rc_corr_build_pyramid_tiled: null pointer");
   RC_CHECK_ARG(D > 0, "rc_corr_build_pyramid_tiled: D must be positive");
-  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16 && precision != RC_PREC_BF16_VOL16) {
+  if (precision != RC_PREC_BF16X3 && precision != RC_PREC_BF16 && precision != RC_PREC_BF16_VOL16 && precision != RC_PREC_FP16_FP8) {
     set_error("rc_corr_build_pyramid_tiled: only the tensor-core precisions write the tiled layout (got %d)",
               precision);
     return RC_ERR_UNSUPPORTED;

@@ -27,6 +27,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 
 #include <cstdlib>
 #include <mutex>
@@ -59,6 +60,7 @@ struct Params {
   int m_tiles, nt_x, nt_y;      // tiles along query pixels / patch grid
   long long total_tiles;
   float scale;
+  const unsigned *amax;         // NPASS == 2: bits of max |x| per (feature map, batch item), [2][B]
   int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
   int tpr[4], ng;               // TILED output only: tiles per tile-row of level l; groups of query pixels per item
   long long gstride[4];         //   floats per group of level l (= kTileGroup * hp * wp)
@@ -70,9 +72,30 @@ constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN 
 // the CTA pair's instruction: M=256 (128 rows in each CTA), N=256 (128 B rows held by each CTA)
 constexpr uint32_t kIdesc2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)((2 * TM) >> 4) << 24);
 
+// the same shape with fp16 operands (kind::f16) or e4m3 operands (kind::f8f6f4): both formats are code 0
+constexpr uint32_t kIdescF = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+constexpr uint32_t kIdescF2 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)((2 * TM) >> 4) << 24);
+
+// RC_PREC_FP16_FP8 (NPASS == 2).  A feature map is scaled by a power of two s so that its largest magnitude lands
+// in [128, 256) and split x*s = hi + lo, hi = fp16(x*s) (lo is then exact in fp32, |lo| <= 2^-4).  Of
+//   (a*sa)(b*sb) = ah*bh + (ah*bl + al*bh) + al*bl
+// the first term runs in fp16; the bracket is ONE contraction over 2x the channels of 8-bit operands
+//   A8 = [ e4m3(16 al) | e4m3(ah / 16) ],  B8 = [ e4m3(bh / 16) | e4m3(16 bl) ]      (128 B per pixel and 64 channels)
+// -- the 16s cancel in the products and put both factors in e4m3's normal range (16|lo| <= 1, |hi|/16 < 16; e4m3
+// keeps 2^-6 .. 448) -- at the 8-bit rate, i.e. for the tensor time of one more fp16 term: 2 units instead of
+// BF16X3's 3.  Rounding the cross terms' factors to 4 significant bits is a ~4 % error on terms that are 2^-12 of
+// the result; al*bl (2^-22) is dropped as in BF16X3.  The epilogue multiplies by scale / (sa*sb).
+__device__ __forceinline__ float norm_mul(unsigned amax_bits) {
+  // 2^(7 - e) for max|x| in [2^e, 2^(e+1)); 1 for an all-zero map; clamped to the finite powers of two
+  if (amax_bits == 0u) return 1.0f;
+  int f = 261 - (int)(amax_bits >> 23);
+  f = f < 1 ? 1 : (f > 254 ? 254 : f);
+  return __uint_as_float((unsigned)f << 23);
+}
+
 template <int NPASS, int NCTA>
 struct Cfg {
-  static constexpr int kOps = (NPASS == 3) ? 2 : 1;          // hi (+ lo)
+  static constexpr int kOps = (NPASS >= 2) ? 2 : 1;          // hi (+ lo, or the 8-bit pair)
   static constexpr int kBBytes = B_BYTES / NCTA;             // a CTA of a pair stages half of the patch
   static constexpr int kStageBytes = kOps * (A_BYTES + kBBytes);
   static constexpr int kStages = 192 * 1024 / kStageBytes;   // 4 / 2 (single CTA), 6 / 3 (pair)
@@ -133,7 +156,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     fence_barrier_init();
     prefetch_tmap(&tmA_hi);
     prefetch_tmap(&tmB_hi);
-    if (NPASS == 3) {
+    if (NPASS >= 2) {
       prefetch_tmap(&tmA_lo);
       prefetch_tmap(&tmB_lo);
     }
@@ -174,7 +197,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             mbar_expect_tx(&full[stage], C::kStageBytes);
             tma_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
             tma_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, by, b);
-            if (NPASS == 3) {
+            if (NPASS >= 2) {
               tma_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
               tma_load_4d(sp + C::kOps * A_BYTES + C::kBBytes, &tmB_lo, &full[stage], kb * TK, nx * PW, by, b);
             }
@@ -183,7 +206,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             if (leader) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
             tma2_load_3d(sp, &tmA_hi, &full[stage], kb * TK, m * TM, b);
             tma2_load_4d(sp + C::kOps * A_BYTES, &tmB_hi, &full[stage], kb * TK, nx * PW, by, b);
-            if (NPASS == 3) {
+            if (NPASS >= 2) {
               tma2_load_3d(sp + A_BYTES, &tmA_lo, &full[stage], kb * TK, m * TM, b);
               tma2_load_4d(sp + C::kOps * A_BYTES + C::kBBytes, &tmB_lo, &full[stage], kb * TK, nx * PW, by, b);
             }
@@ -212,6 +235,22 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
           const uint64_t b_hi = make_sw128_desc(sa + C::kOps * A_BYTES);
           const uint64_t a_lo = make_sw128_desc(sa + A_BYTES);
           const uint64_t b_lo = make_sw128_desc(sa + C::kOps * A_BYTES + C::kBBytes);
+          if constexpr (NPASS == 2) {
+            // fp16 products, then the two cross terms as one e4m3 contraction (the "lo" maps hold the 8-bit pair)
+#pragma unroll
+            for (int k = 0; k < TK / UK; ++k) {
+              const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);
+              const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
+              if (NCTA == 1) umma_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdescF, accum);
+              else umma2_bf16(d_tmem, a_hi + koff, b_hi + koff, kIdescF2, accum);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {  // 128 B rows = 4 x K 32 of 8-bit operands
+              const uint64_t koff = (uint64_t)(k * 2);
+              if (NCTA == 1) umma_f8(d_tmem, a_lo + koff, b_lo + koff, kIdescF, 1u);
+              else umma2_f8(d_tmem, a_lo + koff, b_lo + koff, kIdescF2, 1u);
+            }
+          } else
 #pragma unroll
           for (int k = 0; k < TK / UK; ++k) {
             const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);  // 32 B per K step inside the 128 B row
@@ -260,8 +299,12 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                  pitch2 = TILED ? (size_t)P.gstride[2] : (size_t)h2 * w2, pitch3 = TILED ? (size_t)P.gstride[3] : (size_t)h3 * w3;
     const bool vec0 = P.vec_mask & 1, vec1 = P.vec_mask & 2, vec2 = P.vec_mask & 4, vec3 = P.vec_mask & 8;
     bool peer_pending = false;  // hf=1: our staging buffer still holds the level-2 row for the peer
+    if (NPASS == 2) pdl_wait();  // the normalisation exponents below come from the kernels before this one
     for (long long t = unit0; t < P.total_tiles; t += unit_step) {
       const int b = (int)(t / tiles_per_item);
+      float out_scale = P.scale;
+      if constexpr (NPASS == 2)  // undo the two maps' power-of-two normalisation (exact)
+        out_scale = P.scale * (1.0f / norm_mul(__ldg(P.amax + b))) * (1.0f / norm_mul(__ldg(P.amax + P.B + b)));
       const int rem = (int)(t - (long long)b * tiles_per_item);
       const int mu = rem / nt, n = rem - mu * nt;
       const int m = mu * NCTA + (int)rank;
@@ -331,8 +374,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          v0[i] *= P.scale;
-          v1[i] *= P.scale;
+          v0[i] *= out_scale;
+          v1[i] *= out_scale;
         }
         const int y0 = ny * PH + hf * 4 + 2 * j;
         if constexpr (V16) {
@@ -574,6 +617,83 @@ prep_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __nv_bfl
   }
 }
 
+// ------------------------------------------------------------------ prep for RC_PREC_FP16_FP8
+// largest magnitude of each (feature map, batch item), in two steps without atomics or a memset: kAmaxParts partial
+// maxima per item here, reduced by every warp of the prepass (non-negative floats order like their bit patterns)
+constexpr int kAmaxParts = 64;
+__global__ void __launch_bounds__(256)
+absmax_kernel(const float *__restrict__ f1, const float *__restrict__ f2, unsigned *__restrict__ part, long long per_item) {
+  const int which = blockIdx.y & 1, b = blockIdx.y >> 1;
+  const float *src = (which ? f2 : f1) + (size_t)b * per_item;
+  __shared__ float wmax[8];
+  pdl_launch_dependents();
+  pdl_wait();
+  float m = 0.0f;
+  const long long stride = (long long)gridDim.x * blockDim.x, i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && per_item % 4 == 0) {
+    const float4 *s4 = reinterpret_cast<const float4 *>(src);
+    for (long long i = i0; i < per_item / 4; i += stride) {
+      const float4 v = __ldg(s4 + i);
+      m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+    }
+  } else {
+    for (long long i = i0; i < per_item; i += stride) m = fmaxf(m, fabsf(__ldg(src + i)));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) m = fmaxf(m, wmax[i]);
+    part[(size_t)blockIdx.y * kAmaxParts + blockIdx.x] = __float_as_uint(m);  // blockIdx.y = 2 b + which
+  }
+}
+
+// NCHW fp32 -> K-major fp16 "hi" map and the 8-bit pair map (see norm_mul above), same tiling as prep_kernel
+__global__ void __launch_bounds__(256)
+prep_f16f8_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __half *__restrict__ a_hi, uint8_t *__restrict__ a_8,
+                  __half *__restrict__ b_hi, uint8_t *__restrict__ b_8, const unsigned *__restrict__ part,
+                  unsigned *__restrict__ amax, int B, int D, int Dp, int N) {
+  __shared__ float tile[64][33];
+  const int which = blockIdx.z & 1, b = blockIdx.z >> 1;
+  const float *src = (which ? f2 : f1) + (size_t)b * D * N;
+  __half *hi = (which ? b_hi : a_hi) + (size_t)b * N * Dp;
+  uint8_t *p8 = (which ? b_8 : a_8) + (size_t)b * N * Dp * 2;
+  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  pdl_launch_dependents();
+  pdl_wait();
+  unsigned mx = max(__ldg(part + (size_t)blockIdx.z * kAmaxParts + tx), __ldg(part + (size_t)blockIdx.z * kAmaxParts + 32 + tx));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) amax[which * B + b] = mx;  // for the build's epilogue
+  const float s = norm_mul(mx);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int d = d0 + ty + 8 * i, p = p0 + tx;
+    tile[ty + 8 * i][tx] = (d < D && p < N) ? __ldg(src + (size_t)d * N + p) * s : 0.0f;
+  }
+  __syncthreads();
+  // the lo halves of the 128 B row pair with the other map's hi halves: A = [lo | hi], B = [hi | lo]
+  const int off_lo = which ? 64 : 0, off_hi = which ? 0 : 64;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int pl = ty + 8 * i, p = p0 + pl, d = d0 + 2 * tx;
+    if (p < N) {
+      const float x0 = tile[2 * tx][pl], x1 = tile[2 * tx + 1][pl];
+      const __half2 h2 = __floats2half2_rn(x0, x1);
+      *reinterpret_cast<__half2 *>(hi + (size_t)p * Dp + d) = h2;
+      const float h0 = __low2float(h2), h1 = __high2float(h2);
+      uint8_t *row = p8 + (size_t)p * Dp * 2 + (size_t)blockIdx.y * 128 + 2 * tx;
+      *reinterpret_cast<uint16_t *>(row + off_lo) =
+          __nv_cvt_float2_to_fp8x2(make_float2((x0 - h0) * 16.0f, (x1 - h1) * 16.0f), __NV_SATFINITE, __NV_E4M3);
+      *reinterpret_cast<uint16_t *>(row + off_hi) =
+          __nv_cvt_float2_to_fp8x2(make_float2(h0 * 0.0625f, h1 * 0.0625f), __NV_SATFINITE, __NV_E4M3);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ host side
 static int make_map(CUtensorMap *tm, void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides,
                     const cuuint32_t *box) {
@@ -633,12 +753,14 @@ size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision) {
   if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return 0;
   const size_t per_map = (size_t)B * h * w * round_up64(D) * 2;  // bf16
   const size_t aligned = (per_map + 255) / 256 * 256;
+  if (precision == RC_PREC_FP16_FP8)  // + the magnitudes: [2B] final, [2B][kAmaxParts] partial
+    return aligned * 4 + ((size_t)2 * B * (1 + tc::kAmaxParts) * 4 + 255) / 256 * 256;
   return aligned * 2 * (precision == RC_PREC_BF16X3 ? 2 : 1);
 }
 
 static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
                                int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
-                               bool tiled);
+                               bool tiled, const unsigned *amax = nullptr);
 
 static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv,
                                 int L, int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st,
@@ -654,7 +776,8 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
     return RC_ERR_INVALID;
   }
   const int N = h * w, Dp = round_up64(D);
-  const bool x3 = precision == RC_PREC_BF16X3;
+  const bool f8 = precision == RC_PREC_FP16_FP8;
+  const bool x3 = precision == RC_PREC_BF16X3 || f8;  // two operand maps per feature map
   const bool v16 = precision == RC_PREC_BF16_VOL16;
   if (v16 && !tiled) {
     set_error("RC_PREC_BF16_VOL16 exists in the tiled layout only (rc_corr_build_pyramid_tiled)");
@@ -668,10 +791,16 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
   __nv_bfloat16 *a_lo = x3 ? reinterpret_cast<__nv_bfloat16 *>(base + 2 * per_map) : a_hi;
   __nv_bfloat16 *b_lo = x3 ? reinterpret_cast<__nv_bfloat16 *>(base + 3 * per_map) : b_hi;
 
-  {
-    dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
-    RC_CUDA(launch_pdl(prep_kernel, grid, dim3(256), 0, st, f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0));
+  const dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
+  if (f8) {
+    unsigned *amax = reinterpret_cast<unsigned *>(base + 4 * per_map), *part = amax + 2 * B;
+    RC_CUDA(launch_pdl(absmax_kernel, dim3(kAmaxParts, (unsigned)(2 * B)), dim3(256), 0, st, f1, f2, part, (long long)D * N));
+    RC_CUDA(launch_pdl(prep_f16f8_kernel, grid, dim3(256), 0, st, f1, f2, reinterpret_cast<__half *>(a_hi),
+                       reinterpret_cast<uint8_t *>(a_lo), reinterpret_cast<__half *>(b_hi), reinterpret_cast<uint8_t *>(b_lo),
+                       (const unsigned *)part, amax, B, D, Dp, N));
+    return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled, amax);
   }
+  RC_CUDA(launch_pdl(prep_kernel, grid, dim3(256), 0, st, f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0));
   return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled);
 }
 
@@ -679,9 +808,10 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
 // layout prepass above writes, and what rc_fnet_conv1x1_prep (fnet_head.cu) emits straight from the encoder.
 static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
                                int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
-                               bool tiled) {
+                               bool tiled, const unsigned *amax) {
   using namespace tc;
   const int N = h * w;
+  const bool f8 = precision == RC_PREC_FP16_FP8;
   const bool x3 = precision == RC_PREC_BF16X3;
   const bool v16 = precision == RC_PREC_BF16_VOL16;
   const int ncta = tc::ctas_per_tile();
@@ -710,6 +840,7 @@ static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bf
   P.nt_y = (h + PH - 1) / PH;
   P.total_tiles = (long long)B * P.m_tiles * P.nt_x * P.nt_y;
   P.scale = scale;
+  P.amax = amax;
   P.lv = lv;
   P.vec_mask = 0;
   for (int l = 0; l < 4 && l < L; ++l) {
@@ -742,13 +873,17 @@ static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bf
     if (v16)
       rc = ncta == 2 ? tc::launch<1, 2, true, true>(tmAh, tmAl, tmBh, tmBl, P, st)
                      : tc::launch<1, 1, true, true>(tmAh, tmAl, tmBh, tmBl, P, st);
+    else if (f8)
+      rc = ncta == 2 ? tc::launch<2, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<2, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st);
     else if (ncta == 2)
       rc = x3 ? tc::launch<3, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2, true>(tmAh, tmAl, tmBh, tmBl, P, st);
     else
       rc = x3 ? tc::launch<3, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1, true>(tmAh, tmAl, tmBh, tmBl, P, st);
     return rc;
   }
-  if (ncta == 2)
+  if (f8)
+    rc = ncta == 2 ? tc::launch<2, 2, false>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<2, 1, false>(tmAh, tmAl, tmBh, tmBl, P, st);
+  else if (ncta == 2)
     rc = x3 ? tc::launch<3, 2, false>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 2, false>(tmAh, tmAl, tmBh, tmBl, P, st);
   else
     rc = x3 ? tc::launch<3, 1, false>(tmAh, tmAl, tmBh, tmBl, P, st) : tc::launch<1, 1, false>(tmAh, tmAl, tmBh, tmBl, P, st);

@@ -99,7 +99,9 @@ def conv2d_act(x, weight, bias=None, act=None):
     (reference core/update.py:6-14,33-60,84-97,122-125) on tensor cores (rc_conv2d_fwd): filter taps re-use one fp16
     conversion of the input tile, bias and activation are fused, and `x` may be a tuple (a, b) standing for
     `torch.cat([a, b], dim=1)` without the copy.  weight (Cout, Cin, KH, KW) with KH x KW in 1x1, 3x3, 1x5, 5x1;
-    act in None / "relu" / "sigmoid" / "tanh".  fp16 operands (TF32-class), fp32 accumulate and output.  Inference only."""
+    act in None / "relu" / "sigmoid" / "tanh".  fp16 operands (TF32-class), fp32 accumulate and output.  Inference only.
+    A filter count that is not a multiple of 16 (126 in the motion encoder, 2 in the flow head) is padded with zero
+    filters inside and the result is then a channel-sliced view."""
     global _CONV_CACHE
     from .corr import _WeightCache
     if _CONV_CACHE is None:
@@ -126,19 +128,26 @@ def conv2d_act(x, weight, bias=None, act=None):
         outs = []
         for o0 in range(0, Cout, 256):  # wider layers (the mask head's 576 channels) go slice by slice
             o1 = min(Cout, o0 + 256)
+            co = (o1 - o0 + 15) // 16 * 16  # the kernel's N granule; padded filters are zero, their outputs dropped below
 
-            def make(o0=o0, o1=o1):
-                nbytes = int(L.rc_conv_weight_bytes(o1 - o0, Cin, KH, KW))
+            def make(o0=o0, o1=o1, co=co):
+                nbytes = int(L.rc_conv_weight_bytes(co, Cin, KH, KW))
                 wp_ = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
-                w32 = weight.detach()[o0:o1].float().contiguous()
-                _lib.check(L.rc_conv_prep_weight(w32.data_ptr(), wp_.data_ptr(), o1 - o0, Cin, KH, KW, st), "rc_conv_prep_weight")
+                w32 = torch.zeros((co, Cin, KH, KW), dtype=torch.float32, device=dev)
+                w32[:o1 - o0] = weight.detach()[o0:o1]
+                _lib.check(L.rc_conv_prep_weight(w32.data_ptr(), wp_.data_ptr(), co, Cin, KH, KW, st), "rc_conv_prep_weight")
                 return wp_
 
+            def make_bias(o0=o0, o1=o1, co=co):
+                b32_ = torch.zeros(co, dtype=torch.float32, device=dev)
+                b32_[:o1 - o0] = bias.detach()[o0:o1]
+                return b32_
+
             wp = _CONV_CACHE.get(weight, ("conv", o0, dev.index), make)
-            b32 = None if bias is None else bias.detach()[o0:o1].float().contiguous()
-            out = torch.empty((B, o1 - o0, H, W), dtype=torch.float32, device=dev)
+            b32 = None if bias is None else _CONV_CACHE.get(bias, ("bias", o0, co, dev.index), make_bias)
+            out = torch.empty((B, co, H, W), dtype=torch.float32, device=dev)
             rc = L.rc_conv2d_fwd(xs[0].data_ptr(), C1, xs[1].data_ptr() if len(xs) == 2 else None, wp.data_ptr(),
-                                 None if b32 is None else b32.data_ptr(), out.data_ptr(), B, Cin, o1 - o0, H, W, KH, KW, _ACTS[act], st)
+                                 None if bias is None else b32.data_ptr(), out.data_ptr(), B, Cin, co, H, W, KH, KW, _ACTS[act], st)
             _lib.check(rc, "rc_conv2d_fwd")
-            outs.append(out)
+            outs.append(out if co == o1 - o0 else out[:, :o1 - o0])
     return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)

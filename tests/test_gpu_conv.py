@@ -14,7 +14,8 @@ CASES = [
     # B, C1, C2, Cout, H, W, KH, KW, act                         the layer of core/update.py it stands for
     (1, 256, 0, 192, 55, 128, 3, 3, "relu"),      # convc2 (:85,91)
     (2, 128, 0, 64, 23, 39, 3, 3, "relu"),        # convf2 (:87,93), ragged width
-    (1, 192, 64, 112, 24, 40, 3, 3, "relu"),      # conv on cat([cor, flo]) (:88,95-96); 126 -> 112 here (multiple of 16)
+    (1, 192, 64, 126, 24, 40, 3, 3, "relu"),      # conv on cat([cor, flo]) (:88,95-96): 126 filters, padded to 128 inside
+    (2, 256, 0, 2, 12, 20, 3, 3, None),           # FlowHead conv2 (:10): two filters, padded to 16 inside
     (1, 128, 256, 128, 30, 130, 1, 5, "sigmoid"), # SepConvGRU convz1 / convr1 on cat([h, x]) (:36-37,42-43), two row tiles
     (1, 128, 256, 128, 21, 64, 5, 1, "tanh"),     # SepConvGRU convq2 (:42,50)
     (1, 128, 0, 256, 16, 33, 3, 3, "relu"),       # FlowHead conv1 / mask head conv (:9,123)
@@ -44,7 +45,7 @@ def test_conv2d_act_matches_torch(case):
     pad = (KH // 2, KW // 2)
     want = fn(F.conv2d(x.double(), wgt.double(), bias.double(), padding=pad)).float()
     got = rr.conv2d_act(a if b is None else (a, b), wgt, bias, act)
-    assert got.shape == want.shape and got.dtype == torch.float32 and got.is_contiguous()
+    assert got.shape == want.shape and got.dtype == torch.float32
     assert torch.isfinite(got).all()
     scale = float(F.conv2d(x.double(), wgt.double(), bias.double(), padding=pad).abs().max())  # pre-activation magnitude
     assert float((got - want).abs().max()) <= 2e-3 * max(scale, 1.0), (case, float((got - want).abs().max()), scale)
@@ -58,7 +59,23 @@ def test_conv2d_act_rejects():
     x = torch.zeros(1, 64, 8, 8, device=DEV)
     with pytest.raises(RuntimeError, match="unsupported"):
         rr.conv2d_act(x, torch.zeros(64, 64, 7, 7, device=DEV))
-    with pytest.raises(RuntimeError, match="multiple of 16"):
-        rr.conv2d_act(x, torch.zeros(30, 64, 3, 3, device=DEV))
+    from raft_ros_b200 import _lib
+    L = _lib.lib()
+    assert L.rc_conv2d_fwd(x.data_ptr(), 64, None, x.data_ptr(), None, x.data_ptr(), 1, 64, 30, 8, 8, 3, 3, 0, None) != 0  # C ABI: N granule 16
     with pytest.raises(RuntimeError, match="inference"):
         rr.conv2d_act(x.clone().requires_grad_(True), torch.zeros(64, 64, 3, 3, device=DEV))
+
+
+def test_conv2d_act_sees_a_new_bias_and_an_updated_weight():
+    import raft_ros_b200 as rr
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1, 32, 6, 9, generator=g).to(DEV)
+    w = torch.randn(16, 32, 3, 3, generator=g).to(DEV)
+    b1, b2 = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
+    y1 = rr.conv2d_act(x, w, b1)
+    y2 = rr.conv2d_act(x, w, b2)
+    assert torch.allclose(y2 - y1, torch.ones_like(y1), atol=1e-5)
+    b2.mul_(3.0)
+    assert torch.allclose(rr.conv2d_act(x, w, b2) - y1, 3 * torch.ones_like(y1), atol=1e-5)
+    w.mul_(2.0)
+    assert torch.allclose(rr.conv2d_act(x, w, b1), 2 * y1, atol=1e-4)

@@ -27,7 +27,8 @@ from tests.helpers import cotangent, make_coords, normwise, relmax
 pytestmark = pytest.mark.gpu
 
 DEV = "cuda:0"
-BUILD_TOL = {"fp32": dict(rel=3e-6, norm=2e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
+BUILD_TOL = {"fp32": dict(rel=3e-6, norm=2e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3),
+             "fp16_fp8": dict(rel=1e-4, norm=3e-5)}
 PRECISIONS = ["fp32", "bf16x3", "bf16"]
 LOOKUP_TOL = 2e-5
 
@@ -129,7 +130,7 @@ SHAPES = [
 ]
 
 
-@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("precision", PRECISIONS + ["fp16_fp8"])
 @pytest.mark.parametrize("shape", SHAPES)
 def test_build_vs_oracle(rr, shape, precision):
     B, D, h, w, L, r = shape
@@ -145,6 +146,35 @@ def test_build_vs_oracle(rr, shape, precision):
         assert np.isfinite(got).all()
         assert relmax(got, want[l]) <= tol["rel"], (shape, l, relmax(got, want[l]))
         assert normwise(got, want[l]) <= tol["norm"], (shape, l, normwise(got, want[l]))
+
+
+def test_fp16_fp8_build_is_scale_free_per_item_and_map(rr):
+    """RC_PREC_FP16_FP8 normalises every (feature map, batch item) by a power of two taken from its largest magnitude:
+    the error must not depend on the magnitudes (1e-6 ... 1e+5 here, far outside fp16's and e4m3's own ranges, different
+    for the two maps and the items of one batch), an all-zero map gives zeros, and an infinity stays non-finite."""
+    B, D, h, w, L = 3, 96, 12, 21, 3
+    rng = np.random.default_rng(77)
+    f1 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, h, w)).astype(np.float32)
+    m1 = np.array([1e-6, 1.0, 3e4], np.float32).reshape(B, 1, 1, 1)
+    m2 = np.array([1e5, 7e-3, 1.0], np.float32).reshape(B, 1, 1, 1)
+    f1, f2 = f1 * m1, f2 * m2
+    want = O.corr_build(f1, f2, L)
+    blk = rr.CorrBlock(t(f1), t(f2), num_levels=L, radius=4, precision="fp16_fp8")
+    N = h * w
+    for l in range(L):
+        got = n(blk.corr_pyramid[l]).reshape(B, N, -1)
+        ref = want[l].reshape(B, N, -1)
+        for b in range(B):  # per item: a relative bound against the whole batch would hide the small items
+            assert relmax(got[b], ref[b]) <= 1e-4, (l, b, relmax(got[b], ref[b]))
+            assert normwise(got[b], ref[b]) <= 3e-5, (l, b, normwise(got[b], ref[b]))
+    z = rr.CorrBlock(t(np.zeros_like(f1)), t(f2), num_levels=L, radius=4, precision="fp16_fp8")
+    assert all(bool((lv == 0).all()) for lv in z.corr_pyramid)
+    f1[1, 5, 3, 4] = np.inf
+    bad = n(rr.CorrBlock(t(f1), t(f2), num_levels=1, radius=4, precision="fp16_fp8").corr_pyramid[0]).reshape(B, N, -1)
+    assert not np.isfinite(bad[1]).all() and np.isfinite(bad[0]).all() and np.isfinite(bad[2]).all()
+    with pytest.raises(RuntimeError, match="forward-only"):
+        rr.CorrBlock(t(f2).requires_grad_(True), t(f2), num_levels=L, radius=4, precision="fp16_fp8")
 
 
 def _fuzz_geometries(count=12, seed=20261106):
@@ -716,7 +746,7 @@ TILED_GEOMS = [(1, 64, 8, 32, 4), (2, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 2
                (2, 256, 16, 18, 2), (1, 64, 9, 65, 1), (1, 256, 55, 128, 4)]
 
 
-@pytest.mark.parametrize("prec", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("prec", ["bf16x3", "bf16", "fp16_fp8"])
 @pytest.mark.parametrize("geom", TILED_GEOMS)
 def test_tiled_build_equals_row_build(rr, geom, prec):
     """rc_corr_build_pyramid_tiled writes, tile by tile, exactly the numbers rc_corr_build_pyramid writes
