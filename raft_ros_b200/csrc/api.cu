@@ -31,8 +31,21 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static int encode_tmap(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                       const unsigned long long *strides_bytes, const unsigned int *box, const char *who, bool f32_plain);
+
 int encode_tmap_sw128(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
                       const unsigned long long *strides_bytes, const unsigned int *box, const char *who) {
+  return encode_tmap(tm, base, rank, dims, strides_bytes, box, who, false);
+}
+
+int encode_tmap_f32(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                    const unsigned long long *strides_bytes, const unsigned int *box, const char *who) {
+  return encode_tmap(tm, base, rank, dims, strides_bytes, box, who, true);
+}
+
+static int encode_tmap(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                       const unsigned long long *strides_bytes, const unsigned int *box, const char *who, bool f32_plain) {
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -53,8 +66,9 @@ int encode_tmap_sw128(::CUtensorMap_st *tm, const void *base, int rank, const un
     b[i] = box[i];
     if (i + 1 < rank) st[i] = strides_bytes[i];
   }
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void *>(base), d, st, b, ones,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = fn(tm, f32_plain ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                  const_cast<void *>(base), d, st, b, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  f32_plain ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("%s: cuTensorMapEncodeTiled failed with CUresult %d", who, (int)r);
@@ -491,8 +505,8 @@ int rc_alt_corr_bwd(const float *fmap1, const float *fmap2, const float *coords,
 static int check_conv(const char *fn, int Cout, int Cin, int KH, int KW) {
   RC_CHECK_ARG(Cout > 0 && Cout <= 256 && Cout % 16 == 0, "%s: Cout %d must be a multiple of 16, at most 256", fn, Cout);
   RC_CHECK_ARG(Cin > 0 && Cin <= 4096, "%s: Cin %d out of range", fn, Cin);
-  RC_CHECK_ARG(KH > 0 && KW > 0 && (KH & 1) && (KW & 1) && (KW == 1 ? (8 + KH - 1) * 16 : KH * (128 + KW - 1)) <= 640,
-               "%s: %dx%d filters unsupported (odd sizes whose halo tile fits 640 pixels: 1x1, 3x3, 1x5, KHx1 up to 33x1, ...)", fn, KH, KW);
+  RC_CHECK_ARG(KH > 0 && KW > 0 && (KH & 1) && (KW & 1) && (KW == 1 ? (8 + KH - 1) * 16 : KH * (128 + KW - 1)) <= 400,
+               "%s: %dx%d filters unsupported (odd sizes whose halo tile fits 400 pixels: 1x1, 3x3, 1x5, 3x5, KHx1 up to 17x1)", fn, KH, KW);
   return RC_OK;
 }
 

@@ -56,6 +56,9 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 // rank-1 of strides (bytes).  One definition for every tensor-core kernel of the library (api.cu).
 int encode_tmap_sw128(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
                       const unsigned long long *strides_bytes, const unsigned int *box, const char *who);
+// fp32 elements, no swizzle (zero fill outside the tensor, negative start coordinates included)
+int encode_tmap_f32(::CUtensorMap_st *tm, const void *base, int rank, const unsigned long long *dims,
+                      const unsigned long long *strides_bytes, const unsigned int *box, const char *who);
 
 struct LevelPtrs {
   float *p[RC_MAX_LEVELS];

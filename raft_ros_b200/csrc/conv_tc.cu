@@ -17,7 +17,7 @@
 // place.  Operands are fp16 (11-bit mantissa: the class of TF32, which is what cuDNN runs these convolutions in by
 // torch's default, and of the reference's --mixed_precision autocast), one pass, fp32 accumulation.
 //
-// One CTA per SM, persistent, 14 warps: 0-7 converters, 8-11 epilogue, 12 weight TMA, 13 MMA issue.
+// One CTA per SM, persistent, 15 warps: 0-7 converters, 8-11 epilogue, 12 weight TMA, 13 input TMA, 14 MMA issue.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -29,12 +29,15 @@ namespace cv {
 
 using namespace tc;
 
-constexpr int kConvWarps = 8, kEpiWarps = 4, kProducerWarp = 12, kMmaWarp = 13, kThreads = 14 * 32;
+constexpr int kConvWarps = 8, kEpiWarps = 4, kProducerWarp = 12, kInputWarp = 13, kMmaWarp = 14, kThreads = 15 * 32;
 constexpr int TMPIX = 128;
-constexpr int kMaxHaloPix = 640;                    // 5 rows x 128 (5x1), 3 x 130 (3x3), 1 x 132 (1x5)
-constexpr int kHaloBytes = kMaxHaloPix * 128;       // one 64-channel block of the halo tile: 80 KB
-constexpr int W_BLOCK = 256 * 64 * 2;               // one weight block: up to 256 rows x 64 K
-constexpr int kSmemBytes = 1024 + 2 * kHaloBytes + 2 * W_BLOCK + 1024 /*bias*/ + 256;
+constexpr int kMaxHaloPix = 400;                    // 3 x 130 (3x3), 12 x 16 (5x1 on 8 x 16 tiles), 1 x 132 (1x5)
+constexpr int kHaloBytes = kMaxHaloPix * 128;       // one 64-channel block of the halo tile: 50 KB
+constexpr int kInStages = 4;                        // fp32 input staging: 8 channels of the halo tile per stage, filled by TMA
+constexpr int kInStageBytes = 8 * kMaxHaloPix * 4;  //   [8 channels][rows][columns rounded up to 4] fp32 = 12.5 KB
+constexpr int kRingBytes = 72 * 1024;               // weight ring: as many blocks of (filters of this CTA) x 64 K as fit, at most 8
+constexpr int kMaxStages = 8;
+constexpr int kSmemBytes = 1024 + 2 * kHaloBytes + kInStages * kInStageBytes + kRingBytes + 1024 /*bias*/ + 512;
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 
 struct Params {
@@ -44,6 +47,10 @@ struct Params {
   int B, C1, Cin, Cout, H, W, KH, KW, act;
   int TH, TW;  // output tile: TH rows x TW columns = 128 pixels (1 x 128, or 8 x 16 for filters one column wide)
   int ncb, tiles_x, tiles_y, total_tiles;
+  int BH, BW;            // staged box of the input: TH + KH - 1 rows of (TW + KW - 1 rounded up to 4) columns -- or the whole
+  int box_x0, box_y0;    //   image extent where that is smaller (a box may not exceed the tensor): then it starts at 0 (flags)
+  int nparts, Cn;        // a work item = (pixel tile, one of nparts groups of Cn filters): small images still fill the SMs
+  int stages, stage_bytes;
 };
 
 __device__ __forceinline__ float activate(float v, int act) {
@@ -55,23 +62,30 @@ __device__ __forceinline__ float activate(float v, int act) {
   }
 }
 
+// TMA_IN: the input reaches the converters through a ring of TMA boxes (rows of 16 B multiples, i.e. W % 4 == 0, and a
+// first tensor whose channel count is a multiple of 8); the box's zero fill outside the image IS the padding.  Otherwise
+// the converters read global memory themselves (any width; slower: few bytes in flight per SM).
+template <bool TMA_IN>
 __global__ void __launch_bounds__(kThreads, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX1,
+               const __grid_constant__ CUtensorMap tmX2, const Params P) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = smem_u32(smem_raw);
   const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
   uint8_t *smem = smem_raw + (base_u32 - raw_u32);
-  const uint32_t halo_u32 = base_u32, w_u32 = base_u32 + 2 * kHaloBytes;
-  float *bias_s = reinterpret_cast<float *>(smem + 2 * kHaloBytes + 2 * W_BLOCK);
+  constexpr int kInOff = 2 * kHaloBytes, kWOff = kInOff + kInStages * kInStageBytes;
+  const uint32_t halo_u32 = base_u32, w_u32 = base_u32 + kWOff;
+  float *bias_s = reinterpret_cast<float *>(smem + kWOff + kRingBytes);
   uint64_t *bars = reinterpret_cast<uint64_t *>(bias_s + 256);
-  uint64_t *h_full = bars, *h_empty = bars + 2, *w_full = bars + 4, *w_empty = bars + 6, *acc_full = bars + 8,
-           *acc_empty = bars + 10;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 12);
+  uint64_t *h_full = bars, *h_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6, *w_full = bars + 8,
+           *w_empty = bars + 8 + kMaxStages, *s_full = bars + 8 + 2 * kMaxStages, *s_empty = s_full + kInStages;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(s_empty + kInStages);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int KH = P.KH, KW = P.KW, T = KH * KW, ph = KH >> 1, pw = KW >> 1;
   const int TH = P.TH, TW = P.TW;
   const int RW = TW + 2 * pw, HP = (TH + 2 * ph) * RW;  // halo tile: TH + KH - 1 rows of RW pixels
-  const int Cout = P.Cout, H = P.H, W = P.W;
+  const int Cout = P.Cout, Cn = P.Cn, H = P.H, W = P.W;
+  const int items = P.total_tiles * P.nparts;
   const size_t HW = (size_t)H * W;
   pdl_launch_dependents();
 
@@ -79,13 +93,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&h_full[i], kConvWarps);
       mbar_init(&h_empty[i], 1);
-      mbar_init(&w_full[i], 1);
-      mbar_init(&w_empty[i], 1);
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], kEpiWarps);
     }
+    for (int i = 0; i < kMaxStages; ++i) {
+      mbar_init(&w_full[i], 1);
+      mbar_init(&w_empty[i], 1);
+    }
+    for (int i = 0; i < kInStages; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_empty[i], kConvWarps);
+    }
     fence_barrier_init();
     prefetch_tmap(&tmW);
+    if (TMA_IN) {
+      prefetch_tmap(&tmX1);
+      prefetch_tmap(&tmX2);
+    }
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
   pdl_wait();
@@ -99,32 +123,78 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
     // ===================== converters: input tile with halo -> fp16 operand rows, one 64-channel block at a time =====================
     const int tid = threadIdx.x;
     uint32_t n = 0;  // channel blocks done (over all tiles): buffer n & 1
-    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+    int ist = 0;     // input staging ring
+    uint32_t iphase = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      const int tile = item / P.nparts;
       const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
       const int x0 = txi * TW, y = tyi * TH;
       for (int cb = 0; cb < P.ncb; ++cb, ++n) {
         const uint32_t buf = n & 1;
         mbar_wait(&h_empty[buf], ((n >> 1) & 1) ^ 1);  // the MMAs that read this buffer two blocks ago are done
         const uint32_t hb = halo_u32 + buf * kHaloBytes;
-        for (int it = tid; it < HP * 8; it += kConvWarps * 32) {
-          const int c8 = it / HP, hi = it - c8 * HP;       // 8-channel chunk, halo pixel (consecutive threads: consecutive pixels)
+        if constexpr (TMA_IN) {
+          // eight channels at a time arrive as one fp32 box [8][BH][BW]; a thread turns a halo pixel's 8 values into one
+          // 16 B chunk of its operand row (consecutive lanes: consecutive pixels, conflict-free reads)
+          for (int sub = 0; sub < 8; ++sub) {
+            const bool live = cb * 64 + sub * 8 < P.Cin;  // channel padding of the last block: zeros, nothing staged
+            const float *src = reinterpret_cast<const float *>(smem + kInOff + ist * kInStageBytes);
+            if (live) mbar_wait(&s_full[ist], iphase);
+            // a box pinned to the image origin (image narrower / lower than the halo tile) is shifted against the tile
+            const int dx = P.box_x0 ? pw - x0 : 0, dy = P.box_y0 ? ph - y : 0;
+            for (int hi = tid; hi < HP; hi += kConvWarps * 32) {
+              const int r = hi / RW, xx = hi - r * RW;
+              const int br = r - dy, bx = xx - dx;
+              const bool in = live && (unsigned)br < (unsigned)P.BH && (unsigned)bx < (unsigned)P.BW;
+              float v[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = in ? src[(j * P.BH + br) * P.BW + bx] : 0.0f;
+              uint32_t w4[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w4[j]) : "f"(v[2 * j + 1]), "f"(v[2 * j]));
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + (uint32_t)hi * 128u + (uint32_t)((sub ^ (hi & 7)) << 4)),
+                           "r"(w4[0]), "r"(w4[1]), "r"(w4[2]), "r"(w4[3])
+                           : "memory");
+            }
+            if (live) {
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&s_empty[ist]);
+              if (++ist == kInStages) { ist = 0; iphase ^= 1; }
+            }
+          }
+        } else {
+        // 8-channel chunk c8 of halo pixel hi (consecutive threads: consecutive pixels); two chunks per thread in flight
+        auto load8 = [&](int it, float (&v)[8]) {
+          const int c8 = it / HP, hi = it - c8 * HP;
           const int r = hi / RW, xx = hi - r * RW;
           const int iy = y - ph + r, ix = x0 - pw + xx;
-          const bool inside = (unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W;
+          const bool inside = it < HP * 8 && (unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W;
           const int c0 = cb * 64 + c8 * 8;
-          float v[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int c = c0 + j;
             const float *src = c < P.C1 ? P.x1 + ((size_t)b * P.C1 + c) * HW : P.x2 + ((size_t)b * (P.Cin - P.C1) + (c - P.C1)) * HW;
             v[j] = (inside && c < P.Cin) ? __ldg(src + (size_t)iy * W + ix) : 0.0f;
           }
+        };
+        auto store8 = [&](int it, const float (&v)[8]) {
+          if (it >= HP * 8) return;
+          const int c8 = it / HP, hi = it - c8 * HP;
           uint32_t w4[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w4[j]) : "f"(v[2 * j + 1]), "f"(v[2 * j]));
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + (uint32_t)hi * 128u + (uint32_t)((c8 ^ (hi & 7)) << 4)),
                        "r"(w4[0]), "r"(w4[1]), "r"(w4[2]), "r"(w4[3])
                        : "memory");
+        };
+        constexpr int kStep = kConvWarps * 32;
+        for (int it = tid; it < HP * 8; it += 2 * kStep) {
+          float va[8], vb[8];
+          load8(it, va);
+          load8(it + kStep, vb);
+          store8(it, va);
+          store8(it + kStep, vb);
+        }
         }
         fence_proxy_async_smem();
         __syncwarp();
@@ -136,7 +206,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
     const int e = warp - kConvWarps;
     int acc = 0;
     uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      const int tile = item / P.nparts, n0 = (item - tile * P.nparts) * Cn;  // this item's filters: [n0, n0 + Cn)
       const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
       const int m = e * 32 + lane;  // output pixel of the tile, row-major
       const int y = tyi * TH + m / TW, x = txi * TW + m % TW;
@@ -144,24 +215,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
       mbar_wait(&acc_full[acc], phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(acc * 256);
-      float *o = P.out + (size_t)b * Cout * HW + (size_t)y * W + x;
+      float *o = P.out + ((size_t)b * Cout + n0) * HW + (size_t)y * W + x;
+      const float *bs = bias_s + n0;
       int c0 = 0;
-      for (; c0 + 32 <= Cout; c0 += 32) {
+      for (; c0 + 32 <= Cn; c0 += 32) {
         float v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
         if (pv) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bias_s[c0 + i], P.act));
+          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bs[c0 + i], P.act));
         }
       }
-      if (c0 < Cout) {  // Cout is a multiple of 16
+      if (c0 < Cn) {  // Cn is a multiple of 16
         float v[16];
         tmem_ld16(taddr + c0, v);
         tmem_ld_wait();
         if (pv) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bias_s[c0 + i], P.act));
+          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bs[c0 + i], P.act));
         }
       }
       tc_fence_before();
@@ -175,23 +247,44 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int n0 = (item % P.nparts) * Cn;
         for (int cb = 0; cb < P.ncb; ++cb)
           for (int t = 0; t < T; ++t) {
             mbar_wait(&w_empty[stage], phase ^ 1);
-            mbar_expect_tx(&w_full[stage], (uint32_t)Cout * 128u);
-            tma_load_3d(smem + 2 * kHaloBytes + stage * W_BLOCK, &tmW, &w_full[stage], 0, 0, cb * T + t);
-            if (++stage == 2) { stage = 0; phase ^= 1; }
+            mbar_expect_tx(&w_full[stage], (uint32_t)Cn * 128u);
+            tma_load_3d(smem + kWOff + stage * P.stage_bytes, &tmW, &w_full[stage], 0, n0, cb * T + t);
+            if (++stage == P.stages) { stage = 0; phase ^= 1; }
           }
+      }
+    }
+  } else if (warp == kInputWarp) {
+    // ===================== input boxes: 8 channels x halo tile, fp32, zero-filled outside the image =====================
+    if (TMA_IN && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t bytes = (uint32_t)(8 * P.BH * P.BW * 4);
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int tile = item / P.nparts;
+        const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
+        const int xs = P.box_x0 ? 0 : txi * TW - pw, ys = P.box_y0 ? 0 : tyi * TH - ph;
+        for (int c = 0; c < P.Cin; c += 8) {
+          mbar_wait(&s_empty[stage], phase ^ 1);
+          mbar_expect_tx(&s_full[stage], bytes);
+          if (c < P.C1) tma_load_4d(smem + kInOff + stage * kInStageBytes, &tmX1, &s_full[stage], xs, ys, c, b);
+          else tma_load_4d(smem + kInOff + stage * kInStageBytes, &tmX2, &s_full[stage], xs, ys, c - P.C1, b);
+          if (++stage == kInStages) { stage = 0; phase ^= 1; }
+        }
+      }
     }
   } else {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       // kind::f16: D = f32, A = B = f16, K-major, M = 128, N = Cout
-      const uint32_t idesc = (1u << 4) | ((uint32_t)(Cout >> 3) << 17) | ((uint32_t)(TMPIX >> 4) << 24);
+      const uint32_t idesc = (1u << 4) | ((uint32_t)(Cn >> 3) << 17) | ((uint32_t)(TMPIX >> 4) << 24);
       int ws = 0, acc = 0;
       uint32_t wphase = 0, accphase = 0, n = 0;
-      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
         mbar_wait(&acc_empty[acc], accphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
@@ -208,14 +301,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const Params P) {
             // tap (ky, kx): the tile's 128 output pixels (row-major) see halo pixels ky * RW + kx .. + 127 -- consecutive
             // because the tile is a single row (RW = TW + KW - 1 only matters within it) or the filter a single column (RW = TW)
             const uint64_t adesc = make_sw128_desc(hb + (uint32_t)(ky * RW + kx) * 128u);
-            const uint64_t bdesc = make_sw128_desc(w_u32 + ws * W_BLOCK);
+            const uint64_t bdesc = make_sw128_desc(w_u32 + ws * P.stage_bytes);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, first ? 0u : 1u);
               first = 0;
             }
             umma_commit(&w_empty[ws]);
-            if (++ws == 2) { ws = 0; wphase ^= 1; }
+            if (++ws == P.stages) { ws = 0; wphase ^= 1; }
           }
           umma_commit(&h_empty[buf]);
         }
@@ -260,13 +353,9 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
                    int H, int W, int KH, int KW, int act, cudaStream_t st) {
   using namespace cv;
   const int ncb = (Cin + 63) / 64, T = KH * KW;
-  CUtensorMap tm;
-  {
-    const unsigned long long dims[3] = {64, (unsigned long long)Cout, (unsigned long long)ncb * T};
-    const unsigned long long strides[2] = {128, 128ull * Cout};
-    const unsigned int box[3] = {64, (unsigned int)Cout, 1};
-    if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_conv2d_fwd")) return rc;
-  }
+  int dev = 0, sms = 148;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   Params P{};
   P.x1 = x1; P.x2 = x2; P.bias = bias; P.out = out;
   P.B = B; P.C1 = C1; P.Cin = Cin; P.Cout = Cout; P.H = H; P.W = W; P.KH = KH; P.KW = KW; P.act = act;
@@ -276,12 +365,50 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   P.tiles_x = (W + P.TW - 1) / P.TW;
   P.tiles_y = (H + P.TH - 1) / P.TH;
   P.total_tiles = B * P.tiles_y * P.tiles_x;
-  RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-  int dev = 0, sms = 148;
-  RC_CUDA(cudaGetDevice(&dev));
-  RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int grid = P.total_tiles < sms ? P.total_tiles : sms;
-  RC_CUDA(launch_pdl(conv_tc_kernel, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, P));
+  // few tiles (one frame pair): split the filters over up to 4 CTAs per tile so that the whole GPU works on it
+  P.nparts = 1;
+  for (int p = 2; p <= 4; ++p)
+    if (P.total_tiles * p <= sms && Cout % (16 * p) == 0) P.nparts = p;
+  P.Cn = Cout / P.nparts;
+  P.stage_bytes = (P.Cn * 128 + 1023) / 1024 * 1024;
+  P.stages = kRingBytes / P.stage_bytes < kMaxStages ? kRingBytes / P.stage_bytes : kMaxStages;
+  CUtensorMap tm;
+  {
+    const unsigned long long dims[3] = {64, (unsigned long long)Cout, (unsigned long long)ncb * T};
+    const unsigned long long strides[2] = {128, 128ull * Cout};
+    const unsigned int box[3] = {64, (unsigned int)P.Cn, 1};
+    if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_conv2d_fwd")) return rc;
+  }
+  P.BH = P.TH + KH - 1;
+  P.BW = (P.TW + KW - 1 + 3) & ~3;
+  if (P.BW > W) { P.BW = W; P.box_x0 = 1; }  // (W % 4 == 0 on the TMA path)
+  if (P.BH > H) { P.BH = H; P.box_y0 = 1; }
+  const int items = P.total_tiles * P.nparts;
+  const int grid = items < sms ? items : sms;
+  const int C2 = Cin - C1;
+  const bool tma_in = W % 4 == 0 && (reinterpret_cast<uintptr_t>(x1) & 15) == 0 && P.BH * P.BW <= kMaxHaloPix &&
+                      C1 >= 8 && (C2 == 0 || (C2 >= 8 && C1 % 8 == 0 && (reinterpret_cast<uintptr_t>(x2) & 15) == 0));
+  if (tma_in) {
+    CUtensorMap tx1, tx2;
+    const unsigned int box[4] = {(unsigned int)P.BW, (unsigned int)P.BH, 8, 1};
+    {
+      const unsigned long long dims[4] = {(unsigned long long)W, (unsigned long long)H, (unsigned long long)C1, (unsigned long long)B};
+      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * W * H * C1};
+      if (int rc = encode_tmap_f32(&tx1, x1, 4, dims, strides, box, "rc_conv2d_fwd")) return rc;
+    }
+    if (C2 > 0) {
+      const unsigned long long dims[4] = {(unsigned long long)W, (unsigned long long)H, (unsigned long long)C2, (unsigned long long)B};
+      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * W * H * C2};
+      if (int rc = encode_tmap_f32(&tx2, x2, 4, dims, strides, box, "rc_conv2d_fwd")) return rc;
+    } else {
+      tx2 = tx1;
+    }
+    RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    RC_CUDA(launch_pdl(conv_tc_kernel<true>, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tx1, tx2, P));
+  } else {
+    RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    RC_CUDA(launch_pdl(conv_tc_kernel<false>, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tm, tm, P));
+  }
   return RC_OK;
 }
 

@@ -21,6 +21,10 @@ CASES = [
     (1, 128, 0, 256, 16, 33, 3, 3, "relu"),       # FlowHead conv1 / mask head conv (:9,123)
     (1, 256, 0, 576, 9, 17, 1, 1, None),          # mask head 1x1, 576 channels = three slices (:125)
     (3, 40, 0, 16, 5, 7, 3, 3, None),             # channel count that is not a multiple of 64, tiny image
+    (2, 16, 0, 16, 2, 8, 3, 3, None),             # image lower and narrower than the staged box (box pinned to the origin)
+    (1, 24, 40, 32, 2, 12, 5, 1, "relu"),         # the same for the column filter's 8 x 16 tiles, two inputs
+    (1, 4, 0, 16, 8, 8, 3, 3, None),              # fewer channels than a staged box holds: direct-load path
+    (1, 128, 256, 256, 55, 128, 1, 5, "sigmoid"), # z and r gates as one 256-filter convolution at the real size
 ]
 
 
