@@ -354,7 +354,7 @@ def gpu_reference_run(args, f1, f2, coords, our_value):
         a2 = torch.randn(1, D, H, W, generator=g).to(f1.device)
         c4 = (rr.coords_grid(1, H, W, "cpu") + 2.0 * torch.randn(1, 2, H, W, generator=g)).to(f1.device)
         alt = {"workload": "2160x3840 -> 270x480, D=256, 4 levels r=4, one iteration"}
-        for prec in ("bf16x3", "bf16"):
+        for prec in ("bf16x3", "fp16_fp8", "bf16"):
             blk = rr.AlternateCorrBlock(a1, a2, num_levels=4, radius=4, precision=prec)
             alt[f"ours_{prec}_ms"] = timeit(lambda: blk(c4), 2, 10)
         if ext is not None:

@@ -310,7 +310,18 @@ int rc_alt_corr_fwd(const float *fmap1, const float *fmap2, const float *coords,
  * spatial size (H1, W1) -- a band of query rows of a larger frame, coords and out then are (B, 2, H1, W1)
  * and (B, L*(2r+1)^2, H1, W1) -- against the full (H2, W2) fmap2 pyramid: that is how one large pair is
  * split over several GPUs by query rows.
+ *
+ * RC_PREC_FP16_FP8 on this path (2/3 of BF16X3's tensor work and operand traffic, ~1e-5 normwise): the maps are
+ * prepared by rc_alt_prep_fmap_level_f8 -- hi as fp16, and instead of lo the 8-bit pair map (same byte size) -- after
+ * rc_alt_absmax has put the bits of max|x| per batch item into amax (B words, ZERO-FILLED by the caller; one call per
+ * feature map; the level-0 magnitude serves every pooled level); side = 0 for fmap1, 1 for fmap2.  The setup takes the
+ * pair maps in place of the lo maps with precision = RC_PREC_FP16_FP8, then rc_alt_corr_pyramid_set_norm hands it the
+ * two amax arrays (device memory, alive as long as the setup is used).
  */
+int rc_alt_absmax(const float *fmap, unsigned int *amax, int B, int C, int H, int W, void *stream);
+int rc_alt_prep_fmap_level_f8(const float *fmap, void *hi, void *pair, const unsigned int *amax, int side, int B, int C,
+                              int H, int W, int level, void *stream);
+int rc_alt_corr_pyramid_set_norm(void *setup, const unsigned int *amax1, const unsigned int *amax2);
 int rc_alt_prep_fmap(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, void *stream);
 int rc_alt_prep_fmap_level(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level,
                            void *stream);
@@ -364,8 +375,17 @@ int rc_alt_corr_bwd_det(const float *fmap1, const float *fmap2, const float *coo
  *                rc_conv_weight_bytes() bytes (fp16, [channel block][tap][Cout][64])
  *   bias       : (Cout) fp32 or NULL;   act : RC_ACT_*;   out : (B, Cout, H, W) fp32
  * Cout a multiple of 16, <= 256 (wider layers: call per slice of output channels); KH, KW odd with a halo tile of at
- * most 640 pixels: KH * (128 + KW - 1) for KW > 1, (8 + KH - 1) * 16 for KW = 1 (1x1, 3x3, 1x5, 5x1, 3x1, 1x3, ...).  Operands are rounded to fp16 (saturating), one pass,
+ * most 400 pixels: KH * (128 + KW - 1) for KW > 1, (8 + KH - 1) * 16 for KW = 1 (1x1, 3x3, 1x5, 5x1, 3x5, 1x3, ...).  Operands are rounded to fp16 (saturating), one pass,
  * fp32 accumulation: the class of TF32, which is what cuDNN runs these layers in by torch's default.  Forward only.
+ *
+ * rc_conv2d_ex_fwd is the same convolution for tensors that are channel slices of wider ones and with the GRU's
+ * element-wise steps in the epilogue (core/update.py:43-46,50-53: z, r, r*h, (1-z)*h + z*q), so that a GRU half is two
+ * launches and nothing else:
+ *   x1_bs, x2_bs, out_bs, aux1_bs, aux2_bs : floats from one batch item to the next (0 = dense, C * H * W)
+ *   epilogue = RC_EPI_NONE     : out = act(.)
+ *              RC_EPI_MUL_FROM : out[b, o] = act(.) * (o >= split ? aux1[b, o - split] : 1)     z | r*h in one pass
+ *              RC_EPI_GRU      : out[b, o] = (1 - aux1[b, o]) * aux2[b, o] + aux1[b, o] * act(.)   aux1 = z, aux2 = h
+ *   (out may alias aux2 in RC_EPI_GRU -- every element is read before it is written by the same thread -- but no input)
  */
 #define RC_ACT_NONE 0
 #define RC_ACT_RELU 1
@@ -375,6 +395,13 @@ size_t rc_conv_weight_bytes(int Cout, int Cin, int KH, int KW);
 int rc_conv_prep_weight(const float *weight, void *wprep, int Cout, int Cin, int KH, int KW, void *stream);
 int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, const float *bias, float *out, int B,
                   int Cin, int Cout, int H, int W, int KH, int KW, int act, void *stream);
+#define RC_EPI_NONE 0
+#define RC_EPI_MUL_FROM 1
+#define RC_EPI_GRU 2
+int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, long long x2_bs, const void *wprep,
+                     const float *bias, float *out, long long out_bs, int B, int Cin, int Cout, int H, int W, int KH,
+                     int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs, const float *aux2,
+                     long long aux2_bs, void *stream);
 
 /*
  * RAFT.upsample_flow (core/raft.py:72-83): convex 8x upsampling of the flow field, one launch instead of

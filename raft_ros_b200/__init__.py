@@ -7,11 +7,13 @@ Only the correlation path of the reference (core/corr.py, core/utils/utils.py:57
 alt_cuda_corr/) lives here, plus the two fusions into its neighbours:
 `encoder_head` (the encoder's output 1x1 convolution emitting the build's operand maps) and
 `CorrBlock.lookup_convc1` (the lookup fused into the motion encoder's first convolution);
-everything else of RAFT stays the reference's own torch code.
+`conv2d_act` / `conv2d_fused` / `upsample_flow` for the rest of the per-iteration update, and the host mirrors `UpdateBlock`
+and `FusedRAFT` that run a user's reference-built model through all of them; the encoders' residual stages stay torch.
 """
 from . import alt_cuda_corr  # noqa: F401
 from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION, PreparedFeatures, encoder_head  # noqa: F401
-from .utils import bilinear_sampler, conv2d_act, coords_grid, upsample_flow  # noqa: F401
+from .utils import bilinear_sampler, conv2d_act, conv2d_fused, coords_grid, upsample_flow  # noqa: F401
+from .update import FusedRAFT, UpdateBlock  # noqa: F401
 
 __all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr", "encoder_head",
-           "PreparedFeatures", "upsample_flow", "conv2d_act"]
+           "PreparedFeatures", "upsample_flow", "conv2d_act", "conv2d_fused", "UpdateBlock", "FusedRAFT"]

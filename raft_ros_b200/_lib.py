@@ -87,6 +87,7 @@ _vp = ctypes.c_void_p
 _i = ctypes.c_int
 _f = ctypes.c_float
 _sz = ctypes.c_size_t
+_ll = ctypes.c_longlong
 
 # name -> (restype, argtypes); mirrors include/raftcorr.h one to one
 SIGNATURES = {
@@ -130,6 +131,10 @@ SIGNATURES = {
     "rc_conv_weight_bytes": (_sz, [_i, _i, _i, _i]),
     "rc_conv_prep_weight": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "rc_conv2d_fwd": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_alt_absmax": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "rc_alt_prep_fmap_level_f8": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_alt_corr_pyramid_set_norm": (_i, [_vp, _vp, _vp]),
+    "rc_conv2d_ex_fwd": (_i, [_vp, _i, _ll, _vp, _ll, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
     "rc_convex_upsample_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "rc_alt_corr_bwd_det_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "rc_alt_corr_bwd_det": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),

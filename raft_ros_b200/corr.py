@@ -760,26 +760,40 @@ class AlternateCorrBlock:
         B, C, H1, W1 = f1.shape
         _, _, H2, W2 = f2.shape
         level_shapes(H2, W2, self.num_levels)  # raises if a level would be empty
-        x3 = self._prec == _lib.RC_PREC_BF16X3
+        f8 = self._prec == _lib.RC_PREC_FP16_FP8
+        x3 = self._prec == _lib.RC_PREC_BF16X3 or f8  # two maps per feature map
         Cp = (C + 63) // 64 * 64
         dev = f1.device
         with torch.cuda.device(dev):
-            def prep(f, H, W, level):
-                hi = torch.empty((B, H >> level, W >> level, Cp), dtype=torch.bfloat16, device=dev)
+            if f8:  # power-of-two normalisation per batch item from the largest magnitude of each level-0 map
+                self._amax = torch.zeros((2, B), dtype=torch.int32, device=dev)
+                for i, (f, H, W) in enumerate(((f1, H1, W1), (f2, H2, W2))):
+                    _lib.check(L.rc_alt_absmax(f.data_ptr(), self._amax[i].data_ptr(), B, C, H, W, _stream()), "rc_alt_absmax")
+
+            def prep(f, H, W, level, side=0):
+                hi = torch.empty((B, H >> level, W >> level, Cp), dtype=torch.float16 if f8 else torch.bfloat16, device=dev)
                 lo = torch.empty_like(hi) if x3 else None
+                if f8:
+                    rc = L.rc_alt_prep_fmap_level_f8(f.data_ptr(), hi.data_ptr(), lo.data_ptr(), self._amax[side].data_ptr(), side,
+                                                     B, C, H, W, level, _stream())
+                    _lib.check(rc, "rc_alt_prep_fmap_level_f8")
+                    return hi, lo
                 rc = L.rc_alt_prep_fmap_level(f.data_ptr(), hi.data_ptr(), lo.data_ptr() if x3 else None, B, C, H, W, level,
                                               _stream())
                 _lib.check(rc, "rc_alt_prep_fmap_level")
                 return hi, lo
 
             self._f1_tc = prep(f1, H1, W1, 0)
-            self._f2_tc = [prep(f2, H2, W2, l) for l in range(self.num_levels)]
+            self._f2_tc = [prep(f2, H2, W2, l, 1) for l in range(self.num_levels)]
             self._setup = ctypes.create_string_buffer(int(L.rc_alt_corr_pyramid_setup_bytes()))
             f2_hi = _lib.ptr_array([t[0].data_ptr() for t in self._f2_tc])
             f2_lo = _lib.ptr_array([t[1].data_ptr() if x3 else None for t in self._f2_tc])
             rc = L.rc_alt_corr_pyramid_setup(self._setup, self._f1_tc[0].data_ptr(), self._f1_tc[1].data_ptr() if x3 else None,
                                              f2_hi, f2_lo, B, H1, W1, H2, W2, C, self.num_levels, self.radius, self._prec)
             _lib.check(rc, "rc_alt_corr_pyramid_setup")
+            if f8:
+                _lib.check(L.rc_alt_corr_pyramid_set_norm(self._setup, self._amax[0].data_ptr(), self._amax[1].data_ptr()),
+                           "rc_alt_corr_pyramid_set_norm")
             self._plan_bytes = int(L.rc_alt_corr_pyramid_plan_bytes(B, H1, W1, self.num_levels))
             self._plan = torch.empty(self._plan_bytes, dtype=torch.uint8, device=dev)
         rd = 2 * self.radius + 1

@@ -20,6 +20,8 @@
 //   main kernel : persistent, warp 4 = TMA producer, warp 5 = MMA issuer, warps 0-3 = epilogue
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
 
 #include <cstdlib>
 #include <cstring>
@@ -52,6 +54,9 @@ constexpr int kPatchBytes = 128 * kPatchStrideMax * 4;
 constexpr int kSmemBytes = 1024 + kRingBytes + kPatchBytes + 256;
 constexpr uint32_t kIdescA2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
 constexpr uint32_t kIdescA = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+// fp16 (kind::f16) or e4m3 (kind::f8f6f4) operands: both formats are code 0 (RC_PREC_FP16_FP8, see build_tc.cu)
+constexpr uint32_t kIdescF2 = (1u << 4) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+constexpr uint32_t kIdescF = (1u << 4) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr int kMaxLevels = 4;
 
 struct Maps {
@@ -68,7 +73,16 @@ struct Params {
   float *out;            // (B, L*81, H1, W1)
   const int4 *plan;      // [tile][level] = {box x0, box y0, chunks in x | shape << 16, chunks in y}
   float scale;
+  int f8;                       // RC_PREC_FP16_FP8: pass 0 = fp16 hi * hi, pass 1 = the 8-bit pair maps (both cross terms)
+  const unsigned *amax1, *amax2;  //   bits of max |x| of fmap1 / fmap2 per batch item (their power-of-two normalisation)
 };
+
+__device__ __forceinline__ float alt_norm_mul(unsigned amax_bits) {  // = build_tc.cu's norm_mul
+  if (amax_bits == 0u) return 1.0f;
+  int f = 261 - (int)(amax_bits >> 23);
+  f = f < 1 ? 1 : (f > 254 ? 254 : f);
+  return __uint_as_float((unsigned)f << 23);
+}
 
 // ------------------------------------------------------------------ plan
 template <int R, int NCTA>
@@ -182,6 +196,7 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
   const uint32_t tmem_base = *tmem_slot;
   const int per_item = P.tiles_x * P.tiles_y;
   const int steps = P.k_blocks * P.npass;  // operand-pair steps per chunk
+  const int a_lo_pass = P.f8 ? 1 : 2;      // the pass that takes fmap1's second map (bf16x3: lo * hi is the third)
 
   if (warp == kProducerWarp) {
     if (lane == 0) {
@@ -204,11 +219,11 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
                 uint8_t *sp = smem + stage * kStageBytes;
                 if (NCTA == 1) {
                   mbar_expect_tx(&full[stage], kStageBytes);
-                  tma_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
+                  tma_load_4d(sp, &M.a[pr == a_lo_pass ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
                   tma_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
                 } else {
                   if (leader) mbar_expect_tx(&full[stage], 2 * kStageBytes);  // both CTAs' bytes land on the leader's barrier
-                  tma2_load_4d(sp, &M.a[pr == 2 ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
+                  tma2_load_4d(sp, &M.a[pr == a_lo_pass ? 1 : 0], &full[stage], kb * TK, tx0, ty0, b);
                   tma2_load_4d(sp + A_BYTES, &M.b[l][shape][pr == 1 ? 1 : 0], &full[stage], kb * TK, ox, oy, b);
                   if (!leader) mbar_arrive_leader(&full[stage]);
                 }
@@ -235,11 +250,20 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
               tc_fence_after();
               const uint32_t sa = base_u32 + stage * kStageBytes;
               const uint64_t ad = make_sw128_desc(sa), bd = make_sw128_desc(sa + A_BYTES);
+              if (P.f8 && (s & 1)) {  // npass = 2: odd steps are the 8-bit pair maps, K = 32 per instruction
 #pragma unroll
-              for (int k = 0; k < TK / UK; ++k) {
-                const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);
-                if (NCTA == 1) umma_bf16(d_tmem, ad + koff, bd + koff, kIdescA, (s | k) != 0 ? 1u : 0u);
-                else umma2_bf16(d_tmem, ad + koff, bd + koff, kIdescA2, (s | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < 4; ++k) {
+                  if (NCTA == 1) umma_f8(d_tmem, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), kIdescF, 1u);
+                  else umma2_f8(d_tmem, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), kIdescF2, 1u);
+                }
+              } else {
+                const uint32_t id1 = P.f8 ? kIdescF : kIdescA, id2 = P.f8 ? kIdescF2 : kIdescA2;
+#pragma unroll
+                for (int k = 0; k < TK / UK; ++k) {
+                  const uint64_t koff = (uint64_t)((k * UK * 2) >> 4);
+                  if (NCTA == 1) umma_bf16(d_tmem, ad + koff, bd + koff, id1, (s | k) != 0 ? 1u : 0u);
+                  else umma2_bf16(d_tmem, ad + koff, bd + koff, id2, (s | k) != 0 ? 1u : 0u);
+                }
               }
               if (NCTA == 1) umma_commit(&empty[stage]);
               else umma2_commit_both(&empty[stage]);
@@ -347,8 +371,10 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
           }
         // bilinear taps from the patch, straight into the final layout
         if (pvalid) {
-          const float w00 = (1.0f - dy) * (1.0f - dx) * P.scale, w01 = (1.0f - dy) * dx * P.scale;
-          const float w10 = dy * (1.0f - dx) * P.scale, w11 = dy * dx * P.scale;
+          float sc = P.scale;
+          if (P.f8) sc = sc * (1.0f / alt_norm_mul(__ldg(P.amax1 + b))) * (1.0f / alt_norm_mul(__ldg(P.amax2 + b)));
+          const float w00 = (1.0f - dy) * (1.0f - dx) * sc, w01 = (1.0f - dy) * dx * sc;
+          const float w10 = dy * (1.0f - dx) * sc, w11 = dy * dx * sc;
           float *o = P.out + ((size_t)b * CH + (size_t)l * NTAP) * HW + (size_t)y * P.W1 + x;
 #pragma unroll
           for (int i = 0; i < RD; ++i) {      // x offset (slow index)
@@ -457,6 +483,57 @@ alt_prep_pool_kernel(const float *__restrict__ f, __nv_bfloat16 *__restrict__ hi
   }
 }
 
+// RC_PREC_FP16_FP8 flavour of the two kernels above: the map is multiplied by the power of two of its batch item's
+// largest magnitude (alt_norm_mul), hi = fp16, and the second map holds, per pixel and 64 channels, 128 bytes of e4m3:
+// [16 lo | hi / 16] for fmap1 (side 0), [hi / 16 | 16 lo] for fmap2 (side 1), so that ONE 8-bit contraction over the 128
+// gives both cross terms (build_tc.cu explains the arithmetic).  Pooled levels are means, so level 0's magnitude bounds them.
+template <int LVL>
+__global__ void __launch_bounds__(256)
+alt_prep_f8_kernel(const float *__restrict__ f, __half *__restrict__ hi, uint8_t *__restrict__ pair, const unsigned *__restrict__ amax,
+                   int side, int C, int Cp, int H, int W) {
+  __shared__ float tile[32][33];
+  const int Hl = H >> LVL, Wl = W >> LVL, HWl = Hl * Wl;
+  const int b = blockIdx.z;
+  const float *src = f + (size_t)b * C * H * W;
+  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float s = alt_norm_mul(__ldg(amax + b));
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int d = d0 + ty + 8 * i, p = p0 + tx;
+    float v = 0.0f;
+    if (d < C && p < HWl) v = pooled_at<LVL>(src + (size_t)d * H * W, W, p / Wl, p % Wl) * s;
+    tile[ty + 8 * i][tx] = v;
+  }
+  __syncthreads();
+  const int off_lo = side ? 64 : 0, off_hi = side ? 0 : 64;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, d = d0 + tx;
+    if (p < HWl && d < Cp) {
+      const float x = tile[tx][ty + 8 * i];
+      const __half xh = __float2half_rn(x);
+      const float h = __half2float(xh);
+      hi[((size_t)b * HWl + p) * Cp + d] = xh;
+      uint8_t *row = pair + ((size_t)b * HWl + p) * Cp * 2 + (size_t)(d >> 6) * 128 + (d & 63);
+      row[off_lo] = (uint8_t)__nv_cvt_float_to_fp8((x - h) * 16.0f, __NV_SATFINITE, __NV_E4M3);
+      row[off_hi] = (uint8_t)__nv_cvt_float_to_fp8(h * 0.0625f, __NV_SATFINITE, __NV_E4M3);
+    }
+  }
+}
+
+// largest magnitude per batch item (amax zero-filled by the caller; non-negative floats order like their bit patterns)
+__global__ void __launch_bounds__(256)
+alt_absmax_item_kernel(const float *__restrict__ f, unsigned *__restrict__ amax, long long per_item) {
+  const float *src = f + (size_t)blockIdx.y * per_item;
+  float m = 0.0f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_item; i += (long long)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(__ldg(src + i)));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(amax + blockIdx.y, __float_as_uint(m));
+}
+
 // ------------------------------------------------------------------ host
 static int map4(CUtensorMap *tm, const void *base, int Cp, int W, int H, int B, int bw, int bh) {
   const unsigned long long dims[4] = {(unsigned long long)Cp, (unsigned long long)W, (unsigned long long)H, (unsigned long long)B};
@@ -516,6 +593,37 @@ int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, 
   return RC_OK;
 }
 
+int launch_alt_absmax(const float *fmap, unsigned *amax, int B, long long per_item, cudaStream_t st) {
+  const unsigned bx = (unsigned)std::min<long long>(256, (per_item + 255) / 256);
+  alttc::alt_absmax_item_kernel<<<dim3(bx, (unsigned)B), 256, 0, st>>>(fmap, amax, per_item);
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
+int launch_alt_prep_f8(const float *fmap, void *hi, void *pair, const unsigned *amax, int side, int B, int C, int H, int W,
+                       int level, cudaStream_t st) {
+  using namespace alttc;
+  const int Cp = (C + 63) / 64 * 64, HWl = (H >> level) * (W >> level);
+  if (HWl <= 0) {
+    set_error("rc_alt_prep_fmap_level_f8: level %d of a %dx%d map is empty", level, H, W);
+    return RC_ERR_INVALID;
+  }
+  dim3 grid((unsigned)((HWl + 31) / 32), (unsigned)(Cp / 32), (unsigned)B);
+  __half *h = static_cast<__half *>(hi);
+  uint8_t *p8 = static_cast<uint8_t *>(pair);
+  switch (level) {
+    case 0: alt_prep_f8_kernel<0><<<grid, 256, 0, st>>>(fmap, h, p8, amax, side, C, Cp, H, W); break;
+    case 1: alt_prep_f8_kernel<1><<<grid, 256, 0, st>>>(fmap, h, p8, amax, side, C, Cp, H, W); break;
+    case 2: alt_prep_f8_kernel<2><<<grid, 256, 0, st>>>(fmap, h, p8, amax, side, C, Cp, H, W); break;
+    case 3: alt_prep_f8_kernel<3><<<grid, 256, 0, st>>>(fmap, h, p8, amax, side, C, Cp, H, W); break;
+    default:
+      set_error("rc_alt_prep_fmap_level_f8: level %d unsupported (0..3)", level);
+      return RC_ERR_UNSUPPORTED;
+  }
+  RC_CUDA(cudaGetLastError());
+  return RC_OK;
+}
+
 // One CTA per 8 x 16 query tile by default; RAFT_CORR_ALT_CTAS=2 selects CTA pairs (a 16 x 16 tile per pair).  Measured at
 // 2160x3840: the pairs issue 37 % fewer MMAs (15 instead of 24 chunks per 256 query pixels) but every epilogue thread then
 // scans the chunks of the larger box, and the epilogue becomes the bound: 0.434 vs 0.406 ms (bf16x3), 0.231 vs 0.219 (bf16).
@@ -546,7 +654,8 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
     set_error("rc_alt_corr_pyramid: channel pitch %d must be a multiple of %d", Cp, TK);
     return RC_ERR_INVALID;
   }
-  const bool x3 = precision == RC_PREC_BF16X3;
+  const bool f8 = precision == RC_PREC_FP16_FP8;
+  const bool x3 = precision == RC_PREC_BF16X3 || f8;  // two maps per feature map
   const int ncta = alt_ctas();
   Setup S{};
   S.ncta = ncta;
@@ -569,7 +678,8 @@ int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *c
   }
   P.B = B; P.H1 = H1; P.W1 = W1; P.L = L;
   P.k_blocks = Cp / TK;
-  P.npass = x3 ? 3 : 1;
+  P.npass = f8 ? 2 : (x3 ? 3 : 1);
+  P.f8 = f8 ? 1 : 0;
   P.tiles_x = (W1 + QW - 1) / QW;
   P.tiles_y = (H1 + QH * ncta - 1) / (QH * ncta);
   P.total_tiles = (long long)B * P.tiles_x * P.tiles_y;
@@ -586,7 +696,7 @@ static int alt_tc_run_r(const alttc::Setup &S, cudaStream_t st) {
   {
     const unsigned blocks = (unsigned)((P.total_tiles + 3) / 4);
     RC_CUDA(launch_pdl(alt_plan_kernel<R, NCTA>, dim3(blocks), dim3(128), 0, st, P.coords, const_cast<int4 *>(P.plan), P.B, P.H1,
-                       P.W1, P.L, P.tiles_x, P.tiles_y, P.total_tiles, P.h2[0], P.w2[0], P.npass == 3 ? 1 : 0));
+                       P.W1, P.L, P.tiles_x, P.tiles_y, P.total_tiles, P.h2[0], P.w2[0], P.npass >= 2 ? 1 : 0));
   }
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
   auto kern = alt_tc_kernel<R, NCTA>;
@@ -620,6 +730,10 @@ int alt_tc_run(const void *blob, const float *coords, float *out, float scale, v
     set_error("rc_alt_corr_pyramid_run: the setup blob was not initialised by rc_alt_corr_pyramid_setup");
     return RC_ERR_INVALID;
   }
+  if (S.P.f8 && (S.P.amax1 == nullptr || S.P.amax2 == nullptr)) {
+    set_error("rc_alt_corr_pyramid_run: RC_PREC_FP16_FP8 needs rc_alt_corr_pyramid_set_norm after the setup");
+    return RC_ERR_INVALID;
+  }
   const size_t need = alt_tc_plan_bytes(S.P.B, S.P.H1, S.P.W1, S.P.L);
   if (plan_ws == nullptr || plan_bytes < need || (reinterpret_cast<uintptr_t>(plan_ws) & 15) != 0) {
     set_error("rc_alt_corr_pyramid: plan scratch missing, misaligned or too small (%zu < %zu bytes)", plan_bytes, need);
@@ -631,6 +745,20 @@ int alt_tc_run(const void *blob, const float *coords, float *out, float scale, v
   S.P.scale = scale;
   if (S.ncta == 2) return S.radius == 3 ? alt_tc_run_r<3, 2>(S, st) : alt_tc_run_r<4, 2>(S, st);
   return S.radius == 3 ? alt_tc_run_r<3, 1>(S, st) : alt_tc_run_r<4, 1>(S, st);
+}
+
+int alt_tc_set_norm(void *blob, const unsigned *amax1, const unsigned *amax2) {
+  using namespace alttc;
+  alignas(64) Setup S;
+  memcpy(&S, blob, sizeof(S));
+  if (S.magic != kSetupMagic) {
+    set_error("rc_alt_corr_pyramid_set_norm: the setup blob was not initialised by rc_alt_corr_pyramid_setup");
+    return RC_ERR_INVALID;
+  }
+  S.P.amax1 = amax1;
+  S.P.amax2 = amax2;
+  memcpy(blob, &S, sizeof(S));
+  return RC_OK;
 }
 
 int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo,

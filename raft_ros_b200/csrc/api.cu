@@ -442,6 +442,27 @@ int rc_alt_prep_fmap_level(const float *fmap, void *hi, void *lo, int B, int C, 
   return launch_alt_prep_pooled(fmap, hi, lo, B, C, H, W, level, static_cast<cudaStream_t>(stream));
 }
 
+int rc_alt_absmax(const float *fmap, unsigned int *amax, int B, int C, int H, int W, void *stream) {
+  RC_CHECK_ARG(fmap && amax, "rc_alt_absmax: null pointer");
+  RC_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "rc_alt_absmax: all sizes must be positive");
+  return launch_alt_absmax(fmap, amax, B, (long long)C * H * W, static_cast<cudaStream_t>(stream));
+}
+
+int rc_alt_prep_fmap_level_f8(const float *fmap, void *hi, void *pair, const unsigned int *amax, int side, int B, int C, int H,
+                              int W, int level, void *stream) {
+  RC_CHECK_ARG(fmap && hi && pair && amax, "rc_alt_prep_fmap_level_f8: null pointer");
+  RC_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "rc_alt_prep_fmap_level_f8: all sizes must be positive");
+  RC_CHECK_ARG(level >= 0 && level <= 3 && (side == 0 || side == 1), "rc_alt_prep_fmap_level_f8: level 0..3, side 0 (fmap1) or 1 (fmap2)");
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(hi) & 15) == 0 && (reinterpret_cast<uintptr_t>(pair) & 15) == 0,
+               "rc_alt_prep_fmap_level_f8: outputs must be 16-byte aligned");
+  return launch_alt_prep_f8(fmap, hi, pair, amax, side, B, C, H, W, level, static_cast<cudaStream_t>(stream));
+}
+
+int rc_alt_corr_pyramid_set_norm(void *setup, const unsigned int *amax1, const unsigned int *amax2) {
+  RC_CHECK_ARG(setup && amax1 && amax2, "rc_alt_corr_pyramid_set_norm: null pointer");
+  return alt_tc_set_norm(setup, amax1, amax2);
+}
+
 size_t rc_alt_corr_pyramid_setup_bytes(void) { return alt_tc_setup_bytes(); }
 
 int rc_alt_corr_pyramid_setup(void *setup, const void *fmap1_hi, const void *fmap1_lo, const void *const *fmap2_hi,
@@ -450,8 +471,8 @@ int rc_alt_corr_pyramid_setup(void *setup, const void *fmap1_hi, const void *fma
   if (int rc = check_geometry("rc_alt_corr_pyramid_setup", B, H2, W2, num_levels)) return rc;
   RC_CHECK_ARG(setup && fmap1_hi && fmap2_hi, "rc_alt_corr_pyramid_setup: null pointer");
   RC_CHECK_ARG(H1 > 0 && W1 > 0 && C > 0, "rc_alt_corr_pyramid_setup: sizes must be positive");
-  RC_CHECK_ARG(precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16,
-               "rc_alt_corr_pyramid_setup: precision must be RC_PREC_BF16X3 or RC_PREC_BF16");
+  RC_CHECK_ARG(precision == RC_PREC_BF16X3 || precision == RC_PREC_BF16 || precision == RC_PREC_FP16_FP8,
+               "rc_alt_corr_pyramid_setup: precision must be RC_PREC_BF16X3, RC_PREC_BF16 or RC_PREC_FP16_FP8");
   RC_CHECK_ARG(precision == RC_PREC_BF16 || (fmap1_lo && fmap2_lo), "rc_alt_corr_pyramid_setup: BF16X3 needs the lo parts");
   for (int l = 0; l < num_levels; ++l) {
     RC_CHECK_ARG(fmap2_hi[l] != nullptr, "rc_alt_corr_pyramid_setup: level %d pointer is null", l);
@@ -531,6 +552,35 @@ int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, c
   RC_CHECK_ARG(act >= RC_ACT_NONE && act <= RC_ACT_TANH, "rc_conv2d_fwd: unknown activation %d", act);
   RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "rc_conv2d_fwd: wprep must be 128-byte aligned");
   return launch_conv_tc(x1, C1, x2, wprep, bias, out, B, Cin, Cout, H, W, KH, KW, act, static_cast<cudaStream_t>(stream));
+}
+
+int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, long long x2_bs, const void *wprep,
+                     const float *bias, float *out, long long out_bs, int B, int Cin, int Cout, int H, int W, int KH,
+                     int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs, const float *aux2,
+                     long long aux2_bs, void *stream) {
+  const char *fn = "rc_conv2d_ex_fwd";
+  RC_CHECK_ARG(x1 && wprep && out, "%s: null pointer", fn);
+  RC_CHECK_ARG(B > 0 && H > 0 && W > 0 && (long long)B * H * ((W + 127) / 128) < 0x7fffffffLL, "%s: bad sizes", fn);
+  if (int rc = check_conv(fn, Cout, Cin, KH, KW)) return rc;
+  RC_CHECK_ARG(C1 > 0 && C1 <= Cin && (C1 == Cin || x2 != nullptr), "%s: C1 = %d of Cin = %d needs a second input", fn, C1, Cin);
+  RC_CHECK_ARG(act >= RC_ACT_NONE && act <= RC_ACT_TANH, "%s: unknown activation %d", fn, act);
+  RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "%s: wprep must be 128-byte aligned", fn);
+  const long long hw = (long long)H * W;
+  RC_CHECK_ARG((x1_bs == 0 || x1_bs >= hw * C1) && (x2_bs == 0 || x2_bs >= hw * (Cin - C1)) && (out_bs == 0 || out_bs >= hw * Cout),
+               "%s: a batch stride is smaller than the tensor it strides", fn);
+  RC_CHECK_ARG(epilogue >= RC_EPI_NONE && epilogue <= RC_EPI_GRU, "%s: unknown epilogue %d", fn, epilogue);
+  ConvExtra ex{};
+  ex.x1_bs = x1_bs; ex.x2_bs = x2_bs; ex.out_bs = out_bs;
+  ex.epi = epilogue;
+  if (epilogue == RC_EPI_MUL_FROM) {
+    RC_CHECK_ARG(aux1 && split >= 0 && split <= Cout, "%s: RC_EPI_MUL_FROM needs aux1 and 0 <= split <= Cout", fn);
+    ex.split = split; ex.aux1 = aux1; ex.aux1_bs = aux1_bs ? aux1_bs : hw * (Cout - split);
+  } else if (epilogue == RC_EPI_GRU) {
+    RC_CHECK_ARG(aux1 && aux2, "%s: RC_EPI_GRU needs aux1 (z) and aux2 (h)", fn);
+    ex.aux1 = aux1; ex.aux2 = aux2;
+    ex.aux1_bs = aux1_bs ? aux1_bs : hw * Cout; ex.aux2_bs = aux2_bs ? aux2_bs : hw * Cout;
+  }
+  return launch_conv_tc(x1, C1, x2, wprep, bias, out, B, Cin, Cout, H, W, KH, KW, act, static_cast<cudaStream_t>(stream), &ex);
 }
 
 int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int N, int H, int W, void *stream) {

@@ -125,6 +125,10 @@ int launch_alt_bwd_det(const float *f1, const float *f2, const float *coords, co
                        int H1, int W1, int H2, int W2, int C, int r, void *ws, cudaStream_t st);
 int launch_alt_prep(const float *fmap, void *hi, void *lo, int B, int C, int HW, cudaStream_t st);
 int launch_alt_prep_pooled(const float *fmap, void *hi, void *lo, int B, int C, int H, int W, int level, cudaStream_t st);
+int launch_alt_absmax(const float *fmap, unsigned *amax, int B, long long per_item, cudaStream_t st);
+int launch_alt_prep_f8(const float *fmap, void *hi, void *pair, const unsigned *amax, int side, int B, int C, int H, int W,
+                       int level, cudaStream_t st);
+int alt_tc_set_norm(void *blob, const unsigned *amax1, const unsigned *amax2);
 size_t alt_tc_plan_bytes(int B, int H1, int W1, int L);
 size_t alt_tc_setup_bytes();
 int alt_tc_setup(void *blob, const void *f1_hi, const void *f1_lo, const void *const *f2_hi, const void *const *f2_lo, int B,
@@ -137,8 +141,15 @@ int launch_alt_tc(const void *f1_hi, const void *f1_lo, const void *const *f2_hi
 int launch_pool_tail(const LevelPtrs &lv, int B, int h, int w, int first, int L, cudaStream_t st);
 size_t conv_weight_bytes(int Cout, int Cin, int KH, int KW);
 int launch_conv_prep_weight(const float *w, void *wp, int Cout, int Cin, int KH, int KW, cudaStream_t st);
+// what rc_conv2d_ex_fwd adds to rc_conv2d_fwd: batch strides (channel slices of wider tensors) and the fused GRU epilogues
+struct ConvExtra {
+  long long x1_bs, x2_bs, out_bs;  // floats between batch items; 0 = dense
+  int epi, split;
+  const float *aux1, *aux2;
+  long long aux1_bs, aux2_bs;
+};
 int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, const float *bias, float *out, int B, int Cin, int Cout,
-                   int H, int W, int KH, int KW, int act, cudaStream_t st);
+                   int H, int W, int KH, int KW, int act, cudaStream_t st, const ConvExtra *ex = nullptr);
 int launch_convex_upsample(const float *flow, const float *mask, float *out, int N, int H, int W, cudaStream_t st);
 int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
                         int H, int W, int Ho, int Wo, cudaStream_t st);

@@ -44,6 +44,10 @@ struct Params {
   const float *x1, *x2;  // input = channels [0, C1) of x1 followed by [0, Cin - C1) of x2 (x2 may be null)
   const float *bias;
   float *out;
+  long long x1_bs, x2_bs, out_bs;  // floats from one batch item to the next (a channel slice of a wider tensor has more than C*H*W)
+  int epi, split;                  // RC_EPI_*: what the epilogue does with act(acc + bias)
+  const float *aux1, *aux2;
+  long long aux1_bs, aux2_bs;
   int B, C1, Cin, Cout, H, W, KH, KW, act;
   int TH, TW;  // output tile: TH rows x TW columns = 128 pixels (1 x 128, or 8 x 16 for filters one column wide)
   int ncb, tiles_x, tiles_y, total_tiles;
@@ -65,7 +69,7 @@ __device__ __forceinline__ float activate(float v, int act) {
 // TMA_IN: the input reaches the converters through a ring of TMA boxes (rows of 16 B multiples, i.e. W % 4 == 0, and a
 // first tensor whose channel count is a multiple of 8); the box's zero fill outside the image IS the padding.  Otherwise
 // the converters read global memory themselves (any width; slower: few bytes in flight per SM).
-template <bool TMA_IN>
+template <bool TMA_IN, bool EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX1,
                const __grid_constant__ CUtensorMap tmX2, const Params P) {
@@ -173,7 +177,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int c = c0 + j;
-            const float *src = c < P.C1 ? P.x1 + ((size_t)b * P.C1 + c) * HW : P.x2 + ((size_t)b * (P.Cin - P.C1) + (c - P.C1)) * HW;
+            const float *src = c < P.C1 ? P.x1 + (size_t)b * P.x1_bs + (size_t)c * HW : P.x2 + (size_t)b * P.x2_bs + (size_t)(c - P.C1) * HW;
             v[j] = (inside && c < P.Cin) ? __ldg(src + (size_t)iy * W + ix) : 0.0f;
           }
         };
@@ -215,8 +219,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       mbar_wait(&acc_full[acc], phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(acc * 256);
-      float *o = P.out + ((size_t)b * Cout + n0) * HW + (size_t)y * W + x;
+      const size_t pix = (size_t)y * W + x;
+      float *o = P.out + (size_t)b * P.out_bs + (size_t)n0 * HW + pix;
       const float *bs = bias_s + n0;
+      // RC_EPI_MUL_FROM: channels from `split` on are multiplied by aux1[b, c - split] (the GRU's r * h)
+      // RC_EPI_GRU:      out = (1 - z) * h + z * act(.), z = aux1[b, c], h = aux2[b, c]            (core/update.py:46,53)
+      const float *a1 = P.aux1 ? P.aux1 + (size_t)b * P.aux1_bs + pix : nullptr;
+      const float *a2 = P.aux2 ? P.aux2 + (size_t)b * P.aux2_bs + pix : nullptr;
+      auto finish = [&](float v, int c) {  // c: filter index within the layer
+        v = activate(v + bias_s[c], P.act);
+        if constexpr (EPI) {
+          if (P.epi == RC_EPI_MUL_FROM) {
+            if (c >= P.split) v *= __ldg(a1 + (size_t)(c - P.split) * HW);
+          } else if (P.epi == RC_EPI_GRU) {
+            const float z = __ldg(a1 + (size_t)c * HW), h = __ldg(a2 + (size_t)c * HW);
+            v = (1.0f - z) * h + z * v;
+          }
+        }
+        return v;
+      };
+      (void)bs;
+      (void)a1;
+      (void)a2;
       int c0 = 0;
       for (; c0 + 32 <= Cn; c0 += 32) {
         float v[32];
@@ -224,7 +248,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         tmem_ld_wait();
         if (pv) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bs[c0 + i], P.act));
+          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, finish(v[i], n0 + c0 + i));
         }
       }
       if (c0 < Cn) {  // Cn is a multiple of 16
@@ -233,7 +257,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         tmem_ld_wait();
         if (pv) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, activate(v[i] + bs[c0 + i], P.act));
+          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, finish(v[i], n0 + c0 + i));
         }
       }
       tc_fence_before();
@@ -350,7 +374,7 @@ int launch_conv_prep_weight(const float *w, void *wp, int Cout, int Cin, int KH,
 }
 
 int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, const float *bias, float *out, int B, int Cin, int Cout,
-                   int H, int W, int KH, int KW, int act, cudaStream_t st) {
+                   int H, int W, int KH, int KW, int act, cudaStream_t st, const ConvExtra *ex) {
   using namespace cv;
   const int ncb = (Cin + 63) / 64, T = KH * KW;
   int dev = 0, sms = 148;
@@ -358,6 +382,15 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   Params P{};
   P.x1 = x1; P.x2 = x2; P.bias = bias; P.out = out;
+  const long long hw = (long long)H * W;
+  P.x1_bs = ex && ex->x1_bs ? ex->x1_bs : hw * C1;
+  P.x2_bs = ex && ex->x2_bs ? ex->x2_bs : hw * (Cin - C1);
+  P.out_bs = ex && ex->out_bs ? ex->out_bs : hw * Cout;
+  if (ex) {
+    P.epi = ex->epi; P.split = ex->split;
+    P.aux1 = ex->aux1; P.aux2 = ex->aux2;
+    P.aux1_bs = ex->aux1_bs; P.aux2_bs = ex->aux2_bs;
+  }
   P.B = B; P.C1 = C1; P.Cin = Cin; P.Cout = Cout; P.H = H; P.W = W; P.KH = KH; P.KW = KW; P.act = act;
   P.ncb = ncb;
   if (KW == 1 && KH > 1) { P.TH = 8; P.TW = 16; }  // vertical filters: a square-ish tile keeps the halo at 1.5x instead of KH x
@@ -386,28 +419,30 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   const int items = P.total_tiles * P.nparts;
   const int grid = items < sms ? items : sms;
   const int C2 = Cin - C1;
-  const bool tma_in = W % 4 == 0 && (reinterpret_cast<uintptr_t>(x1) & 15) == 0 && P.BH * P.BW <= kMaxHaloPix &&
-                      C1 >= 8 && (C2 == 0 || (C2 >= 8 && C1 % 8 == 0 && (reinterpret_cast<uintptr_t>(x2) & 15) == 0));
+  const bool tma_in = W % 4 == 0 && (reinterpret_cast<uintptr_t>(x1) & 15) == 0 && P.BH * P.BW <= kMaxHaloPix && P.x1_bs % 4 == 0 &&
+                      C1 >= 8 && (C2 == 0 || (C2 >= 8 && C1 % 8 == 0 && (reinterpret_cast<uintptr_t>(x2) & 15) == 0 && P.x2_bs % 4 == 0));
   if (tma_in) {
     CUtensorMap tx1, tx2;
     const unsigned int box[4] = {(unsigned int)P.BW, (unsigned int)P.BH, 8, 1};
     {
       const unsigned long long dims[4] = {(unsigned long long)W, (unsigned long long)H, (unsigned long long)C1, (unsigned long long)B};
-      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * W * H * C1};
+      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * (unsigned long long)P.x1_bs};
       if (int rc = encode_tmap_f32(&tx1, x1, 4, dims, strides, box, "rc_conv2d_fwd")) return rc;
     }
     if (C2 > 0) {
       const unsigned long long dims[4] = {(unsigned long long)W, (unsigned long long)H, (unsigned long long)C2, (unsigned long long)B};
-      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * W * H * C2};
+      const unsigned long long strides[3] = {4ull * W, 4ull * W * H, 4ull * (unsigned long long)P.x2_bs};
       if (int rc = encode_tmap_f32(&tx2, x2, 4, dims, strides, box, "rc_conv2d_fwd")) return rc;
     } else {
       tx2 = tx1;
     }
-    RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    RC_CUDA(launch_pdl(conv_tc_kernel<true>, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tx1, tx2, P));
+    auto kern = P.epi != RC_EPI_NONE ? conv_tc_kernel<true, true> : conv_tc_kernel<true, false>;
+    RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    RC_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tx1, tx2, P));
   } else {
-    RC_CUDA(cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    RC_CUDA(launch_pdl(conv_tc_kernel<false>, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tm, tm, P));
+    auto kern = P.epi != RC_EPI_NONE ? conv_tc_kernel<false, true> : conv_tc_kernel<false, false>;
+    RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    RC_CUDA(launch_pdl(kern, dim3((unsigned)grid), dim3(kThreads), (size_t)kSmemBytes, st, tm, tm, tm, P));
   }
   return RC_OK;
 }

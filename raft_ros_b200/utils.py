@@ -94,6 +94,97 @@ _ACTS = {None: 0, "none": 0, "relu": 1, "sigmoid": 2, "tanh": 3}
 _CONV_CACHE = None
 
 
+_EPIS = {None: 0, "mul_from": 1, "gru": 2}
+
+
+def _chw(t, name):
+    """(B, C, H, W) fp32 CUDA tensor whose items are dense C x H x W blocks (a channel slice of a wider tensor is fine):
+    returns its batch stride in floats."""
+    if (not t.is_cuda) or t.dim() != 4 or t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be a (B,C,H,W) fp32 CUDA tensor")
+    B, C, H, W = t.shape
+    if t.stride(3) != 1 or t.stride(2) != W or t.stride(1) != H * W or (B > 1 and t.stride(0) < C * H * W):
+        raise RuntimeError(f"{name}: items must be dense C*H*W blocks (got strides {t.stride()})")
+    return t.stride(0) if B > 1 else C * H * W
+
+
+def _prepared_filters(weight, bias, o0, o1, dev, st):
+    """fp16 filter blocks (and the padded bias) of output channels [o0, o1), cached per weight / bias tensor object."""
+    global _CONV_CACHE
+    from .corr import _WeightCache
+    if _CONV_CACHE is None:
+        _CONV_CACHE = _WeightCache()
+    L = _lib.lib()
+    _, Cin, KH, KW = weight.shape
+    co = (o1 - o0 + 15) // 16 * 16  # the kernel's N granule; padded filters are zero, their outputs dropped by the caller
+
+    def make():
+        nbytes = int(L.rc_conv_weight_bytes(co, Cin, KH, KW))
+        wp_ = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+        w32 = torch.zeros((co, Cin, KH, KW), dtype=torch.float32, device=dev)
+        w32[:o1 - o0] = weight.detach()[o0:o1]
+        _lib.check(L.rc_conv_prep_weight(w32.data_ptr(), wp_.data_ptr(), co, Cin, KH, KW, st), "rc_conv_prep_weight")
+        return wp_
+
+    def make_bias():
+        b32_ = torch.zeros(co, dtype=torch.float32, device=dev)
+        b32_[:o1 - o0] = bias.detach()[o0:o1]
+        return b32_
+
+    wp = _CONV_CACHE.get(weight, ("conv", o0, o1, dev.index), make)
+    b32 = None if bias is None else _CONV_CACHE.get(bias, ("bias", o0, o1, dev.index), make_bias)
+    return wp, b32, co
+
+
+def conv2d_fused(x, weight, bias=None, act=None, out=None, epilogue=None, split=0, aux1=None, aux2=None):
+    """rc_conv2d_ex_fwd: `conv2d_act` for at most 256 filters whose inputs, output and epilogue operands may be channel
+    slices of wider tensors (no `.contiguous()` copies, the output written in place into `out`), with the GRU's
+    element-wise steps fused: epilogue "mul_from" multiplies the output channels from `split` on by `aux1` (z | r*h from
+    one convolution, core/update.py:43-45), "gru" returns (1 - aux1) * aux2 + aux1 * act(conv) (:46).  Inference only."""
+    xs = x if isinstance(x, (tuple, list)) else (x,)
+    if len(xs) not in (1, 2):
+        raise RuntimeError("conv2d_fused: x must be one tensor or a pair")
+    if torch.is_grad_enabled() and (any(t.requires_grad for t in xs) or weight.requires_grad):
+        raise RuntimeError("conv2d_fused: inference only (no gradient); use torch's convolution for training")
+    if act not in _ACTS or epilogue not in _EPIS:
+        raise ValueError(f"unknown act {act!r} / epilogue {epilogue!r}")
+    bs = [_chw(t, "x") for t in xs]
+    B, C1, H, W = xs[0].shape
+    Cin = C1 + (xs[1].shape[1] if len(xs) == 2 else 0)
+    if len(xs) == 2 and (xs[1].shape[0] != B or xs[1].shape[2:] != xs[0].shape[2:]):
+        raise RuntimeError("conv2d_fused: the two inputs must agree in batch and spatial size")
+    if weight.dim() != 4 or weight.shape[1] != Cin:
+        raise RuntimeError(f"conv2d_fused: weight must be (Cout, {Cin}, KH, KW), got {tuple(weight.shape)}")
+    Cout, _, KH, KW = weight.shape
+    if Cout > 256:
+        raise RuntimeError("conv2d_fused: at most 256 filters per call (conv2d_act slices wider layers)")
+    dev = xs[0].device
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        wp, b32, co = _prepared_filters(weight, bias, 0, Cout, dev, st)
+        if out is None:
+            out = torch.empty((B, co, H, W), dtype=torch.float32, device=dev)
+        elif out.shape != (B, co, H, W):
+            raise RuntimeError(f"conv2d_fused: out must be {(B, co, H, W)} (filters padded to a multiple of 16), got {tuple(out.shape)}")
+        obs = _chw(out, "out")
+        a1 = a2 = None
+        a1bs = a2bs = 0
+        if epilogue == "mul_from":
+            if aux1 is None or aux1.shape != (B, co - split, H, W):
+                raise RuntimeError(f"conv2d_fused: 'mul_from' needs aux1 of shape {(B, co - split, H, W)}")
+            a1, a1bs = aux1, _chw(aux1, "aux1")
+        elif epilogue == "gru":
+            if aux1 is None or aux2 is None or aux1.shape != (B, co, H, W) or aux2.shape != (B, co, H, W):
+                raise RuntimeError(f"conv2d_fused: 'gru' needs aux1 (z) and aux2 (h) of shape {(B, co, H, W)}")
+            a1, a1bs, a2, a2bs = aux1, _chw(aux1, "aux1"), aux2, _chw(aux2, "aux2")
+        rc = _lib.lib().rc_conv2d_ex_fwd(xs[0].data_ptr(), C1, bs[0], xs[1].data_ptr() if len(xs) == 2 else None,
+                                         bs[1] if len(xs) == 2 else 0, wp.data_ptr(), None if b32 is None else b32.data_ptr(),
+                                         out.data_ptr(), obs, B, Cin, co, H, W, KH, KW, _ACTS[act], _EPIS[epilogue], split,
+                                         None if a1 is None else a1.data_ptr(), a1bs, None if a2 is None else a2.data_ptr(), a2bs, st)
+        _lib.check(rc, "rc_conv2d_ex_fwd")
+    return out if co == Cout else out[:, :Cout]
+
+
 def conv2d_act(x, weight, bias=None, act=None):
     """`act(F.conv2d(x, weight, bias, padding="same"))` for the stride-1 convolutions of the per-iteration update
     (reference core/update.py:6-14,33-60,84-97,122-125) on tensor cores (rc_conv2d_fwd): filter taps re-use one fp16
@@ -102,10 +193,6 @@ def conv2d_act(x, weight, bias=None, act=None):
     act in None / "relu" / "sigmoid" / "tanh".  fp16 operands (TF32-class), fp32 accumulate and output.  Inference only.
     A filter count that is not a multiple of 16 (126 in the motion encoder, 2 in the flow head) is padded with zero
     filters inside and the result is then a channel-sliced view."""
-    global _CONV_CACHE
-    from .corr import _WeightCache
-    if _CONV_CACHE is None:
-        _CONV_CACHE = _WeightCache()
     xs = x if isinstance(x, (tuple, list)) else (x,)
     if len(xs) not in (1, 2) or any((not t.is_cuda) or t.dim() != 4 for t in xs) or not weight.is_cuda:
         raise RuntimeError("conv2d_act: x must be one or two (B,C,H,W) CUDA tensors and weight a CUDA tensor")
@@ -128,23 +215,7 @@ def conv2d_act(x, weight, bias=None, act=None):
         outs = []
         for o0 in range(0, Cout, 256):  # wider layers (the mask head's 576 channels) go slice by slice
             o1 = min(Cout, o0 + 256)
-            co = (o1 - o0 + 15) // 16 * 16  # the kernel's N granule; padded filters are zero, their outputs dropped below
-
-            def make(o0=o0, o1=o1, co=co):
-                nbytes = int(L.rc_conv_weight_bytes(co, Cin, KH, KW))
-                wp_ = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
-                w32 = torch.zeros((co, Cin, KH, KW), dtype=torch.float32, device=dev)
-                w32[:o1 - o0] = weight.detach()[o0:o1]
-                _lib.check(L.rc_conv_prep_weight(w32.data_ptr(), wp_.data_ptr(), co, Cin, KH, KW, st), "rc_conv_prep_weight")
-                return wp_
-
-            def make_bias(o0=o0, o1=o1, co=co):
-                b32_ = torch.zeros(co, dtype=torch.float32, device=dev)
-                b32_[:o1 - o0] = bias.detach()[o0:o1]
-                return b32_
-
-            wp = _CONV_CACHE.get(weight, ("conv", o0, dev.index), make)
-            b32 = None if bias is None else _CONV_CACHE.get(bias, ("bias", o0, co, dev.index), make_bias)
+            wp, b32, co = _prepared_filters(weight, bias, o0, o1, dev, st)
             out = torch.empty((B, co, H, W), dtype=torch.float32, device=dev)
             rc = L.rc_conv2d_fwd(xs[0].data_ptr(), C1, xs[1].data_ptr() if len(xs) == 2 else None, wp.data_ptr(),
                                  None if bias is None else b32.data_ptr(), out.data_ptr(), B, Cin, co, H, W, KH, KW, _ACTS[act], st)

@@ -380,7 +380,8 @@ def test_alt_backward_fmap2_grad_is_bit_reproducible(rr, monkeypatch):
     assert rc == 4 and b"workspace" in L.rc_last_error()
 
 
-ALT_TOL = {"fp32": dict(rel=5e-6, norm=3e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3)}
+ALT_TOL = {"fp32": dict(rel=5e-6, norm=3e-6), "bf16x3": dict(rel=1e-4, norm=3e-5), "bf16": dict(rel=3e-2, norm=6e-3),
+           "fp16_fp8": dict(rel=1e-4, norm=3e-5)}
 
 
 _ALT_WANT = {}
@@ -408,7 +409,7 @@ def _alt_want(geom, kind):
     return _ALT_WANT[key]
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16", "fp16_fp8"])
 @pytest.mark.parametrize("geom", [(2, 64, 24, 32, 4), (1, 256, 27, 40, 4), (1, 96, 23, 39, 3), (1, 256, 55, 128, 4)])
 @pytest.mark.parametrize("kind", ["sigma4", "sigma32", "grid", "oob", "huge"])
 def test_alternate_block_vs_oracle(rr, geom, kind, precision):
@@ -433,7 +434,7 @@ def test_alternate_block_vs_oracle(rr, geom, kind, precision):
     assert torch.equal(blk(coords), b)  # deterministic
 
 
-@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16", "fp16_fp8"])
 @pytest.mark.parametrize("geom", [(2, 128, 24, 32, 4), (1, 128, 23, 39, 3), (1, 96, 46, 62, 4)])
 def test_alternate_block_radius3(rr, geom, precision):
     """raft-small (core/raft.py:33: corr_radius = 3, 128 feature channels) on the tensor-core on-the-fly kernel,
@@ -484,7 +485,7 @@ def test_alt_prep_pools_like_avg_pool2d(rr, shape):
         assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]), (shape, level)
 
 
-@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16", "fp16_fp8"])
 def test_alternate_block_query_row_band(rr, precision):
     """A band of query rows against the full fmap2 (how one large pair is split over GPUs):
     bit-identical to the same rows of the whole-frame block when the band starts on a (16-row) tile row, and within

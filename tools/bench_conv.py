@@ -8,10 +8,15 @@ sys.path.insert(0, '.')
 import raft_ros_b200 as rr
 
 def t(fn, reps=20):
+    """device time per call: the calls are captured in a CUDA graph, so host-side launch cost does not count"""
     for _ in range(3): fn()
-    torch.cuda.synchronize(); a, e = torch.cuda.Event(True), torch.cuda.Event(True); a.record()
-    for _ in range(reps): fn()
-    e.record(); torch.cuda.synchronize(); return a.elapsed_time(e) / reps * 1e3
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps): fn()
+    g.replay(); torch.cuda.synchronize(); a, e = torch.cuda.Event(True), torch.cuda.Event(True); a.record()
+    for _ in range(3): g.replay()
+    e.record(); torch.cuda.synchronize(); return a.elapsed_time(e) / (3 * reps) * 1e3
 
 LAYERS = [("convc2 3x3 256->192 relu", 256, 0, 192, 3, 3, "relu"), ("conv 3x3 (192+64)->128 relu", 192, 64, 128, 3, 3, "relu"),
           ("gru convz1 1x5 (128+256)->128 sigmoid", 128, 256, 128, 1, 5, "sigmoid"), ("gru convq2 5x1 (128+256)->128 tanh", 128, 256, 128, 5, 1, "tanh"),
