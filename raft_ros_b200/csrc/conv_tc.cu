@@ -33,11 +33,13 @@ constexpr int kConvWarps = 8, kEpiWarps = 4, kProducerWarp = 12, kInputWarp = 13
 constexpr int TMPIX = 128;
 constexpr int kMaxHaloPix = 400;                    // 3 x 130 (3x3), 12 x 16 (5x1 on 8 x 16 tiles), 1 x 132 (1x5)
 constexpr int kHaloBytes = kMaxHaloPix * 128;       // one 64-channel block of the halo tile: 50 KB
-constexpr int kInStages = 4;                        // fp32 input staging: 8 channels of the halo tile per stage, filled by TMA
+constexpr int kInStages = 12;                       // fp32 input staging: 8 channels of the halo tile per stage, filled by TMA (at most; P.in_stages)
 constexpr int kInStageBytes = 8 * kMaxHaloPix * 4;  //   [8 channels][rows][columns rounded up to 4] fp32 = 12.5 KB
-constexpr int kRingBytes = 72 * 1024;               // weight ring: as many blocks of (filters of this CTA) x 64 K as fit, at most 8
-constexpr int kMaxStages = 8;
-constexpr int kSmemBytes = 1024 + 2 * kHaloBytes + kInStages * kInStageBytes + kRingBytes + 1024 /*bias*/ + 512;
+constexpr int kMaxStages = 12;                      // weight ring: as many blocks of (filters of this CTA) x 64 K as the rest holds
+constexpr int kTailBytes = 1024 /*bias*/ + 512 /*barriers*/;
+constexpr int kSmemBytes = 227 * 1024;              // all of it: what the halo and staging buffers of this filter shape leave goes to the ring
+constexpr int kDataBytes = kSmemBytes - 1024 /*alignment slack*/ - kTailBytes;
+static_assert(2 * kHaloBytes + 4 * kInStageBytes + 2 * 32 * 1024 <= kDataBytes, "four input stages and two 32 KB weight stages must always fit");
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 
 struct Params {
@@ -55,14 +57,24 @@ struct Params {
   int box_x0, box_y0;    //   image extent where that is smaller (a box may not exceed the tensor): then it starts at 0 (flags)
   int nparts, Cn;        // a work item = (pixel tile, one of nparts groups of Cn filters): small images still fill the SMs
   int stages, stage_bytes;
+  int in_stages;
+  int halo_bytes, in_stage_bytes, in_off, w_off;  // shared-memory layout of this launch: [2 halo][kInStages staging][ring][bias, barriers]
 };
 
-__device__ __forceinline__ float activate(float v, int act) {
-  switch (act) {
-    case RC_ACT_RELU: return fmaxf(v, 0.0f);
-    case RC_ACT_SIGMOID: return 1.0f / (1.0f + __expf(-v));
-    case RC_ACT_TANH: return tanhf(v);
-    default: return v;
+// The activation of a whole register chunk, branched ONCE per chunk: a per-element switch is if-converted by the compiler
+// into evaluating every activation for every element (exp, reciprocal and tanh for a ReLU layer: measured 4.4 us of a
+// 18 us kernel).  tanh(v) = 1 - 2 / (1 + e^(2v)): absolute error ~1e-7, exact limits at both ends.
+template <int N>
+__device__ __forceinline__ void activate_all(float (&v)[N], int act) {
+  if (act == RC_ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = fmaxf(v[i], 0.0f);
+  } else if (act == RC_ACT_SIGMOID) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = __fdividef(1.0f, 1.0f + __expf(-v[i]));
+  } else if (act == RC_ACT_TANH) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * v[i]));
   }
 }
 
@@ -77,9 +89,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
   const uint32_t raw_u32 = smem_u32(smem_raw);
   const uint32_t base_u32 = (raw_u32 + 1023u) & ~1023u;
   uint8_t *smem = smem_raw + (base_u32 - raw_u32);
-  constexpr int kInOff = 2 * kHaloBytes, kWOff = kInOff + kInStages * kInStageBytes;
+  const int kInOff = P.in_off, kWOff = P.w_off, kHaloB = P.halo_bytes, kInStageB = P.in_stage_bytes;
   const uint32_t halo_u32 = base_u32, w_u32 = base_u32 + kWOff;
-  float *bias_s = reinterpret_cast<float *>(smem + kWOff + kRingBytes);
+  float *bias_s = reinterpret_cast<float *>(smem + kDataBytes);
   uint64_t *bars = reinterpret_cast<uint64_t *>(bias_s + 256);
   uint64_t *h_full = bars, *h_empty = bars + 2, *acc_full = bars + 4, *acc_empty = bars + 6, *w_full = bars + 8,
            *w_empty = bars + 8 + kMaxStages, *s_full = bars + 8 + 2 * kMaxStages, *s_empty = s_full + kInStages;
@@ -133,37 +145,62 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       const int tile = item / P.nparts;
       const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
       const int x0 = txi * TW, y = tyi * TH;
+      // TMA path: this thread's halo pixels tid and tid + 256 (HP <= 400): offset in a staged box (-1: outside the box, i.e.
+      // zero), row offset and swizzle phase in the operand tile
+      const int plane = P.BH * P.BW;
+      int hp_src0 = -1, hp_src1 = -1;
+      uint32_t hp_dst0 = 0, hp_dst1 = 0, hp_sw0 = 0, hp_sw1 = 0;
+      bool hp_ok0 = false, hp_ok1 = false;
+      if constexpr (TMA_IN) {
+        // a box pinned to the image origin (image narrower / lower than the halo tile) is shifted against the tile
+        const int dx = P.box_x0 ? pw - x0 : 0, dy = P.box_y0 ? ph - y : 0;
+        auto place = [&](int hi, int &src_off, uint32_t &dst, uint32_t &sw, bool &ok) {
+          ok = hi < HP;
+          const int r = hi / RW, xx = hi - r * RW;
+          const int br = r - dy, bx = xx - dx;
+          src_off = (ok && (unsigned)br < (unsigned)P.BH && (unsigned)bx < (unsigned)P.BW) ? br * P.BW + bx : -1;
+          dst = (uint32_t)hi * 128u;
+          sw = (uint32_t)(hi & 7);
+        };
+        place(tid, hp_src0, hp_dst0, hp_sw0, hp_ok0);
+        place(tid + kConvWarps * 32, hp_src1, hp_dst1, hp_sw1, hp_ok1);
+      }
       for (int cb = 0; cb < P.ncb; ++cb, ++n) {
         const uint32_t buf = n & 1;
         mbar_wait(&h_empty[buf], ((n >> 1) & 1) ^ 1);  // the MMAs that read this buffer two blocks ago are done
-        const uint32_t hb = halo_u32 + buf * kHaloBytes;
+        const uint32_t hb = halo_u32 + buf * kHaloB;
         if constexpr (TMA_IN) {
           // eight channels at a time arrive as one fp32 box [8][BH][BW]; a thread turns a halo pixel's 8 values into one
-          // 16 B chunk of its operand row (consecutive lanes: consecutive pixels, conflict-free reads)
+          // 16 B chunk of its operand row (consecutive lanes: consecutive pixels, conflict-free reads).  A thread owns
+          // the same (up to two) halo pixels for the whole tile: their offsets are formed once (hp_* below).
           for (int sub = 0; sub < 8; ++sub) {
             const bool live = cb * 64 + sub * 8 < P.Cin;  // channel padding of the last block: zeros, nothing staged
-            const float *src = reinterpret_cast<const float *>(smem + kInOff + ist * kInStageBytes);
+            const float *src = reinterpret_cast<const float *>(smem + kInOff + ist * kInStageB);
             if (live) mbar_wait(&s_full[ist], iphase);
-            // a box pinned to the image origin (image narrower / lower than the halo tile) is shifted against the tile
-            const int dx = P.box_x0 ? pw - x0 : 0, dy = P.box_y0 ? ph - y : 0;
-            for (int hi = tid; hi < HP; hi += kConvWarps * 32) {
-              const int r = hi / RW, xx = hi - r * RW;
-              const int br = r - dy, bx = xx - dx;
-              const bool in = live && (unsigned)br < (unsigned)P.BH && (unsigned)bx < (unsigned)P.BW;
-              float v[8];
+            float v0[8], v1[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = in ? src[(j * P.BH + br) * P.BW + bx] : 0.0f;
-              uint32_t w4[4];
-#pragma unroll
-              for (int j = 0; j < 4; ++j) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w4[j]) : "f"(v[2 * j + 1]), "f"(v[2 * j]));
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + (uint32_t)hi * 128u + (uint32_t)((sub ^ (hi & 7)) << 4)),
-                           "r"(w4[0]), "r"(w4[1]), "r"(w4[2]), "r"(w4[3])
-                           : "memory");
+            for (int j = 0; j < 8; ++j) {
+              v0[j] = (live && hp_src0 >= 0) ? src[hp_src0 + j * plane] : 0.0f;
+              v1[j] = (live && hp_src1 >= 0) ? src[hp_src1 + j * plane] : 0.0f;
             }
+            uint32_t w0[4], w1[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w0[j]) : "f"(v0[2 * j + 1]), "f"(v0[2 * j]));
+              asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w1[j]) : "f"(v1[2 * j + 1]), "f"(v1[2 * j]));
+            }
+            if (hp_ok0)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + hp_dst0 + (uint32_t)((sub ^ hp_sw0) << 4)), "r"(w0[0]),
+                           "r"(w0[1]), "r"(w0[2]), "r"(w0[3])
+                           : "memory");
+            if (hp_ok1)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hb + hp_dst1 + (uint32_t)((sub ^ hp_sw1) << 4)), "r"(w1[0]),
+                           "r"(w1[1]), "r"(w1[2]), "r"(w1[3])
+                           : "memory");
             if (live) {
               __syncwarp();
               if (lane == 0) mbar_arrive(&s_empty[ist]);
-              if (++ist == kInStages) { ist = 0; iphase ^= 1; }
+              if (++ist == P.in_stages) { ist = 0; iphase ^= 1; }
             }
           }
         } else {
@@ -216,48 +253,96 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       const int m = e * 32 + lane;  // output pixel of the tile, row-major
       const int y = tyi * TH + m / TW, x = txi * TW + m % TW;
       const bool pv = x < W && y < H;
-      mbar_wait(&acc_full[acc], phase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + (uint32_t)(acc * 256);
       const size_t pix = (size_t)y * W + x;
       float *o = P.out + (size_t)b * P.out_bs + (size_t)n0 * HW + pix;
-      const float *bs = bias_s + n0;
-      // RC_EPI_MUL_FROM: channels from `split` on are multiplied by aux1[b, c - split] (the GRU's r * h)
-      // RC_EPI_GRU:      out = (1 - z) * h + z * act(.), z = aux1[b, c], h = aux2[b, c]            (core/update.py:46,53)
-      const float *a1 = P.aux1 ? P.aux1 + (size_t)b * P.aux1_bs + pix : nullptr;
-      const float *a2 = P.aux2 ? P.aux2 + (size_t)b * P.aux2_bs + pix : nullptr;
-      auto finish = [&](float v, int c) {  // c: filter index within the layer
-        v = activate(v + bias_s[c], P.act);
-        if constexpr (EPI) {
-          if (P.epi == RC_EPI_MUL_FROM) {
-            if (c >= P.split) v *= __ldg(a1 + (size_t)(c - P.split) * HW);
-          } else if (P.epi == RC_EPI_GRU) {
-            const float z = __ldg(a1 + (size_t)c * HW), h = __ldg(a2 + (size_t)c * HW);
-            v = (1.0f - z) * h + z * v;
+      if constexpr (EPI) {
+        // RC_EPI_MUL_FROM: channels from `split` on are multiplied by aux1[b, c - split] (the GRU's r * h)
+        // RC_EPI_GRU:      out = (1 - z) * h + z * act(.), z = aux1[b, c], h = aux2[b, c]            (core/update.py:46,53)
+        // The operands of 16 filters are fetched one chunk ahead -- the first before the accumulator is even complete --
+        // so that their L2 round trips overlap the MMAs and the previous chunk's stores instead of adding up.
+        const bool gru = P.epi == RC_EPI_GRU;
+        const float *a1 = P.aux1 + (size_t)b * P.aux1_bs + pix;
+        const float *a2 = gru ? P.aux2 + (size_t)b * P.aux2_bs + pix : a1;
+        auto fetch = [&](int c0, float (&u)[16], float (&w)[16]) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int c = n0 + c0 + i;
+            if (gru) {
+              u[i] = __ldg(a1 + (size_t)c * HW);
+              w[i] = __ldg(a2 + (size_t)c * HW);
+            } else {
+              u[i] = c >= P.split ? __ldg(a1 + (size_t)(c - P.split) * HW) : 1.0f;
+              w[i] = 0.0f;
+            }
+          }
+        };
+        float u[16], w[16];
+        if (pv) fetch(0, u, w);
+        mbar_wait(&acc_full[acc], phase);
+        tc_fence_after();
+        for (int c0 = 0; c0 < Cn; c0 += 16) {
+          float v[16], un[16], wn[16];
+          tmem_ld16(taddr + c0, v);
+          if (pv && c0 + 16 < Cn) fetch(c0 + 16, un, wn);
+          tmem_ld_wait();
+          float bv[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) bv[i] = bias_s[n0 + c0 + i];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] += bv[i];
+          activate_all(v, P.act);
+          if (gru) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = (1.0f - u[i]) * w[i] + u[i] * v[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] *= u[i];
+          }
+          if (pv) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            u[i] = un[i];
+            w[i] = wn[i];
           }
         }
-        return v;
-      };
-      (void)bs;
-      (void)a1;
-      (void)a2;
-      int c0 = 0;
-      for (; c0 + 32 <= Cn; c0 += 32) {
-        float v[32];
-        tmem_ld32(taddr + c0, v);
-        tmem_ld_wait();
-        if (pv) {
+      } else {
+        mbar_wait(&acc_full[acc], phase);
+        tc_fence_after();
+        const float *bs = bias_s + n0;
+        int c0 = 0;
+        for (; c0 + 32 <= Cn; c0 += 32) {
+          float v[32];
+          tmem_ld32(taddr + c0, v);
+          float bv[32];  // (before the stores: their "memory" clobber would otherwise pin every bias load to its own store)
 #pragma unroll
-          for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, finish(v[i], n0 + c0 + i));
+          for (int i = 0; i < 32; ++i) bv[i] = bs[c0 + i];
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] += bv[i];
+          activate_all(v, P.act);
+          if (pv) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+          }
         }
-      }
-      if (c0 < Cn) {  // Cn is a multiple of 16
-        float v[16];
-        tmem_ld16(taddr + c0, v);
-        tmem_ld_wait();
-        if (pv) {
+        if (c0 < Cn) {  // Cn is a multiple of 16
+          float v[16];
+          tmem_ld16(taddr + c0, v);
+          float bv[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, finish(v[i], n0 + c0 + i));
+          for (int i = 0; i < 16; ++i) bv[i] = bs[c0 + i];
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] += bv[i];
+          activate_all(v, P.act);
+          if (pv) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+          }
         }
       }
       tc_fence_before();
@@ -295,9 +380,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         for (int c = 0; c < P.Cin; c += 8) {
           mbar_wait(&s_empty[stage], phase ^ 1);
           mbar_expect_tx(&s_full[stage], bytes);
-          if (c < P.C1) tma_load_4d(smem + kInOff + stage * kInStageBytes, &tmX1, &s_full[stage], xs, ys, c, b);
-          else tma_load_4d(smem + kInOff + stage * kInStageBytes, &tmX2, &s_full[stage], xs, ys, c - P.C1, b);
-          if (++stage == kInStages) { stage = 0; phase ^= 1; }
+          if (c < P.C1) tma_load_4d(smem + kInOff + stage * kInStageB, &tmX1, &s_full[stage], xs, ys, c, b);
+          else tma_load_4d(smem + kInOff + stage * kInStageB, &tmX2, &s_full[stage], xs, ys, c - P.C1, b);
+          if (++stage == P.in_stages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -317,7 +402,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
           const uint32_t buf = n & 1;
           mbar_wait(&h_full[buf], (n >> 1) & 1);
           tc_fence_after();
-          const uint32_t hb = halo_u32 + buf * kHaloBytes;
+          const uint32_t hb = halo_u32 + buf * kHaloB;
           for (int t = 0; t < T; ++t) {
             const int ky = t / KW, kx = t - ky * KW;
             mbar_wait(&w_full[ws], wphase);
@@ -404,7 +489,24 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
     if (P.total_tiles * p <= sms && Cout % (16 * p) == 0) P.nparts = p;
   P.Cn = Cout / P.nparts;
   P.stage_bytes = (P.Cn * 128 + 1023) / 1024 * 1024;
-  P.stages = kRingBytes / P.stage_bytes < kMaxStages ? kRingBytes / P.stage_bytes : kMaxStages;
+  P.BH = P.TH + KH - 1;
+  P.BW = (P.TW + KW - 1 + 3) & ~3;
+  if (P.BW > W) { P.BW = W; P.box_x0 = 1; }  // (W % 4 == 0 on the TMA path)
+  if (P.BH > H) { P.BH = H; P.box_y0 = 1; }
+  {
+    const int halo_pix = (P.TH + KH - 1) * (P.TW + KW - 1);
+    P.halo_bytes = (halo_pix * 128 + 1023) / 1024 * 1024;
+    P.in_stage_bytes = (8 * P.BH * P.BW * 4 + 127) / 128 * 128;
+    P.in_off = 2 * P.halo_bytes;
+    // the weights get two stages or 48 KB, the input staging what is left (4 .. kInStages boxes in flight: a frame pair
+    // alone is bound by the latency of these rings), the weights then the remainder
+    const int w_min = 2 * P.stage_bytes > 48 * 1024 ? 2 * P.stage_bytes : 48 * 1024;
+    int ins = (kDataBytes - P.in_off - w_min - 1024) / P.in_stage_bytes;
+    P.in_stages = ins < 4 ? 4 : (ins > kInStages ? kInStages : ins);
+    P.w_off = (P.in_off + P.in_stages * P.in_stage_bytes + 1023) / 1024 * 1024;
+    const int ring = kDataBytes - P.w_off;
+    P.stages = ring / P.stage_bytes < kMaxStages ? ring / P.stage_bytes : kMaxStages;
+  }
   CUtensorMap tm;
   {
     const unsigned long long dims[3] = {64, (unsigned long long)Cout, (unsigned long long)ncb * T};
@@ -412,10 +514,6 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
     const unsigned int box[3] = {64, (unsigned int)P.Cn, 1};
     if (int rc = encode_tmap_sw128(&tm, wp, 3, dims, strides, box, "rc_conv2d_fwd")) return rc;
   }
-  P.BH = P.TH + KH - 1;
-  P.BW = (P.TW + KW - 1 + 3) & ~3;
-  if (P.BW > W) { P.BW = W; P.box_x0 = 1; }  // (W % 4 == 0 on the TMA path)
-  if (P.BH > H) { P.BH = H; P.box_y0 = 1; }
   const int items = P.total_tiles * P.nparts;
   const int grid = items < sms ? items : sms;
   const int C2 = Cin - C1;

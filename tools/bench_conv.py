@@ -39,3 +39,27 @@ for B in (1, 8):
         flops = 2.0 * B * 55 * 128 * Cout * (C1 + C2) * KH * KW
         print(json.dumps({"layer": name, "B": B, "ours_us": round(us_ours, 1), "cudnn_tf32_us": round(us_tf32, 1), "cudnn_fp32_us": round(us_fp32, 1),
                           "ours_tflops": round(flops / us_ours / 1e6, 1)}), flush=True)
+
+# a GRU half (core/update.py:41-46) at 55x128: two conv2d_fused launches against the reference's torch ops
+for B in (1, 8):
+    g = torch.Generator().manual_seed(2)
+    h = torch.tanh(torch.randn(B, 128, 55, 128, generator=g)).cuda()
+    x = torch.randn(B, 256, 55, 128, generator=g).cuda()
+    wz, wr, wq = ((torch.randn(128, 384, 1, 5, generator=g) / 40).cuda() for _ in range(3))
+    bz = br = bq = torch.zeros(128).cuda()
+    wzr, bzr = torch.cat([wz, wr]), torch.cat([bz, br])
+    def ref_half():
+        hx = torch.cat([h, x], dim=1)
+        z = torch.sigmoid(F.conv2d(hx, wz, bz, padding=(0, 2)))
+        r = torch.sigmoid(F.conv2d(hx, wr, br, padding=(0, 2)))
+        q = torch.tanh(F.conv2d(torch.cat([r * h, x], dim=1), wq, bq, padding=(0, 2)))
+        return (1 - z) * h + z * q
+    def our_half():
+        zr = rr.conv2d_fused((h, x), wzr, bzr, "sigmoid", epilogue="mul_from", split=128, aux1=h)
+        return rr.conv2d_fused((zr[:, 128:], x), wq, bq, "tanh", epilogue="gru", aux1=zr[:, :128], aux2=h)
+    torch.backends.cudnn.allow_tf32 = True
+    us_ref = t(ref_half)
+    us_ours = t(our_half)
+    us_zr = t(lambda: rr.conv2d_fused((h, x), wzr, bzr, "sigmoid", epilogue="mul_from", split=128, aux1=h))
+    print(json.dumps({"layer": "GRU half 1x5 (z, r, r*h, q, blend)", "B": B, "ours_us": round(us_ours, 1), "ours_zr_us": round(us_zr, 1),
+                      "torch_cudnn_tf32_us": round(us_ref, 1)}), flush=True)
