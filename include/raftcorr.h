@@ -382,6 +382,8 @@ int rc_alt_corr_bwd_det(const float *fmap1, const float *fmap2, const float *coo
  * element-wise steps in the epilogue (core/update.py:43-46,50-53: z, r, r*h, (1-z)*h + z*q), so that a GRU half is two
  * launches and nothing else:
  *   x1_bs, x2_bs, out_bs, aux1_bs, aux2_bs : floats from one batch item to the next (0 = dense, C * H * W)
+ *   store_channels : only filters [0, store_channels) are written (0 = all): the zero filters that pad a filter count to
+ *                    a multiple of 16 then touch nothing (the motion encoder's 126 filters next to the 2 flow channels)
  *   epilogue = RC_EPI_NONE     : out = act(.)
  *              RC_EPI_MUL_FROM : out[b, o] = act(.) * (o >= split ? aux1[b, o - split] : 1)     z | r*h in one pass
  *              RC_EPI_GRU      : out[b, o] = (1 - aux1[b, o]) * aux2[b, o] + aux1[b, o] * act(.)   aux1 = z, aux2 = h
@@ -399,9 +401,23 @@ int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, c
 #define RC_EPI_MUL_FROM 1
 #define RC_EPI_GRU 2
 int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, long long x2_bs, const void *wprep,
-                     const float *bias, float *out, long long out_bs, int B, int Cin, int Cout, int H, int W, int KH,
-                     int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs, const float *aux2,
-                     long long aux2_bs, void *stream);
+                     const float *bias, float *out, long long out_bs, int store_channels, int B, int Cin, int Cout, int H,
+                     int W, int KH, int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs,
+                     const float *aux2, long long aux2_bs, void *stream);
+
+/*
+ * The two remaining pieces of an iteration (core/update.py:86,92 `flo = F.relu(self.convf1(flow))`; core/raft.py:123,
+ * 131-132 `flow = coords1 - coords0 ... coords1 = coords1 + delta_flow`), one launch each:
+ * rc_small_conv_relu_fwd : K x K "same" convolution (K odd <= 7) of a map with 1..4 channels (the flow field) + bias
+ *                          (+ ReLU if relu != 0) on CUDA cores, fp32: in (B, Cin, H, W), weight (Cout, Cin, K, K),
+ *                          out (B, Cout, H, W)
+ * rc_flow_update         : coords1 (B, 2, H, W, dense) += delta (B, 2, H, W, batch stride delta_bs floats, 0 = dense);
+ *                          flow = coords1 - coords0 is written to flow_out and, if not NULL, flow_out2 (own batch strides)
+ */
+int rc_small_conv_relu_fwd(const float *in, const float *weight, const float *bias, float *out, int B, int Cin, int Cout,
+                           int H, int W, int K, int relu, void *stream);
+int rc_flow_update(float *coords1, const float *delta, long long delta_bs, const float *coords0, float *flow_out,
+                   long long flow_bs, float *flow_out2, long long flow2_bs, int B, int H, int W, void *stream);
 
 /*
  * RAFT.upsample_flow (core/raft.py:72-83): convex 8x upsampling of the flow field, one launch instead of

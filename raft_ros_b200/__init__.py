@@ -12,8 +12,10 @@ and `FusedRAFT` that run a user's reference-built model through all of them; the
 """
 from . import alt_cuda_corr  # noqa: F401
 from .corr import AlternateCorrBlock, CorrBlock, DEFAULT_PRECISION, PreparedFeatures, encoder_head  # noqa: F401
-from .utils import bilinear_sampler, conv2d_act, conv2d_fused, coords_grid, upsample_flow  # noqa: F401
+from .utils import (bilinear_sampler, conv2d_act, conv2d_fused, coords_grid, flow_update, small_conv_relu,  # noqa: F401
+                    upsample_flow)
 from .update import FusedRAFT, UpdateBlock  # noqa: F401
 
 __all__ = ["CorrBlock", "AlternateCorrBlock", "bilinear_sampler", "coords_grid", "alt_cuda_corr", "encoder_head",
-           "PreparedFeatures", "upsample_flow", "conv2d_act", "conv2d_fused", "UpdateBlock", "FusedRAFT"]
+           "PreparedFeatures", "upsample_flow", "conv2d_act", "conv2d_fused", "small_conv_relu", "flow_update", "UpdateBlock",
+           "FusedRAFT"]

@@ -134,7 +134,9 @@ SIGNATURES = {
     "rc_alt_absmax": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "rc_alt_prep_fmap_level_f8": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "rc_alt_corr_pyramid_set_norm": (_i, [_vp, _vp, _vp]),
-    "rc_conv2d_ex_fwd": (_i, [_vp, _i, _ll, _vp, _ll, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
+    "rc_conv2d_ex_fwd": (_i, [_vp, _i, _ll, _vp, _ll, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
+    "rc_small_conv_relu_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "rc_flow_update": (_i, [_vp, _vp, _ll, _vp, _vp, _ll, _vp, _ll, _i, _i, _i, _vp]),
     "rc_convex_upsample_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "rc_alt_corr_bwd_det_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "rc_alt_corr_bwd_det": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),

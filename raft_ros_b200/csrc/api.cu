@@ -555,10 +555,11 @@ int rc_conv2d_fwd(const float *x1, int C1, const float *x2, const void *wprep, c
 }
 
 int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, long long x2_bs, const void *wprep,
-                     const float *bias, float *out, long long out_bs, int B, int Cin, int Cout, int H, int W, int KH,
-                     int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs, const float *aux2,
-                     long long aux2_bs, void *stream) {
+                     const float *bias, float *out, long long out_bs, int store_channels, int B, int Cin, int Cout, int H,
+                     int W, int KH, int KW, int act, int epilogue, int split, const float *aux1, long long aux1_bs,
+                     const float *aux2, long long aux2_bs, void *stream) {
   const char *fn = "rc_conv2d_ex_fwd";
+  RC_CHECK_ARG(store_channels >= 0 && store_channels <= Cout, "%s: store_channels %d outside 0..Cout", fn, store_channels);
   RC_CHECK_ARG(x1 && wprep && out, "%s: null pointer", fn);
   RC_CHECK_ARG(B > 0 && H > 0 && W > 0 && (long long)B * H * ((W + 127) / 128) < 0x7fffffffLL, "%s: bad sizes", fn);
   if (int rc = check_conv(fn, Cout, Cin, KH, KW)) return rc;
@@ -566,11 +567,12 @@ int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, 
   RC_CHECK_ARG(act >= RC_ACT_NONE && act <= RC_ACT_TANH, "%s: unknown activation %d", fn, act);
   RC_CHECK_ARG((reinterpret_cast<uintptr_t>(wprep) & 127) == 0, "%s: wprep must be 128-byte aligned", fn);
   const long long hw = (long long)H * W;
-  RC_CHECK_ARG((x1_bs == 0 || x1_bs >= hw * C1) && (x2_bs == 0 || x2_bs >= hw * (Cin - C1)) && (out_bs == 0 || out_bs >= hw * Cout),
+  RC_CHECK_ARG((x1_bs == 0 || x1_bs >= hw * C1) && (x2_bs == 0 || x2_bs >= hw * (Cin - C1)) && (out_bs == 0 || out_bs >= hw * (store_channels ? store_channels : Cout)),
                "%s: a batch stride is smaller than the tensor it strides", fn);
   RC_CHECK_ARG(epilogue >= RC_EPI_NONE && epilogue <= RC_EPI_GRU, "%s: unknown epilogue %d", fn, epilogue);
   ConvExtra ex{};
   ex.x1_bs = x1_bs; ex.x2_bs = x2_bs; ex.out_bs = out_bs;
+  ex.store_channels = store_channels;
   ex.epi = epilogue;
   if (epilogue == RC_EPI_MUL_FROM) {
     RC_CHECK_ARG(aux1 && split >= 0 && split <= Cout, "%s: RC_EPI_MUL_FROM needs aux1 and 0 <= split <= Cout", fn);
@@ -581,6 +583,23 @@ int rc_conv2d_ex_fwd(const float *x1, int C1, long long x1_bs, const float *x2, 
     ex.aux1_bs = aux1_bs ? aux1_bs : hw * Cout; ex.aux2_bs = aux2_bs ? aux2_bs : hw * Cout;
   }
   return launch_conv_tc(x1, C1, x2, wprep, bias, out, B, Cin, Cout, H, W, KH, KW, act, static_cast<cudaStream_t>(stream), &ex);
+}
+
+int rc_small_conv_relu_fwd(const float *in, const float *weight, const float *bias, float *out, int B, int Cin, int Cout, int H,
+                           int W, int K, int relu, void *stream) {
+  RC_CHECK_ARG(in && weight && out, "rc_small_conv_relu_fwd: null pointer");
+  RC_CHECK_ARG(B > 0 && B <= 65535 && Cout > 0 && H > 0 && W > 0, "rc_small_conv_relu_fwd: bad sizes");
+  RC_CHECK_ARG(Cin >= 1 && Cin <= 4 && K >= 1 && K <= 7 && (K & 1), "rc_small_conv_relu_fwd: Cin 1..4 and K odd, at most 7 (got %d, %d)", Cin, K);
+  return launch_small_conv_relu(in, weight, bias, out, B, Cin, Cout, H, W, K, relu, static_cast<cudaStream_t>(stream));
+}
+
+int rc_flow_update(float *coords1, const float *delta, long long delta_bs, const float *coords0, float *flow_out,
+                   long long flow_bs, float *flow_out2, long long flow2_bs, int B, int H, int W, void *stream) {
+  RC_CHECK_ARG(coords1 && delta && coords0 && flow_out, "rc_flow_update: null pointer");
+  RC_CHECK_ARG(B > 0 && H > 0 && W > 0, "rc_flow_update: bad sizes");
+  const long long hw2 = 2LL * H * W;
+  return launch_flow_update(coords1, delta, delta_bs ? delta_bs : hw2, coords0, flow_out, flow_bs ? flow_bs : hw2, flow_out2,
+                            flow2_bs ? flow2_bs : hw2, B, H, W, static_cast<cudaStream_t>(stream));
 }
 
 int rc_convex_upsample_fwd(const float *flow, const float *mask, float *out, int N, int H, int W, void *stream) {

@@ -144,12 +144,17 @@ int launch_conv_prep_weight(const float *w, void *wp, int Cout, int Cin, int KH,
 // what rc_conv2d_ex_fwd adds to rc_conv2d_fwd: batch strides (channel slices of wider tensors) and the fused GRU epilogues
 struct ConvExtra {
   long long x1_bs, x2_bs, out_bs;  // floats between batch items; 0 = dense
+  int store_channels;              // only the first so many filters are stored (0 = all): zero-padded filters write nothing
   int epi, split;
   const float *aux1, *aux2;
   long long aux1_bs, aux2_bs;
 };
 int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, const float *bias, float *out, int B, int Cin, int Cout,
                    int H, int W, int KH, int KW, int act, cudaStream_t st, const ConvExtra *ex = nullptr);
+int launch_small_conv_relu(const float *in, const float *w, const float *bias, float *out, int B, int Cin, int Cout, int H,
+                           int W, int K, int relu, cudaStream_t st);
+int launch_flow_update(float *coords1, const float *delta, long long delta_bs, const float *coords0, float *flow_out,
+                       long long flow_bs, float *flow_out2, long long flow2_bs, int B, int H, int W, cudaStream_t st);
 int launch_convex_upsample(const float *flow, const float *mask, float *out, int N, int H, int W, cudaStream_t st);
 int launch_bilinear_fwd(const float *img, const float *coords, float *out, float *mask, int M, int C,
                         int H, int W, int Ho, int Wo, cudaStream_t st);

@@ -48,6 +48,7 @@ struct Params {
   float *out;
   long long x1_bs, x2_bs, out_bs;  // floats from one batch item to the next (a channel slice of a wider tensor has more than C*H*W)
   int epi, split;                  // RC_EPI_*: what the epilogue does with act(acc + bias)
+  int cstore;                      // filters [0, cstore) are stored, the rest (zero padding of the filter count) dropped
   const float *aux1, *aux2;
   long long aux1_bs, aux2_bs;
   int B, C1, Cin, Cout, H, W, KH, KW, act;
@@ -301,7 +302,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
           }
           if (pv) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+            for (int i = 0; i < 16; ++i)
+              if (n0 + c0 + i < P.cstore) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
           }
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
@@ -326,7 +328,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
           activate_all(v, P.act);
           if (pv) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+            for (int i = 0; i < 32; ++i)
+              if (n0 + c0 + i < P.cstore) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
           }
         }
         if (c0 < Cn) {  // Cn is a multiple of 16
@@ -341,7 +344,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
           activate_all(v, P.act);
           if (pv) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
+            for (int i = 0; i < 16; ++i)
+              if (n0 + c0 + i < P.cstore) st_stream(o + (size_t)(c0 + i) * HW, v[i]);
           }
         }
       }
@@ -471,6 +475,7 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   P.x1_bs = ex && ex->x1_bs ? ex->x1_bs : hw * C1;
   P.x2_bs = ex && ex->x2_bs ? ex->x2_bs : hw * (Cin - C1);
   P.out_bs = ex && ex->out_bs ? ex->out_bs : hw * Cout;
+  P.cstore = ex && ex->store_channels > 0 ? ex->store_channels : Cout;
   if (ex) {
     P.epi = ex->epi; P.split = ex->split;
     P.aux1 = ex->aux1; P.aux2 = ex->aux2;

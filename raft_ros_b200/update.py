@@ -21,7 +21,7 @@ import torch
 import torch.nn.functional as F
 
 from .corr import AlternateCorrBlock, CorrBlock, encoder_head
-from .utils import conv2d_fused, coords_grid, upsample_flow
+from .utils import conv2d_fused, coords_grid, flow_update, small_conv_relu, upsample_flow
 
 __all__ = ["UpdateBlock", "FusedRAFT"]
 
@@ -53,20 +53,22 @@ class UpdateBlock:
         self.has_mask = hasattr(ub, "mask")
         self.sep = hasattr(ub.gru, "convz1")
 
-    # ---- motion encoder (core/update.py:71-77, 90-97) -> the GRU input x = [inp | out | flow]
+    # ---- motion encoder (core/update.py:71-77, 90-97) -> the GRU input x = [inp | out | flow]; x's flow channels
+    # already hold `flow` (dense copy: the input of convf1)
     def _motion_into_x(self, x, cdim, cor, flow):
         me = self.ub.encoder
         if hasattr(me, "convc2"):
             cor = conv2d_fused(cor, me.convc2.weight, me.convc2.bias, "relu")
-        flo = conv2d_fused(F.relu(me.convf1(flow)), me.convf2.weight, me.convf2.bias, "relu")
+        k = me.convf1.weight.shape[-1]
+        flo = small_conv_relu(flow, me.convf1.weight, me.convf1.bias) if k <= 7 and flow.shape[1] <= 4 else F.relu(me.convf1(flow))
+        flo = conv2d_fused(flo, me.convf2.weight, me.convf2.bias, "relu")
         co = me.conv.weight.shape[0]
-        cop = (co + 15) // 16 * 16  # filters are padded to 16: the padding lands on the two flow channels, rewritten next
-        if cop - co <= 2:
-            conv2d_fused((cor, flo), me.conv.weight, me.conv.bias, "relu", out=x[:, cdim:cdim + cop])
-        else:
-            x[:, cdim:cdim + co] = conv2d_fused((cor, flo), me.conv.weight, me.conv.bias, "relu")
-        x[:, cdim + co:cdim + co + 2] = flow
+        conv2d_fused((cor, flo), me.conv.weight, me.conv.bias, "relu", out=x[:, cdim:cdim + co])  # no torch.cat: written in place
         return x
+
+    def flow_slice(self, x, cdim):
+        co = self.ub.encoder.conv.weight.shape[0]
+        return x[:, cdim + co:cdim + co + 2]
 
     def _gru_half(self, h, x, cz, cr, cq, name):
         hd = h.shape[1]
@@ -107,7 +109,10 @@ class UpdateBlock:
         with torch.no_grad():
             me = self.ub.encoder
             cor = conv2d_fused(corr.float().contiguous(), me.convc1.weight, me.convc1.bias, "relu")
-            x = self._motion_into_x(self._x_buffer(inp.float(), flow), inp.shape[1], cor, flow.float())
+            flow = flow.float().contiguous()
+            x = self._x_buffer(inp.float(), flow)
+            self.flow_slice(x, inp.shape[1]).copy_(flow)
+            x = self._motion_into_x(x, inp.shape[1], cor, flow)
             net = self._gru(net.float().contiguous(), x)
             mask, delta = self.heads(net, upsample)
             return net, mask, delta
@@ -141,6 +146,13 @@ class FusedRAFT:
         self.graph = graph
         self.update = UpdateBlock(model.update_block)
         self._graphs = {}
+        self._side = {}
+
+    def _side_stream(self, device):
+        s = self._side.get(device.index)
+        if s is None:
+            s = self._side[device.index] = torch.cuda.Stream(device)
+        return s
 
     def _forward(self, image1, image2, iters, flow_init):
         m = self.model
@@ -150,17 +162,24 @@ class FusedRAFT:
         hdim, cdim = m.hidden_dim, m.context_dim
         amp = bool(getattr(args, "mixed_precision", False))
         enc = m.fnet
+        # the context encoder does not depend on the feature encoder (core/raft.py:99-114): it runs on a second stream
+        cur = torch.cuda.current_stream(image1.device)
+        side = self._side_stream(image1.device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.autocast("cuda", enabled=amp):
+            cnet = m.cnet(image1)
         with torch.autocast("cuda", enabled=amp):
             y = torch.cat([image1, image2], dim=0)  # core/extractor.py:168-192 (small :239-264) up to conv2's input
             y = enc.layer3(enc.layer2(enc.layer1(enc.relu1(enc.norm1(enc.conv1(y))))))
-            cnet = m.cnet(image1)
         if getattr(args, "alternate_corr", False):
             f = enc.conv2(y.float()).float()
             corr_fn = AlternateCorrBlock(f[:f.shape[0] // 2], f[f.shape[0] // 2:], radius=args.corr_radius, precision=self.precision)
         else:
             prep = encoder_head(y.float(), enc.conv2.weight, enc.conv2.bias)  # conv2 + .float() + the build's layout prepass
             corr_fn = CorrBlock.from_prepared(prep, radius=args.corr_radius, precision=self.precision)
-        net, inp = torch.split(cnet.float(), [hdim, cdim], dim=1)
+        cur.wait_stream(side)
+        cnet.record_stream(cur)
+        net, inp = torch.split(cnet.float().contiguous(), [hdim, cdim], dim=1)
         net, inp = torch.tanh(net).contiguous(), torch.relu(inp)
         N, _, H, W = image1.shape
         coords0 = coords_grid(N, H // 8, W // 8, device=image1.device)
@@ -169,11 +188,11 @@ class FusedRAFT:
             coords1 = coords1 + flow_init
         flow = coords1 - coords0
         x = self.update._x_buffer(inp, flow)
+        xflow = self.update.flow_slice(x, cdim)
+        xflow.copy_(flow)
         for it in range(iters):
-            flow = coords1 - coords0
             net, _, delta = self.update.step(net, x, cdim, corr_fn, coords1, flow)
-            coords1 = coords1 + delta
-        flow = coords1 - coords0
+            flow_update(coords1, delta, coords0, flow, xflow)  # coords1 += delta; flow = coords1 - coords0 (core/raft.py:123,131-132)
         if self.update.has_mask:
             # the mask of the last iteration's hidden state (core/raft.py:128,137)
             flow_up = upsample_flow(flow, self.update.up_mask(net))

@@ -162,10 +162,13 @@ def conv2d_fused(x, weight, bias=None, act=None, out=None, epilogue=None, split=
     with torch.cuda.device(dev):
         st = torch.cuda.current_stream().cuda_stream
         wp, b32, co = _prepared_filters(weight, bias, 0, Cout, dev, st)
+        store = 0
         if out is None:
             out = torch.empty((B, co, H, W), dtype=torch.float32, device=dev)
+        elif out.shape == (B, Cout, H, W):
+            store = Cout  # the zero filters padding Cout to a multiple of 16 are computed but not stored
         elif out.shape != (B, co, H, W):
-            raise RuntimeError(f"conv2d_fused: out must be {(B, co, H, W)} (filters padded to a multiple of 16), got {tuple(out.shape)}")
+            raise RuntimeError(f"conv2d_fused: out must be {(B, Cout, H, W)}, got {tuple(out.shape)}")
         obs = _chw(out, "out")
         a1 = a2 = None
         a1bs = a2bs = 0
@@ -179,10 +182,49 @@ def conv2d_fused(x, weight, bias=None, act=None, out=None, epilogue=None, split=
             a1, a1bs, a2, a2bs = aux1, _chw(aux1, "aux1"), aux2, _chw(aux2, "aux2")
         rc = _lib.lib().rc_conv2d_ex_fwd(xs[0].data_ptr(), C1, bs[0], xs[1].data_ptr() if len(xs) == 2 else None,
                                          bs[1] if len(xs) == 2 else 0, wp.data_ptr(), None if b32 is None else b32.data_ptr(),
-                                         out.data_ptr(), obs, B, Cin, co, H, W, KH, KW, _ACTS[act], _EPIS[epilogue], split,
+                                         out.data_ptr(), obs, store, B, Cin, co, H, W, KH, KW, _ACTS[act], _EPIS[epilogue], split,
                                          None if a1 is None else a1.data_ptr(), a1bs, None if a2 is None else a2.data_ptr(), a2bs, st)
         _lib.check(rc, "rc_conv2d_ex_fwd")
-    return out if co == Cout else out[:, :Cout]
+    return out if out.shape[1] == Cout else out[:, :Cout]
+
+
+def small_conv_relu(x, weight, bias=None, relu=True):
+    """`F.relu(F.conv2d(x, weight, bias, padding=K//2))` for a map with 1..4 channels and K x K filters, K odd <= 7: the
+    motion encoder's convf1 on the flow field (reference core/update.py:86,92; small :67,73) as one fp32 CUDA-core launch
+    (rc_small_conv_relu_fwd) instead of cuDNN's convolution between two layout conversions.  Inference only."""
+    if (not x.is_cuda) or x.dim() != 4 or weight.dim() != 4 or weight.shape[1] != x.shape[1] or weight.shape[2] != weight.shape[3]:
+        raise RuntimeError("small_conv_relu: x (B,Cin,H,W) CUDA, weight (Cout,Cin,K,K)")
+    if torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad):
+        raise RuntimeError("small_conv_relu: inference only (no gradient)")
+    x = x.detach().float().contiguous()
+    w = weight.detach().float().contiguous()
+    b = None if bias is None else bias.detach().float().contiguous()
+    B, Cin, H, W = x.shape
+    Cout, _, K, _ = w.shape
+    with torch.cuda.device(x.device):
+        out = torch.empty((B, Cout, H, W), dtype=torch.float32, device=x.device)
+        rc = _lib.lib().rc_small_conv_relu_fwd(x.data_ptr(), w.data_ptr(), None if b is None else b.data_ptr(), out.data_ptr(), B, Cin,
+                                               Cout, H, W, K, 1 if relu else 0, torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "rc_small_conv_relu_fwd")
+    return out
+
+
+def flow_update(coords1, delta, coords0, flow_out, flow_out2=None):
+    """coords1 += delta; flow_out (and flow_out2) = coords1 - coords0, in place and in one launch (rc_flow_update): reference
+    core/raft.py:123,131-132.  coords1 / coords0 dense (B,2,H,W) fp32; delta and the outputs may be channel slices."""
+    B, _, H, W = coords1.shape
+    if not (coords1.is_contiguous() and coords0.is_contiguous() and coords1.dtype == torch.float32 and coords0.dtype == torch.float32):
+        raise RuntimeError("flow_update: coords1 / coords0 must be dense fp32 (B,2,H,W)")
+    for t, name in ((delta, "delta"), (flow_out, "flow_out")) + (((flow_out2, "flow_out2"),) if flow_out2 is not None else ()):
+        if tuple(t.shape) != (B, 2, H, W):
+            raise RuntimeError(f"flow_update: {name} must be {(B, 2, H, W)}")
+    with torch.cuda.device(coords1.device):
+        rc = _lib.lib().rc_flow_update(coords1.data_ptr(), delta.data_ptr(), _chw(delta, "delta"), coords0.data_ptr(), flow_out.data_ptr(),
+                                       _chw(flow_out, "flow_out"), None if flow_out2 is None else flow_out2.data_ptr(),
+                                       0 if flow_out2 is None else _chw(flow_out2, "flow_out2"), B, H, W,
+                                       torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "rc_flow_update")
+    return coords1
 
 
 def conv2d_act(x, weight, bias=None, act=None):

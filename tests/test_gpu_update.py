@@ -66,14 +66,35 @@ def test_conv_writes_into_a_channel_slice(rr):
     wgt, bias = 0.05 * _rand(g, 126, 96, 3, 3), 0.1 * _rand(g, 126)
     x = torch.full((B, 256, H, W), float("nan"), device=DEV)
     x[:, :128] = 7.0
-    rr.conv2d_fused((a, b), wgt, bias, "relu", out=x[:, 128:256])
+    rr.conv2d_fused((a, b), wgt, bias, "relu", out=x[:, 128:254])  # 126 filters: the two that pad them to 128 store nothing
     want = F.relu(F.conv2d(torch.cat([a, b], 1).double(), wgt.double(), bias.double(), padding=1)).float()
     assert float((x[:, 128:254] - want).abs().max()) <= 3e-3 * float(want.abs().max())
-    assert bool((x[:, 254:] == 0).all()) and bool((x[:, :128] == 7.0).all())  # zero filters pad 126 to 128; nothing else touched
+    assert bool(torch.isnan(x[:, 254:]).all()) and bool((x[:, :128] == 7.0).all())  # nothing else touched
+    rr.conv2d_fused((a, b), wgt, bias, "relu", out=x[:, 128:256])  # a slice of the padded count takes the zero filters' zeros
+    assert bool((x[:, 254:] == 0).all())
     with pytest.raises(RuntimeError, match="out must be"):
-        rr.conv2d_fused((a, b), wgt, bias, "relu", out=x[:, 128:254])
+        rr.conv2d_fused((a, b), wgt, bias, "relu", out=x[:, 128:250])
     with pytest.raises(RuntimeError, match="dense"):
         rr.conv2d_fused(a[:, :, :, ::2], wgt[:, :64], bias)
+
+
+def test_small_conv_relu_and_flow_update(rr):
+    g = torch.Generator().manual_seed(9)
+    for (B, Cin, Cout, H, W, K) in [(2, 2, 128, 21, 37, 7), (1, 2, 64, 55, 128, 7), (1, 3, 20, 9, 11, 3)]:
+        x, w, b = _rand(g, B, Cin, H, W), 0.1 * _rand(g, Cout, Cin, K, K), 0.1 * _rand(g, Cout)
+        want = F.relu(F.conv2d(x.double(), w.double(), b.double(), padding=K // 2)).float()
+        got = rr.small_conv_relu(x, w, b)
+        assert got.shape == want.shape and float((got - want).abs().max()) <= 2e-5 * max(1.0, float(want.abs().max()))
+    B, H, W = 2, 13, 22
+    c0 = rr.coords_grid(B, H, W, DEV)
+    c1 = c0 + _rand(g, B, 2, H, W)
+    wide = _rand(g, B, 16, H, W)
+    xbuf = torch.zeros(B, 40, H, W, device=DEV)
+    flow = torch.empty(B, 2, H, W, device=DEV)
+    want_c1 = c1 + wide[:, :2]
+    rr.flow_update(c1, wide[:, :2], c0, flow, xbuf[:, 30:32])
+    assert torch.equal(c1, want_c1) and torch.equal(flow, want_c1 - c0) and torch.equal(xbuf[:, 30:32], flow)
+    assert bool((xbuf[:, :30] == 0).all()) and bool((xbuf[:, 32:] == 0).all())
 
 
 def _update_inputs(core, small, B, H, W, g):
