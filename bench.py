@@ -226,6 +226,58 @@ def cpu_reference_run(args, steps, warmup, budget_s):
                       f"{len(times)} timed steps, mean"}
 
 
+def raft_forward_run(args):
+    """Its own key, never the headline: the reference's whole test-mode RAFT.forward (core/raft.py:86-144; its own files
+    from oracle/_ref/core, random-init raft-things weights, one 440x1024 pair, args.iters iterations, TF32 as torch
+    defaults it) next to raft_ros_b200.FusedRAFT on the same model -- the call the ROS node makes per image pair
+    (ros/scripts/main.py:117-149).  None when the reference's files are not on the box."""
+    import argparse as ap
+    import warnings
+
+    import torch
+    import torch.nn.functional as F
+
+    import raft_ros_b200 as rr
+    from oracle import build_ref_core
+
+    core = build_ref_core.load()
+    if core is None:
+        return None
+    import core.raft  # noqa: F401
+    warnings.filterwarnings("ignore")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(1234)
+    model = core.raft.RAFT(ap.Namespace(small=False, mixed_precision=False, alternate_corr=False)).to(dev).eval()
+    H, W = args.height, args.width
+    g = torch.Generator().manual_seed(77)
+    low = torch.rand(1, 3, H // 8 + 2, W // 8 + 2, generator=g)
+    big = F.interpolate(low, size=(H + 16, W + 16), mode="bicubic", align_corners=False).clamp(0, 1)
+    tex = (big + 0.15 * torch.rand(1, 3, H + 16, W + 16, generator=g)).clamp(0, 1) * 255.0
+    im1, im2 = tex[:, :, 8:8 + H, 8:8 + W].contiguous().to(dev), tex[:, :, 5:5 + H, 11:11 + W].contiguous().to(dev)
+
+    def timeit(fn, warm=3, reps=10):
+        for _ in range(warm):
+            out = fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps, out
+
+    K = args.iters
+    with torch.no_grad():
+        ms_ref, (flow_ref, _) = timeit(lambda: model(im1, im2, iters=K, test_mode=True))
+        ms_eager, _ = timeit(lambda fr=rr.FusedRAFT(model): fr(im1, im2, iters=K))
+        ms_graph, (flow_g, _) = timeit(lambda fr=rr.FusedRAFT(model, graph=True): fr(im1, im2, iters=K))
+    return {"what": f"RAFT.forward, raft-things architecture, random init, one {H}x{W} pair, {K} iterations, test_mode",
+            "reference_ms": ms_ref, "reference": "the reference's own files on the same GPU, TF32 as torch defaults it",
+            "fused_raft_ms": ms_eager, "fused_raft_graph_ms": ms_graph, "speedup_graph": ms_ref / ms_graph,
+            "epe_px_vs_reference": float((flow_g - flow_ref).norm(dim=1).mean()), "mean_flow_px": float(flow_ref.norm(dim=1).mean())}
+
+
 def fused_convc1_run(args, f1, f2, coords):
     """Its own key, never the headline: the step with every lookup fused into the motion encoder's convc1 + ReLU
     (CorrBlock.lookup_convc1 = rc_corr_lookup_convc1_fwd, fp16 operands) against the unfused pair it replaces on
@@ -641,6 +693,13 @@ def run_ours(args):
             line["fused"] = fused_convc1_run(args, f1, f2, coords)
         except Exception as e:
             log(f"[bench] fused lookup+convc1 leg failed: {type(e).__name__}: {e}")
+    if world == 1 and tiled and not args.no_fast_paths and args.radius == 4 and args.levels == 4:
+        try:
+            rf = raft_forward_run(args)
+            if rf is not None:
+                line["raft_forward"] = rf
+        except Exception as e:
+            log(f"[bench] RAFT.forward leg failed: {type(e).__name__}: {e}")
     if world == 1 and not args.no_gpu_reference:
         try:
             line["gpu_reference"] = gpu_reference_run(args, f1, f2, coords, value)

@@ -13,49 +13,53 @@ constexpr int kMaxTaps = 4 * 7 * 7;  // Cin <= 4, K <= 7
 constexpr int OG = 16;               // output channels per thread
 
 // out[b, o, y, x] = relu(bias[o] + sum_{c, ky, kx} w[o, c, ky, kx] * in[b, c, y + ky - K/2, x + kx - K/2])
-// A thread owns one pixel and OG filters; the filters of the block's group sit in shared memory as [tap][OG] and are
-// read as broadcast float4; the input taps come straight from global memory (coalesced along x, L1-resident halo).
-__global__ void __launch_bounds__(128)
+// A block owns 128 pixels of one row and OG filters: the input rows with their halo (zero outside the image) and the
+// filters ([tap][OG], read as broadcast float4) sit in shared memory; a thread owns one pixel.
+constexpr int TWS = 128;
+__global__ void __launch_bounds__(TWS)
 small_conv_relu_kernel(const float *__restrict__ in, const float *__restrict__ w, const float *__restrict__ bias,
-                       float *__restrict__ out, int Cin, int Cout, int H, int W, int K, int relu) {
+                       float *__restrict__ out, int Cin, int Cout, int H, int W, int K, int relu, int tiles_x) {
   __shared__ __align__(16) float ws[kMaxTaps * OG];
   __shared__ float bs[OG];
-  const int taps = Cin * K * K, og = blockIdx.y, b = blockIdx.z;
+  __shared__ float tile[4 * 7 * (TWS + 6)];
+  const int taps = Cin * K * K, og = blockIdx.y, b = blockIdx.z, r = K >> 1, RWS = TWS + K - 1;
+  const int y = blockIdx.x / tiles_x, x0 = (blockIdx.x - y * tiles_x) * TWS;
   pdl_launch_dependents();
-  for (int i = threadIdx.x; i < taps * OG; i += blockDim.x) {
-    const int t = i / OG, o = og * OG + (i - t * OG);
-    ws[i] = o < Cout ? __ldg(w + (size_t)o * taps + t) : 0.0f;
+  for (int i = threadIdx.x; i < taps * OG; i += TWS) {  // coalesced read of OG filters, transposed into [tap][OG]
+    const int o = i / taps, t = i - o * taps;
+    ws[t * OG + o] = og * OG + o < Cout ? __ldg(w + (size_t)(og * OG + o) * taps + t) : 0.0f;
   }
   if (threadIdx.x < OG) bs[threadIdx.x] = (bias && og * OG + threadIdx.x < Cout) ? __ldg(bias + og * OG + threadIdx.x) : 0.0f;
   pdl_wait();
+  const float *src = in + (size_t)b * Cin * H * W;
+  for (int i = threadIdx.x; i < Cin * K * RWS; i += TWS) {
+    const int row = i / RWS, col = i - row * RWS, c = row / K, ky = row - c * K;
+    const int iy = y + ky - r, ix = x0 + col - r;
+    tile[i] = ((unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W) ? __ldg(src + ((size_t)c * H + iy) * W + ix) : 0.0f;
+  }
   __syncthreads();
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= H * W) return;
-  const int y = p / W, x = p - y * W, r = K >> 1;
+  const int x = x0 + threadIdx.x;
   float acc[OG];
 #pragma unroll
   for (int i = 0; i < OG; ++i) acc[i] = bs[i];
-  const float *src = in + (size_t)b * Cin * H * W;
   int t = 0;
-  for (int c = 0; c < Cin; ++c)
-    for (int ky = 0; ky < K; ++ky) {
-      const int iy = y + ky - r;
-      const bool rowok = (unsigned)iy < (unsigned)H;
-      for (int kx = 0; kx < K; ++kx, ++t) {
-        const int ix = x + kx - r;
-        const float v = (rowok && (unsigned)ix < (unsigned)W) ? __ldg(src + ((size_t)c * H + iy) * W + ix) : 0.0f;
-        const float4 *w4 = reinterpret_cast<const float4 *>(ws + t * OG);
+  for (int row = 0; row < Cin * K; ++row) {
+    const float *trow = tile + row * RWS + threadIdx.x;
+    for (int kx = 0; kx < K; ++kx, ++t) {
+      const float v = trow[kx];
+      const float4 *w4 = reinterpret_cast<const float4 *>(ws + t * OG);
 #pragma unroll
-        for (int q = 0; q < OG / 4; ++q) {
-          const float4 f = w4[q];
-          acc[4 * q + 0] = fmaf(f.x, v, acc[4 * q + 0]);
-          acc[4 * q + 1] = fmaf(f.y, v, acc[4 * q + 1]);
-          acc[4 * q + 2] = fmaf(f.z, v, acc[4 * q + 2]);
-          acc[4 * q + 3] = fmaf(f.w, v, acc[4 * q + 3]);
-        }
+      for (int q = 0; q < OG / 4; ++q) {
+        const float4 f = w4[q];
+        acc[4 * q + 0] = fmaf(f.x, v, acc[4 * q + 0]);
+        acc[4 * q + 1] = fmaf(f.y, v, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(f.z, v, acc[4 * q + 2]);
+        acc[4 * q + 3] = fmaf(f.w, v, acc[4 * q + 3]);
       }
     }
-  float *o = out + ((size_t)b * Cout + og * OG) * H * W + p;
+  }
+  if (x >= W) return;
+  float *o = out + ((size_t)b * Cout + og * OG) * H * W + (size_t)y * W + x;
 #pragma unroll
   for (int i = 0; i < OG; ++i)
     if (og * OG + i < Cout) o[(size_t)i * H * W] = relu ? fmaxf(acc[i], 0.0f) : acc[i];
@@ -84,8 +88,9 @@ flow_update_kernel(float *__restrict__ coords1, const float *__restrict__ delta,
 int launch_small_conv_relu(const float *in, const float *w, const float *bias, float *out, int B, int Cin, int Cout, int H,
                            int W, int K, int relu, cudaStream_t st) {
   using namespace glue;
-  const dim3 grid((unsigned)((H * W + 127) / 128), (unsigned)((Cout + OG - 1) / OG), (unsigned)B);
-  RC_CUDA(launch_pdl(small_conv_relu_kernel, grid, dim3(128), 0, st, in, w, bias, out, Cin, Cout, H, W, K, relu));
+  const int tiles_x = (W + TWS - 1) / TWS;
+  const dim3 grid((unsigned)(H * tiles_x), (unsigned)((Cout + OG - 1) / OG), (unsigned)B);
+  RC_CUDA(launch_pdl(small_conv_relu_kernel, grid, dim3(TWS), 0, st, in, w, bias, out, Cin, Cout, H, W, K, relu, tiles_x));
   return RC_OK;
 }
 
