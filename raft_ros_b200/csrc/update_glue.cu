@@ -10,59 +10,95 @@ namespace rc {
 namespace glue {
 
 constexpr int kMaxTaps = 4 * 7 * 7;  // Cin <= 4, K <= 7
-constexpr int OG = 16;               // output channels per thread
+constexpr int OG = 8;                // filters per thread
+constexpr int FG = 32;               // filters per block: one warp per OG of them
+constexpr int PX = 4;                // consecutive pixels per thread
+constexpr int TWS = 32 * PX;         // pixels of a row per block
+constexpr int RWP = TWS + 8;         // pitch of a staged input row (halo of up to 3 + 3, rounded to a float4)
 
 // out[b, o, y, x] = relu(bias[o] + sum_{c, ky, kx} w[o, c, ky, kx] * in[b, c, y + ky - K/2, x + kx - K/2])
-// A block owns 128 pixels of one row and OG filters: the input rows with their halo (zero outside the image) and the
-// filters ([tap][OG], read as broadcast float4) sit in shared memory; a thread owns one pixel.
-constexpr int TWS = 128;
-__global__ void __launch_bounds__(TWS)
+// A block owns 128 pixels of one row and FG filters: the input rows with their halo (zero outside the image) and the
+// filters ([tap][FG]) sit in shared memory.  A thread owns PX consecutive pixels x OG filters (32 accumulators): per
+// input row it reads 12 inputs (three conflict-free float4) and, per tap, its 8 filters as two broadcast float4 --
+// 32 FMAs per 2 shared-memory loads.
+__global__ void __launch_bounds__(FG / OG * 32)
 small_conv_relu_kernel(const float *__restrict__ in, const float *__restrict__ w, const float *__restrict__ bias,
                        float *__restrict__ out, int Cin, int Cout, int H, int W, int K, int relu, int tiles_x) {
-  __shared__ __align__(16) float ws[kMaxTaps * OG];
-  __shared__ float bs[OG];
-  __shared__ float tile[4 * 7 * (TWS + 6)];
-  const int taps = Cin * K * K, og = blockIdx.y, b = blockIdx.z, r = K >> 1, RWS = TWS + K - 1;
+  __shared__ __align__(16) float ws[kMaxTaps * FG];
+  __shared__ float bs[FG];
+  __shared__ __align__(16) float tile[4 * 7 * RWP];
+  const int taps = Cin * K * K, fg = blockIdx.y, b = blockIdx.z, r = K >> 1;
   const int y = blockIdx.x / tiles_x, x0 = (blockIdx.x - y * tiles_x) * TWS;
+  const int lane = threadIdx.x & 31, og = threadIdx.x >> 5;
   pdl_launch_dependents();
-  for (int i = threadIdx.x; i < taps * OG; i += TWS) {  // coalesced read of OG filters, transposed into [tap][OG]
+  // (both staging loops are unrolled so that eight loads are in flight per thread: with one at a time their latency,
+  // ~50 round trips per block, was the whole kernel: 20 us for 88 MFLOP)
+#pragma unroll 8
+  for (int i = threadIdx.x; i < taps * FG; i += FG / OG * 32) {  // coalesced read of FG filters, transposed into [tap][FG]
     const int o = i / taps, t = i - o * taps;
-    ws[t * OG + o] = og * OG + o < Cout ? __ldg(w + (size_t)(og * OG + o) * taps + t) : 0.0f;
+    ws[t * FG + o] = fg * FG + o < Cout ? __ldg(w + (size_t)(fg * FG + o) * taps + t) : 0.0f;
   }
-  if (threadIdx.x < OG) bs[threadIdx.x] = (bias && og * OG + threadIdx.x < Cout) ? __ldg(bias + og * OG + threadIdx.x) : 0.0f;
+  if (threadIdx.x < FG) bs[threadIdx.x] = (bias && fg * FG + threadIdx.x < Cout) ? __ldg(bias + fg * FG + threadIdx.x) : 0.0f;
   pdl_wait();
   const float *src = in + (size_t)b * Cin * H * W;
-  for (int i = threadIdx.x; i < Cin * K * RWS; i += TWS) {
-    const int row = i / RWS, col = i - row * RWS, c = row / K, ky = row - c * K;
+#pragma unroll 8
+  for (int i = threadIdx.x; i < Cin * K * RWP; i += FG / OG * 32) {  // staged column j <-> image column x0 + j - r
+    const int row = i / RWP, col = i - row * RWP, c = row / K, ky = row - c * K;
     const int iy = y + ky - r, ix = x0 + col - r;
     tile[i] = ((unsigned)iy < (unsigned)H && (unsigned)ix < (unsigned)W) ? __ldg(src + ((size_t)c * H + iy) * W + ix) : 0.0f;
   }
   __syncthreads();
-  const int x = x0 + threadIdx.x;
-  float acc[OG];
+  float acc[PX][OG];
 #pragma unroll
-  for (int i = 0; i < OG; ++i) acc[i] = bs[i];
-  int t = 0;
+  for (int p = 0; p < PX; ++p)
+#pragma unroll
+    for (int i = 0; i < OG; ++i) acc[p][i] = bs[og * OG + i];
   for (int row = 0; row < Cin * K; ++row) {
-    const float *trow = tile + row * RWS + threadIdx.x;
-    for (int kx = 0; kx < K; ++kx, ++t) {
-      const float v = trow[kx];
-      const float4 *w4 = reinterpret_cast<const float4 *>(ws + t * OG);
+    float v[12];
+    const float4 *t4 = reinterpret_cast<const float4 *>(tile + row * RWP + PX * lane);
 #pragma unroll
-      for (int q = 0; q < OG / 4; ++q) {
-        const float4 f = w4[q];
-        acc[4 * q + 0] = fmaf(f.x, v, acc[4 * q + 0]);
-        acc[4 * q + 1] = fmaf(f.y, v, acc[4 * q + 1]);
-        acc[4 * q + 2] = fmaf(f.z, v, acc[4 * q + 2]);
-        acc[4 * q + 3] = fmaf(f.w, v, acc[4 * q + 3]);
+    for (int q = 0; q < 3; ++q) {
+      const float4 f = t4[q];
+      v[4 * q] = f.x; v[4 * q + 1] = f.y; v[4 * q + 2] = f.z; v[4 * q + 3] = f.w;
+    }
+    const float *wrow = ws + (size_t)row * K * FG + og * OG;
+#pragma unroll
+    for (int kx = 0; kx < 7; ++kx) {
+      if (kx < K) {
+        const float4 *w4 = reinterpret_cast<const float4 *>(wrow + kx * FG);
+#pragma unroll
+        for (int q = 0; q < OG / 4; ++q) {
+          const float4 f = w4[q];
+#pragma unroll
+          for (int p = 0; p < PX; ++p) {
+            acc[p][4 * q + 0] = fmaf(f.x, v[p + kx], acc[p][4 * q + 0]);
+            acc[p][4 * q + 1] = fmaf(f.y, v[p + kx], acc[p][4 * q + 1]);
+            acc[p][4 * q + 2] = fmaf(f.z, v[p + kx], acc[p][4 * q + 2]);
+            acc[p][4 * q + 3] = fmaf(f.w, v[p + kx], acc[p][4 * q + 3]);
+          }
+        }
       }
     }
   }
+  const int x = x0 + PX * lane;
   if (x >= W) return;
-  float *o = out + ((size_t)b * Cout + og * OG) * H * W + (size_t)y * W + x;
+  float *o = out + ((size_t)b * Cout + fg * FG + og * OG) * H * W + (size_t)y * W + x;
+  const bool vec = x + PX <= W && (reinterpret_cast<uintptr_t>(o) & 15) == 0 && (((size_t)H * W) & 3) == 0;
 #pragma unroll
-  for (int i = 0; i < OG; ++i)
-    if (og * OG + i < Cout) o[(size_t)i * H * W] = relu ? fmaxf(acc[i], 0.0f) : acc[i];
+  for (int i = 0; i < OG; ++i) {
+    if (fg * FG + og * OG + i >= Cout) break;
+    float q[PX];
+#pragma unroll
+    for (int p = 0; p < PX; ++p) q[p] = relu ? fmaxf(acc[p][i], 0.0f) : acc[p][i];
+    float *oc = o + (size_t)i * H * W;
+    if (vec) {
+      *reinterpret_cast<float4 *>(oc) = make_float4(q[0], q[1], q[2], q[3]);
+    } else {
+#pragma unroll
+      for (int p = 0; p < PX; ++p)
+        if (x + p < W) oc[p] = q[p];
+    }
+  }
 }
 
 // coords1 (B, 2, H, W) += delta (B, 2, H, W with its own batch stride); flow = coords1 - coords0 -> flow_out and, if
@@ -89,8 +125,8 @@ int launch_small_conv_relu(const float *in, const float *w, const float *bias, f
                            int W, int K, int relu, cudaStream_t st) {
   using namespace glue;
   const int tiles_x = (W + TWS - 1) / TWS;
-  const dim3 grid((unsigned)(H * tiles_x), (unsigned)((Cout + OG - 1) / OG), (unsigned)B);
-  RC_CUDA(launch_pdl(small_conv_relu_kernel, grid, dim3(TWS), 0, st, in, w, bias, out, Cin, Cout, H, W, K, relu, tiles_x));
+  const dim3 grid((unsigned)(H * tiles_x), (unsigned)((Cout + FG - 1) / FG), (unsigned)B);
+  RC_CUDA(launch_pdl(small_conv_relu_kernel, grid, dim3(FG / OG * 32), 0, st, in, w, bias, out, Cin, Cout, H, W, K, relu, tiles_x));
   return RC_OK;
 }
 

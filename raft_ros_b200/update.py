@@ -11,7 +11,10 @@ classes -- its weights, its encoders -- with the hot layers on this library's ke
   encoder output layer              encoder_head                       (rc_fnet_conv1x1_prep)
   convex upsampling                 upsample_flow                      (rc_convex_upsample_fwd)
 
-What stays torch / cuDNN: the encoders' residual stages, convf1 (7x7 on two channels), the mask head's 576-wide 1x1.
+  convf1 (7x7 on the flow) + ReLU    small_conv_relu                    (rc_small_conv_relu_fwd)
+  coords1 += delta; flow = ...       flow_update                        (rc_flow_update)
+
+What stays torch / cuDNN: the encoders' residual stages and the mask head's 576-wide 1x1.
 In test mode only the last iteration's upsampled flow is returned (core/raft.py:141-142), so the mask head and the
 upsampling run once, after the loop.  Nothing here imports the reference: it duck-types the modules it is given.
 """

@@ -25,6 +25,11 @@ CASES = [
     (1, 24, 40, 32, 2, 12, 5, 1, "relu"),         # the same for the column filter's 8 x 16 tiles, two inputs
     (1, 4, 0, 16, 8, 8, 3, 3, None),              # fewer channels than a staged box holds: direct-load path
     (1, 128, 256, 256, 55, 128, 1, 5, "sigmoid"), # z and r gates as one 256-filter convolution at the real size
+    (8, 256, 0, 192, 55, 128, 3, 3, "relu"),      # batch 8: 440 tiles, three per CTA (the persistent loop and its ring phases)
+    (3, 64, 64, 64, 55, 128, 1, 5, "tanh"),       # 165 tiles: some CTAs do two, some one
+    (8, 128, 256, 128, 21, 64, 5, 1, "sigmoid"),  # many 8 x 16 tiles of the column filters
+    (5, 48, 0, 126, 31, 40, 3, 3, None),          # several tiles per CTA with a padded filter count
+    (5, 48, 0, 32, 31, 39, 3, 3, None),           # the same on the direct-load path (odd width)
 ]
 
 

@@ -35,7 +35,8 @@ def _rand(g, *shape):
     return torch.randn(*shape, generator=g).to(DEV)
 
 
-@pytest.mark.parametrize("geom", [(2, 128, 256, 24, 40, 1, 5), (1, 96, 146, 13, 22, 3, 3), (2, 128, 256, 17, 16, 5, 1)])
+@pytest.mark.parametrize("geom", [(2, 128, 256, 24, 40, 1, 5), (1, 96, 146, 13, 22, 3, 3), (2, 128, 256, 17, 16, 5, 1),
+                                  (7, 128, 256, 24, 40, 1, 5)])  # the last one: 168 tiles, more than one per CTA, with the GRU epilogues
 def test_gru_half_in_two_launches(rr, geom):
     """z | r*h from one convolution (epilogue mul_from), then (1-z)h + z tanh(conv([r*h, x])) (epilogue gru), with the
     operands of the second launch being channel slices of the first one's output (core/update.py:16-31, 33-60)."""

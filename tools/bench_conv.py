@@ -63,3 +63,13 @@ for B in (1, 8):
     us_zr = t(lambda: rr.conv2d_fused((h, x), wzr, bzr, "sigmoid", epilogue="mul_from", split=128, aux1=h))
     print(json.dumps({"layer": "GRU half 1x5 (z, r, r*h, q, blend)", "B": B, "ours_us": round(us_ours, 1), "ours_zr_us": round(us_zr, 1),
                       "torch_cudnn_tf32_us": round(us_ref, 1)}), flush=True)
+
+# convf1: the 7x7 convolution of the flow field + ReLU (core/update.py:86,92)
+for B in (1, 8):
+    g = torch.Generator().manual_seed(4)
+    fl = torch.randn(B, 2, 55, 128, generator=g).cuda()
+    w7 = (torch.randn(128, 2, 7, 7, generator=g) / 10).cuda(); b7 = torch.zeros(128).cuda()
+    torch.backends.cudnn.allow_tf32 = True
+    us_ref = t(lambda: F.relu(F.conv2d(fl, w7, b7, padding=3)))
+    us_ours = t(lambda: rr.small_conv_relu(fl, w7, b7))
+    print(json.dumps({"layer": "convf1 7x7 2->128 + ReLU (CUDA cores, fp32)", "B": B, "ours_us": round(us_ours, 1), "cudnn_tf32_us": round(us_ref, 1)}), flush=True)

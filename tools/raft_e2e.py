@@ -91,6 +91,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--height", type=int, default=440)
     ap.add_argument("--width", type=int, default=1024)
+    ap.add_argument("--batch", type=int, default=1, help="frame pairs per forward (the pair is repeated with small noise)")
     a = ap.parse_args()
     core = build_ref_core.load()
     if core is None:
@@ -101,7 +102,11 @@ def main():
     torch.manual_seed(1234)
     model = core.raft.RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False)).to(DEV).eval()
     im1, im2 = images(a.height, a.width)
-    res = {"case": f"RAFT.forward raft-things {a.height}x{a.width}, batch 1, iters {a.iters}, test_mode", "tf32": "torch defaults"}
+    if a.batch > 1:
+        g = torch.Generator(device=DEV).manual_seed(3)
+        im1 = (im1.repeat(a.batch, 1, 1, 1) + 2.0 * torch.rand(a.batch, *im1.shape[1:], device=DEV, generator=g)).clamp(0, 255)
+        im2 = (im2.repeat(a.batch, 1, 1, 1) + 2.0 * torch.rand(a.batch, *im2.shape[1:], device=DEV, generator=g)).clamp(0, 255)
+    res = {"case": f"RAFT.forward raft-things {a.height}x{a.width}, batch {a.batch}, iters {a.iters}, test_mode", "tf32": "torch defaults"}
     with torch.no_grad():
         ms_ref, (flow_ref, up_ref) = timed(lambda: model(im1, im2, iters=a.iters, test_mode=True))
         res["reference_ms"] = ms_ref
