@@ -34,7 +34,8 @@ constexpr int TMPIX = 128;
 constexpr int kMaxHaloPix = 400;                    // 3 x 130 (3x3), 12 x 16 (5x1 on 8 x 16 tiles), 1 x 132 (1x5)
 constexpr int kHaloBytes = kMaxHaloPix * 128;       // one 64-channel block of the halo tile: 50 KB
 constexpr int kInStages = 12;                       // fp32 input staging: 8 channels of the halo tile per stage, filled by TMA (at most; P.in_stages)
-constexpr int kInStageBytes = 8 * kMaxHaloPix * 4;  //   [8 channels][rows][columns rounded up to 4] fp32 = 12.5 KB
+constexpr int kMaxBoxPix = 448;                     // staged box: rows rounded up to 8 columns (3 x 136)
+constexpr int kInStageBytes = 8 * kMaxBoxPix * 4;  //   [8 channels][rows][columns rounded up to 4] fp32 = 12.5 KB
 constexpr int kMaxStages = 12;                      // weight ring: as many blocks of (filters of this CTA) x 64 K as the rest holds
 constexpr int kTailBytes = 1024 /*bias*/ + 512 /*barriers*/;
 constexpr int kSmemBytes = 227 * 1024;              // all of it: what the halo and staging buffers of this filter shape leave goes to the ring
@@ -56,6 +57,7 @@ struct Params {
   int ncb, tiles_x, tiles_y, total_tiles;
   int BH, BW;            // staged box of the input: TH + KH - 1 rows of (TW + KW - 1 rounded up to 4) columns -- or the whole
   int box_x0, box_y0;    //   image extent where that is smaller (a box may not exceed the tensor): then it starts at 0 (flags)
+  int box_shift;         // columns between the box's 16 B-aligned start and the halo tile's first column
   int nparts, Cn;        // a work item = (pixel tile, one of nparts groups of Cn filters): small images still fill the SMs
   int stages, stage_bytes;
   int in_stages;
@@ -80,7 +82,8 @@ __device__ __forceinline__ void activate_all(float (&v)[N], int act) {
 }
 
 // TMA_IN: the input reaches the converters through a ring of TMA boxes (rows of 16 B multiples, i.e. W % 4 == 0, and a
-// first tensor whose channel count is a multiple of 8); the box's zero fill outside the image IS the padding.  Otherwise
+// first tensor whose channel count is a multiple of 8); the box's zero fill outside the image IS the padding.  A box
+// starts on a 16 B boundary of the image row (whole rows above the image are fine, a start at column x0 - 1 is not).  Otherwise
 // the converters read global memory themselves (any width; slower: few bytes in flight per SM).
 template <bool TMA_IN, bool EPI>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -154,7 +157,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       bool hp_ok0 = false, hp_ok1 = false;
       if constexpr (TMA_IN) {
         // a box pinned to the image origin (image narrower / lower than the halo tile) is shifted against the tile
-        const int dx = P.box_x0 ? pw - x0 : 0, dy = P.box_y0 ? ph - y : 0;
+        const int dx = P.box_x0 ? pw - x0 : -P.box_shift, dy = P.box_y0 ? ph - y : 0;
         auto place = [&](int hi, int &src_off, uint32_t &dst, uint32_t &sw, bool &ok) {
           ok = hi < HP;
           const int r = hi / RW, xx = hi - r * RW;
@@ -380,7 +383,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
       for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int tile = item / P.nparts;
         const int txi = tile % P.tiles_x, by = tile / P.tiles_x, tyi = by % P.tiles_y, b = by / P.tiles_y;
-        const int xs = P.box_x0 ? 0 : txi * TW - pw, ys = P.box_y0 ? 0 : tyi * TH - ph;
+        const int xs = P.box_x0 ? 0 : txi * TW - pw - P.box_shift, ys = P.box_y0 ? 0 : tyi * TH - ph;
         for (int c = 0; c < P.Cin; c += 8) {
           mbar_wait(&s_empty[stage], phase ^ 1);
           mbar_expect_tx(&s_full[stage], bytes);
@@ -495,8 +498,11 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   P.Cn = Cout / P.nparts;
   P.stage_bytes = (P.Cn * 128 + 1023) / 1024 * 1024;
   P.BH = P.TH + KH - 1;
-  P.BW = (P.TW + KW - 1 + 3) & ~3;
-  if (P.BW > W) { P.BW = W; P.box_x0 = 1; }  // (W % 4 == 0 on the TMA path)
+  // a box must START on a 16 B boundary of the image row (a start at column x0 - 1 was measured to fault at run time;
+  // whole rows below the image are fine): it starts up to 3 columns left of the halo tile and is that much wider
+  P.box_shift = (((KW >> 1) + 3) & ~3) - (KW >> 1);
+  P.BW = (P.box_shift + P.TW + KW - 1 + 3) & ~3;
+  if (P.BW > W) { P.BW = W; P.box_x0 = 1; P.box_shift = 0; }  // (W % 4 == 0 on the TMA path)
   if (P.BH > H) { P.BH = H; P.box_y0 = 1; }
   {
     const int halo_pix = (P.TH + KH - 1) * (P.TW + KW - 1);
@@ -522,7 +528,7 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
   const int items = P.total_tiles * P.nparts;
   const int grid = items < sms ? items : sms;
   const int C2 = Cin - C1;
-  const bool tma_in = W % 4 == 0 && (reinterpret_cast<uintptr_t>(x1) & 15) == 0 && P.BH * P.BW <= kMaxHaloPix && P.x1_bs % 4 == 0 &&
+  const bool tma_in = W % 4 == 0 && (reinterpret_cast<uintptr_t>(x1) & 15) == 0 && P.BH * P.BW <= kMaxBoxPix && P.x1_bs % 4 == 0 &&
                       C1 >= 8 && (C2 == 0 || (C2 >= 8 && C1 % 8 == 0 && (reinterpret_cast<uintptr_t>(x2) & 15) == 0 && P.x2_bs % 4 == 0));
   if (tma_in) {
     CUtensorMap tx1, tx2;

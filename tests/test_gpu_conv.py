@@ -30,6 +30,10 @@ CASES = [
     (8, 128, 256, 128, 21, 64, 5, 1, "sigmoid"),  # many 8 x 16 tiles of the column filters
     (5, 48, 0, 126, 31, 40, 3, 3, None),          # several tiles per CTA with a padded filter count
     (5, 48, 0, 32, 31, 39, 3, 3, None),           # the same on the direct-load path (odd width)
+    (1, 64, 0, 32, 47, 156, 3, 3, "relu"),        # KITTI's 47 x 156 grid: two tiles per row, staged boxes that start left of x0
+    (1, 96, 146, 96, 47, 156, 3, 3, "tanh"),      # raft-small's GRU candidate convolution there (two inputs, 146 channels)
+    (2, 128, 256, 128, 9, 300, 1, 5, "sigmoid"),  # three tiles per row, 1x5
+    (1, 64, 0, 48, 11, 260, 3, 5, None),          # 3x5 filters, a last tile of 4 columns
 ]
 
 

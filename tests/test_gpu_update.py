@@ -148,6 +148,24 @@ def _images(H, W):
     return tex[:, :, 8:8 + H, 8:8 + W].contiguous().to(DEV), tex[:, :, 5:5 + H, 11:11 + W].contiguous().to(DEV)
 
 
+def test_fused_raft_on_a_kitti_frame(rr, ref_core):
+    """376 x 1248 (the ROS launch file's KITTI input, raft-small and raft-things): a 47 x 156 feature grid, i.e. more than
+    one convolution tile per row and ragged everything."""
+    core = ref_core
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    im1, im2 = _images(376, 1248)
+    for small in (True, False):
+        torch.manual_seed(1234)
+        model = core.raft.RAFT(argparse.Namespace(small=small, mixed_precision=False, alternate_corr=False)).to(DEV).eval()
+        with torch.no_grad():
+            flow_ref, up_ref = model(im1, im2, iters=8, test_mode=True)
+        flow, up = rr.FusedRAFT(model, graph=True)(im1, im2, iters=8)
+        epe = float((flow - flow_ref).norm(dim=1).mean())
+        print(f"FusedRAFT 376x1248 small={small}: EPE {epe:.2e} px")
+        assert epe <= 0.005 and float((up - up_ref).norm(dim=1).mean()) <= 0.04, (small, epe)
+
+
 @pytest.mark.parametrize("small,alternate", [(False, False), (True, False), (False, True)], ids=["things", "small", "things-alternate"])
 def test_fused_raft_matches_the_reference_forward(rr, ref_core, monkeypatch, small, alternate):
     core = ref_core

@@ -92,6 +92,7 @@ def main():
     ap.add_argument("--height", type=int, default=440)
     ap.add_argument("--width", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=1, help="frame pairs per forward (the pair is repeated with small noise)")
+    ap.add_argument("--small", action="store_true", help="raft-small (the ROS launch file's default model)")
     a = ap.parse_args()
     core = build_ref_core.load()
     if core is None:
@@ -100,13 +101,13 @@ def main():
     import core.raft  # noqa: F401
     warnings.filterwarnings("ignore")
     torch.manual_seed(1234)
-    model = core.raft.RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False)).to(DEV).eval()
+    model = core.raft.RAFT(argparse.Namespace(small=a.small, mixed_precision=False, alternate_corr=False)).to(DEV).eval()
     im1, im2 = images(a.height, a.width)
     if a.batch > 1:
         g = torch.Generator(device=DEV).manual_seed(3)
         im1 = (im1.repeat(a.batch, 1, 1, 1) + 2.0 * torch.rand(a.batch, *im1.shape[1:], device=DEV, generator=g)).clamp(0, 255)
         im2 = (im2.repeat(a.batch, 1, 1, 1) + 2.0 * torch.rand(a.batch, *im2.shape[1:], device=DEV, generator=g)).clamp(0, 255)
-    res = {"case": f"RAFT.forward raft-things {a.height}x{a.width}, batch {a.batch}, iters {a.iters}, test_mode", "tf32": "torch defaults"}
+    res = {"case": f"RAFT.forward {'raft-small' if a.small else 'raft-things'} {a.height}x{a.width}, batch {a.batch}, iters {a.iters}, test_mode", "tf32": "torch defaults"}
     with torch.no_grad():
         ms_ref, (flow_ref, up_ref) = timed(lambda: model(im1, im2, iters=a.iters, test_mode=True))
         res["reference_ms"] = ms_ref
@@ -118,19 +119,20 @@ def main():
             core.raft.CorrBlock = saved
         res["dropin_ms"] = ms_drop
         res["dropin_epe_px"] = float((flow_drop - flow_ref).norm(dim=1).mean())
-        ms_fused, (flow_fused, _) = timed(lambda: fused_forward(model, im1, im2, a.iters))
+        ms_fused, (flow_fused, _) = timed(lambda: fused_forward(model, im1, im2, a.iters)) if not a.small else (float("nan"), (flow_ref, None))
         res["fused_ms"] = ms_fused
         res["fused_epe_px"] = float((flow_fused - flow_ref).norm(dim=1).mean())
         # CUDA graph of the fused forward
         s1, s2 = im1.clone(), im2.clone()
-        graph = torch.cuda.CUDAGraph()
-        fused_forward(model, s1, s2, a.iters)
-        torch.cuda.synchronize()
-        with torch.cuda.graph(graph):
-            g_flow, g_up = fused_forward(model, s1, s2, a.iters)
-        ms_graph, _ = timed(graph.replay)
-        res["fused_graph_ms"] = ms_graph
-        res["fused_graph_epe_px"] = float((g_flow - flow_ref).norm(dim=1).mean())
+        if not a.small:  # (the round-2 mid-way variant: raft-things only)
+            graph = torch.cuda.CUDAGraph()
+            fused_forward(model, s1, s2, a.iters)
+            torch.cuda.synchronize()
+            with torch.cuda.graph(graph):
+                g_flow, g_up = fused_forward(model, s1, s2, a.iters)
+            ms_graph, _ = timed(graph.replay)
+            res["fused_graph_ms"] = ms_graph
+            res["fused_graph_epe_px"] = float((g_flow - flow_ref).norm(dim=1).mean())
         fr = rr.FusedRAFT(model)
         ms_c, (flow_c, up_c) = timed(lambda: fr(im1, im2, iters=a.iters))
         res["fusedraft_ms"] = ms_c
@@ -146,6 +148,32 @@ def main():
         res["reference_tf32_vs_fp32_epe_px"] = float((flow_ref - flow32).norm(dim=1).mean())
         res["fusedraft_vs_fp32_epe_px"] = float((flow_c - flow32).norm(dim=1).mean())
         res["mean_flow_px"] = float(flow_ref.norm(dim=1).mean())
+        if a.batch == 1:
+            # the ROS node's callback (ros/scripts/main.py:117-149) by wall clock: two uint8 HxWx3 host images in, the
+            # upsampled flow as a host HxWx2 array out
+            import time
+            import numpy as np
+            h1 = np.ascontiguousarray(im1[0].permute(1, 2, 0).byte().cpu().numpy())
+            h2 = np.ascontiguousarray(im2[0].permute(1, 2, 0).byte().cpu().numpy())
+
+            def callback(fwd):
+                i1 = torch.from_numpy(h1).permute(2, 0, 1).float()[None].to(DEV)
+                i2 = torch.from_numpy(h2).permute(2, 0, 1).float()[None].to(DEV)
+                _, up = fwd(i1, i2)
+                return up[0].permute(1, 2, 0).cpu().numpy()
+
+            def wall(fwd, reps=20):
+                for _ in range(3):
+                    callback(fwd)
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    callback(fwd)
+                return (time.perf_counter() - t0) / reps * 1e3
+
+            torch.backends.cudnn.allow_tf32 = True
+            torch.backends.cuda.matmul.allow_tf32 = True
+            res["ros_callback_reference_ms"] = wall(lambda i1, i2: model(i1, i2, iters=a.iters, test_mode=True))
+            res["ros_callback_fusedraft_graph_ms"] = wall(lambda i1, i2: frg(i1, i2, iters=a.iters))
     print(json.dumps(res), flush=True)
 
 
