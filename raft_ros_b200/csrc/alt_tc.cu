@@ -300,8 +300,11 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
         const float inv = 1.0f / (float)(1 << l);
         float dx, dy;
         const int x0 = safe_floor_int(cx * inv, &dx) - R, y0 = safe_floor_int(cy * inv, &dy) - R;
+        // windows wholly inside the level are wholly written by the chunks of the plan's box: only the others need zeros
+        if (!(x0 >= 0 && y0 >= 0 && x0 + PN <= P.w2[l] && y0 + PN <= P.h2[l])) {
 #pragma unroll 4
-        for (int i = 0; i < NPATCH; ++i) sts32(patch + i * 4, 0.0f);
+          for (int i = 0; i < NPATCH; ++i) sts32(patch + i * 4, 0.0f);
+        }
         const int4 pl = __ldg(P.plan + t * P.L + l);
         const int shape = pl.z >> 16, ncx = pl.z & 0xffff;
         const int cw = shape ? CW1 : CW0, chh = shape ? CH1 : CH0;
@@ -376,12 +379,14 @@ alt_tc_kernel(const __grid_constant__ Maps M, const Params P) {
           const float w00 = (1.0f - dy) * (1.0f - dx) * sc, w01 = (1.0f - dy) * dx * sc;
           const float w10 = dy * (1.0f - dx) * sc, w11 = dy * dx * sc;
           float *o = P.out + ((size_t)b * CH + (size_t)l * NTAP) * HW + (size_t)y * P.W1 + x;
+          float col0[PN], col1[PN];
 #pragma unroll
-          for (int i = 0; i < RD; ++i) {      // x offset (slow index)
-            float col0[PN], col1[PN];
+          for (int j = 0; j < PN; ++j) col1[j] = lds32(patch + (j * PN) * 4);
+#pragma unroll
+          for (int i = 0; i < RD; ++i) {      // x offset (slow index); a patch column is read once and used for two offsets
 #pragma unroll
             for (int j = 0; j < PN; ++j) {
-              col0[j] = lds32(patch + (j * PN + i) * 4);
+              col0[j] = col1[j];
               col1[j] = lds32(patch + (j * PN + i + 1) * 4);
             }
 #pragma unroll
