@@ -166,6 +166,27 @@ def test_fused_raft_on_a_kitti_frame(rr, ref_core):
         assert epe <= 0.005 and float((up - up_ref).norm(dim=1).mean()) <= 0.04, (small, epe)
 
 
+def test_fused_raft_with_a_mixed_precision_model(rr, ref_core):
+    """`--mixed_precision` (core/raft.py:98-115,127: encoders and update block under fp16 autocast): FusedRAFT keeps the
+    encoders under autocast and runs the update block on its fp16-operand kernels.  Both sides are fp16-class here, so the
+    bound is the reference's own distance between its fp16 and fp32 runs (measured and printed), with 0.05 px as a cap."""
+    core = ref_core
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(1234)
+    im1, im2 = _images(184, 320)
+    model = core.raft.RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False)).to(DEV).eval()
+    with torch.no_grad():
+        f32, _ = model(im1, im2, iters=12, test_mode=True)
+        model.args.mixed_precision = True
+        f16, _ = model(im1, im2, iters=12, test_mode=True)
+    ours, up = rr.FusedRAFT(model)(im1, im2, iters=12)
+    d_ref = float((f16 - f32).norm(dim=1).mean())
+    d_ours = float((ours - f32).norm(dim=1).mean())
+    print(f"mixed precision: reference fp16 vs fp32 {d_ref:.2e} px, FusedRAFT vs fp32 {d_ours:.2e} px")
+    assert torch.isfinite(up).all() and d_ours <= max(2.0 * d_ref, 0.005) and d_ours <= 0.05, (d_ref, d_ours)
+
+
 @pytest.mark.parametrize("small,alternate", [(False, False), (True, False), (False, True)], ids=["things", "small", "things-alternate"])
 def test_fused_raft_matches_the_reference_forward(rr, ref_core, monkeypatch, small, alternate):
     core = ref_core
