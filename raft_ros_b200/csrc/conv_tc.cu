@@ -21,6 +21,8 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -509,9 +511,9 @@ int launch_conv_tc(const float *x1, int C1, const float *x2, const void *wp, con
     P.halo_bytes = (halo_pix * 128 + 1023) / 1024 * 1024;
     P.in_stage_bytes = (8 * P.BH * P.BW * 4 + 127) / 128 * 128;
     P.in_off = 2 * P.halo_bytes;
-    // the weights get two stages or 48 KB, the input staging what is left (4 .. kInStages boxes in flight: a frame pair
-    // alone is bound by the latency of these rings), the weights then the remainder
-    const int w_min = 2 * P.stage_bytes > 48 * 1024 ? 2 * P.stage_bytes : 48 * 1024;
+    // the weights get two stages or 96 KB (measured: 48 -> 96 KB is 57 -> 51 us on convc2 at batch 8 and nothing elsewhere),
+    // the input staging what is left (4 .. kInStages boxes in flight), the weights then the remainder
+    const int w_min = 2 * P.stage_bytes > 96 * 1024 ? 2 * P.stage_bytes : 96 * 1024;
     int ins = (kDataBytes - P.in_off - w_min - 1024) / P.in_stage_bytes;
     P.in_stages = ins < 4 ? 4 : (ins > kInStages ? kInStages : ins);
     P.w_off = (P.in_off + P.in_stages * P.in_stage_bytes + 1023) / 1024 * 1024;
