@@ -209,6 +209,12 @@ class FusedRAFT:
         with torch.no_grad():
             if not self.graph:
                 return self._forward(image1, image2, iters, flow_init)
+            # a graph holds the converted weights it was captured with: weights changed in place since (load_state_dict,
+            # an optimiser step) invalidate every captured graph
+            stamp = sum(p._version for p in self.model.parameters())
+            if stamp != getattr(self, "_stamp", None):
+                self._graphs.clear()
+                self._stamp = stamp
             key = (tuple(image1.shape), image1.device.index, int(iters), flow_init is not None)
             ent = self._graphs.get(key)
             if ent is None:

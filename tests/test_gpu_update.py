@@ -219,3 +219,10 @@ def test_fused_raft_matches_the_reference_forward(rr, ref_core, monkeypatch, sma
     assert float((gflow - flow).abs().max()) <= 1e-4 and float((gup - up).abs().max()) <= 1e-3
     with pytest.raises(RuntimeError, match="test-mode"):
         fused(im1, im2, iters=2, test_mode=False)
+    if not small and not alternate:
+        # weights changed in place after the capture (load_state_dict): the graph is rebuilt, not replayed stale
+        with torch.no_grad():
+            model.update_block.flow_head.conv2.weight.mul_(0.5)
+            ref2, _ = model(im1, im2, iters=12, test_mode=True)
+        g2, _ = graphed(im1, im2, iters=12)
+        assert float((g2 - ref2).norm(dim=1).mean()) <= 0.005 and float((g2 - gflow).abs().max()) > 1e-3
