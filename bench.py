@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--iters", type=int, default=12, help="lookups per build")
     ap.add_argument("--levels", type=int, default=4)
     ap.add_argument("--radius", type=int, default=4)
-    ap.add_argument("--precision", default=os.environ.get("RAFT_CORR_PRECISION", "bf16x3"),
+    ap.add_argument("--precision", default=os.environ.get("RAFT_CORR_PRECISION", "fp16_fp8"),
                     choices=["fp32", "bf16x3", "bf16", "bf16_vol16", "fp16_fp8"])
     ap.add_argument("--l2-fetch", type=int, default=int(os.environ.get("RAFT_CORR_L2_FETCH", "0")),
                     help="set cudaLimitMaxL2FetchGranularity (32/64/128); 0 = leave the driver default")
@@ -52,7 +52,7 @@ def parse():
                          "'rows' the reference's (B*h*w,1,h_l,w_l) arrays")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fast-paths", action="store_true",
-                    help="skip the extra bf16 / bf16_vol16 measurements appended to the default bf16x3 line")
+                    help="skip the other precisions' measurements appended to the default line")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true",
                     help="skip the comparator leg: the reference's own torch ops / alt_cuda_corr binary on this GPU")
@@ -76,12 +76,14 @@ def measured_traffic(kernel, args, layout="rows"):
     it was captured at).  Only valid for the configuration it was captured on, else None.
     Returns (dram_read + dram_write, detail dict)."""
     p = os.path.join(ROOT, "profiles", "r02_traffic.json")
-    default = (args.batch, args.height, args.width, args.dim, args.levels, args.radius, args.precision)
-    if default != (8, 440, 1024, 256, 4, 4, "bf16x3") or layout != "tiled" or not os.path.exists(p):
+    default = (args.batch, args.height, args.width, args.dim, args.levels, args.radius)
+    if default != (8, 440, 1024, 256, 4, 4) or args.precision not in ("bf16x3", "fp16_fp8") or layout != "tiled" or not os.path.exists(p):
         return None, None
     try:
         d = json.load(open(p))
         k = d["kernels"][kernel]
+        if kernel == "build" and args.precision == "fp16_fp8":  # (the lookup is the same kernel for every build precision)
+            k = d["kernels"]["build_fp16_fp8"]
         detail = {"dram_read": k["dram_read"], "dram_write": k["dram_write"], "sm_write": k["sm_write"],
                   "sm_read": k.get("sm_read"), "kernel_us_under_ncu": k.get("us"), "commit": d.get("commit"),
                   "note": "dram_write counts only what reached DRAM before the kernel ended; sm_write is what the SMs "
@@ -642,8 +644,9 @@ def run_ours(args):
     b_build, b_look, b_total = algorithmic_bytes(B, N, D, h, w, L, r, K, 2 if args.precision == "bf16_vol16" else 4)
     kern = {
         "build": {"launches_per_step": 2, "ms": build_ms, "alg_bytes": b_build, "gbs": b_build / (build_ms * 1e-3) / 1e9,
-                  "share_of_step": build_ms / ms_step, "flops": 2.0 * B * N * N * D * {"bf16x3": 3, "fp16_fp8": 3}.get(args.precision, 1),
-                  "tflops": 2.0 * B * N * N * D * {"bf16x3": 3, "fp16_fp8": 3}.get(args.precision, 1) / (build_ms * 1e-3) / 1e12},
+                  "share_of_step": build_ms / ms_step, "flops": 2.0 * B * N * N * D * {"bf16x3": 3, "fp16_fp8": 2}.get(args.precision, 1),
+                  "tflops": 2.0 * B * N * N * D * {"bf16x3": 3, "fp16_fp8": 2}.get(args.precision, 1) / (build_ms * 1e-3) / 1e12,
+                  "flops_note": "bf16-equivalent tensor work: bf16x3 = 3 passes; fp16_fp8 = 1 fp16 pass + 1 e4m3 pass of twice the K at twice the rate"},
         "lookup": {"launches_per_step": K, "ms": look_ms, "alg_bytes": b_look, "gbs": b_look / (look_ms * 1e-3) / 1e9,
                    "share_of_step": look_ms * K / ms_step},
     }
@@ -667,10 +670,11 @@ def run_ours(args):
     }
     if e2e is not None:
         line["e2e"] = e2e
-    if world == 1 and tiled and not args.no_fast_paths and args.precision == "bf16x3":
-        # the same step with the stated-bounds fast paths, for the record (not the headline value)
+    if world == 1 and tiled and not args.no_fast_paths and args.precision in ("bf16x3", "fp16_fp8"):
+        # the same step with the other precisions, for the record (not the headline value): the other fp32-class one and the
+        # stated-bounds fast paths
         extra = {}
-        for prec in ("fp16_fp8", "bf16", "bf16_vol16"):
+        for prec in (("bf16x3" if args.precision == "fp16_fp8" else "fp16_fp8"), "bf16", "bf16_vol16"):
             def fstep():
                 lv = build_pyramid_tiled_raw(f1, f2, L, prec)
                 for k in range(K):

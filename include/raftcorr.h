@@ -51,10 +51,11 @@ extern "C" {
                              /* reads; tiled layout only (rc_corr_build_pyramid_tiled +       */
                              /* rc_corr_lookup_tiled16_fwd); +2.4e-4 relative storage error   */
 
-#define RC_PREC_FP16_FP8 4 /* tcgen05, fp16 products plus 8-bit compensation: x*2^k = hi + lo with hi fp16 (k per  */
-                          /* feature map and batch item from its largest magnitude), the products hi*hi run in  */
-                          /* fp16 and the two cross terms hi*lo + lo*hi as ONE e4m3 contraction at twice the    */
-                          /* rate: 2/3 of BF16X3's tensor work; normwise error ~2e-5 (<= 1e-4 relative)         */
+#define RC_PREC_FP16_FP8 4 /* tcgen05, fp16 products plus 8-bit compensation: every pixel's D-vector times 2^k = hi + lo */
+                          /* with hi fp16 (k from that pixel's largest magnitude, found by the layout prepass itself);   */
+                          /* the products hi*hi run in fp16 and the two cross terms hi*lo + lo*hi as ONE e4m3            */
+                          /* contraction at twice the rate: 2/3 of BF16X3's tensor work; normwise error ~1e-5            */
+                          /* (<= 1e-4 relative whatever the magnitudes); forward only                                    */
 
 int rc_version(void);
 const char *rc_last_error(void);

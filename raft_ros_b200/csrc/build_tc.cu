@@ -60,7 +60,7 @@ struct Params {
   int m_tiles, nt_x, nt_y;      // tiles along query pixels / patch grid
   long long total_tiles;
   float scale;
-  const unsigned *amax;         // NPASS == 2: bits of max |x| per (feature map, batch item), [2][B]
+  const float *inv_sa, *inv_sb; // NPASS == 2: 1 / (power-of-two normalisation) of every pixel of fmap1 / fmap2, [B][N] each
   int vec_mask;                 // bit l: rows of level l are 16 B aligned -> vector stores
   int tpr[4], ng;               // TILED output only: tiles per tile-row of level l; groups of query pixels per item
   long long gstride[4];         //   floats per group of level l (= kTileGroup * hp * wp)
@@ -76,7 +76,7 @@ constexpr uint32_t kIdesc2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN
 constexpr uint32_t kIdescF = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 constexpr uint32_t kIdescF2 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)((2 * TM) >> 4) << 24);
 
-// RC_PREC_FP16_FP8 (NPASS == 2).  A feature map is scaled by a power of two s so that its largest magnitude lands
+// RC_PREC_FP16_FP8 (NPASS == 2).  Every PIXEL of a feature map (its D-vector) is scaled by a power of two s so that its largest magnitude lands
 // in [128, 256) and split x*s = hi + lo, hi = fp16(x*s) (lo is then exact in fp32, |lo| <= 2^-4).  Of
 //   (a*sa)(b*sb) = ah*bh + (ah*bl + al*bh) + al*bl
 // the first term runs in fp16; the bracket is ONE contraction over 2x the channels of 8-bit operands
@@ -84,7 +84,9 @@ constexpr uint32_t kIdescF2 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32
 // -- the 16s cancel in the products and put both factors in e4m3's normal range (16|lo| <= 1, |hi|/16 < 16; e4m3
 // keeps 2^-6 .. 448) -- at the 8-bit rate, i.e. for the tensor time of one more fp16 term: 2 units instead of
 // BF16X3's 3.  Rounding the cross terms' factors to 4 significant bits is a ~4 % error on terms that are 2^-12 of
-// the result; al*bl (2^-22) is dropped as in BF16X3.  The epilogue multiplies by scale / (sa*sb).
+// the result; al*bl (2^-22) is dropped as in BF16X3.  The epilogue multiplies element (p, q) by scale / (sa[p] * sb[q]):
+// per-pixel factors cost it one shuffle and one multiply per element, and cost the prepass nothing (a pixel's 256
+// channels are in one block) -- a per-map factor needed a separate pass over the feature maps (20 us at batch 8).
 __device__ __forceinline__ float norm_mul(unsigned amax_bits) {
   // 2^(7 - e) for max|x| in [2^e, 2^(e+1)); 1 for an all-zero map; clamped to the finite powers of two
   if (amax_bits == 0u) return 1.0f;
@@ -303,8 +305,6 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     for (long long t = unit0; t < P.total_tiles; t += unit_step) {
       const int b = (int)(t / tiles_per_item);
       float out_scale = P.scale;
-      if constexpr (NPASS == 2)  // undo the two maps' power-of-two normalisation (exact)
-        out_scale = P.scale * (1.0f / norm_mul(__ldg(P.amax + b))) * (1.0f / norm_mul(__ldg(P.amax + P.B + b)));
       const int rem = (int)(t - (long long)b * tiles_per_item);
       const int mu = rem / nt, n = rem - mu * nt;
       const int m = mu * NCTA + (int)rank;
@@ -348,6 +348,19 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_col), "f"(lo_col));
         return __uint_as_float(r);
       };
+      // NPASS == 2: undo the power-of-two normalisation of this thread's query pixel (row) and of the target pixels
+      // (columns; lane i holds column x0 + i of this warp's four patch rows, handed round by shuffles below).  Exact.
+      // Fetched before the accumulator is complete, so the round trip overlaps the MMAs.
+      float sb[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+      if constexpr (NPASS == 2) {
+        const float ra = lane < rows_valid ? __ldg(P.inv_sa + (size_t)b * N + prow0 + lane) : 0.0f;
+        out_scale = P.scale * ra;
+#pragma unroll
+        for (int r4 = 0; r4 < 4; ++r4) {
+          const int yy = ny * PH + hf * 4 + r4;
+          sb[r4] = (yy < h && x0 + lane < w) ? __ldg(P.inv_sb + (size_t)b * N + (size_t)yy * w + x0 + lane) : 0.0f;
+        }
+      }
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TN + hf * (TN / 2));
@@ -372,10 +385,18 @@ build_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             else mbar_arrive_leader(&tempty[acc]);  // the pair's MMA thread lives in the leader CTA
           }
         }
+        if constexpr (NPASS == 2) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          v0[i] *= out_scale;
-          v1[i] *= out_scale;
+          for (int i = 0; i < 32; ++i) {
+            v0[i] *= out_scale * __shfl_sync(0xffffffffu, sb[2 * j], i);
+            v1[i] *= out_scale * __shfl_sync(0xffffffffu, sb[2 * j + 1], i);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            v0[i] *= out_scale;
+            v1[i] *= out_scale;
+          }
         }
         const int y0 = ny * PH + hf * 4 + 2 * j;
         if constexpr (V16) {
@@ -618,79 +639,70 @@ prep_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __nv_bfl
 }
 
 // ------------------------------------------------------------------ prep for RC_PREC_FP16_FP8
-// largest magnitude of each (feature map, batch item), in two steps without atomics or a memset: kAmaxParts partial
-// maxima per item here, reduced by every warp of the prepass (non-negative floats order like their bit patterns)
-constexpr int kAmaxParts = 64;
-__global__ void __launch_bounds__(256)
-absmax_kernel(const float *__restrict__ f1, const float *__restrict__ f2, unsigned *__restrict__ part, long long per_item) {
-  const int which = blockIdx.y & 1, b = blockIdx.y >> 1;
-  const float *src = (which ? f2 : f1) + (size_t)b * per_item;
-  __shared__ float wmax[8];
-  pdl_launch_dependents();
-  pdl_wait();
-  float m = 0.0f;
-  const long long stride = (long long)gridDim.x * blockDim.x, i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && per_item % 4 == 0) {
-    const float4 *s4 = reinterpret_cast<const float4 *>(src);
-    for (long long i = i0; i < per_item / 4; i += stride) {
-      const float4 v = __ldg(s4 + i);
-      m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
-    }
-  } else {
-    for (long long i = i0; i < per_item; i += stride) m = fmaxf(m, fabsf(__ldg(src + i)));
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = m;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int i = 1; i < 8; ++i) m = fmaxf(m, wmax[i]);
-    part[(size_t)blockIdx.y * kAmaxParts + blockIdx.x] = __float_as_uint(m);  // blockIdx.y = 2 b + which
-  }
-}
-
-// NCHW fp32 -> K-major fp16 "hi" map and the 8-bit pair map (see norm_mul above), same tiling as prep_kernel
+// NCHW fp32 -> K-major fp16 "hi" map and the 8-bit pair map (see norm_mul above), each pixel normalised by its own power
+// of two; 1 / that power goes to inv_s[b][p] for the build's epilogue.  One block = 32 pixels x all channels: first the
+// pixels' largest magnitudes (coalesced along the pixels), then the 64-channel blocks as in prep_kernel (the block's
+// 32 KB of input are re-read from L1 / L2).
 __global__ void __launch_bounds__(256)
 prep_f16f8_kernel(const float *__restrict__ f1, const float *__restrict__ f2, __half *__restrict__ a_hi, uint8_t *__restrict__ a_8,
-                  __half *__restrict__ b_hi, uint8_t *__restrict__ b_8, const unsigned *__restrict__ part,
-                  unsigned *__restrict__ amax, int B, int D, int Dp, int N) {
+                  __half *__restrict__ b_hi, uint8_t *__restrict__ b_8, float *__restrict__ inv_sa, float *__restrict__ inv_sb,
+                  int D, int Dp, int N) {
   __shared__ float tile[64][33];
-  const int which = blockIdx.z & 1, b = blockIdx.z >> 1;
+  __shared__ float pmax[8][33];
+  __shared__ float pscale[32];
+  const int which = blockIdx.y & 1, b = blockIdx.y >> 1;
   const float *src = (which ? f2 : f1) + (size_t)b * D * N;
   __half *hi = (which ? b_hi : a_hi) + (size_t)b * N * Dp;
   uint8_t *p8 = (which ? b_8 : a_8) + (size_t)b * N * Dp * 2;
-  const int p0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
+  float *inv_s = (which ? inv_sb : inv_sa) + (size_t)b * N;
+  const int p0 = blockIdx.x * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
   pdl_launch_dependents();
   pdl_wait();
-  unsigned mx = max(__ldg(part + (size_t)blockIdx.z * kAmaxParts + tx), __ldg(part + (size_t)blockIdx.z * kAmaxParts + 32 + tx));
+  {
+    float m = 0.0f;
+    const int p = p0 + tx;
+    if (p < N) {
+#pragma unroll 8
+      for (int d = ty; d < D; d += 8) m = fmaxf(m, fabsf(__ldg(src + (size_t)d * N + p)));
+    }
+    pmax[ty][tx] = m;
+    __syncthreads();
+    if (ty == 0) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) amax[which * B + b] = mx;  // for the build's epilogue
-  const float s = norm_mul(mx);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int d = d0 + ty + 8 * i, p = p0 + tx;
-    tile[ty + 8 * i][tx] = (d < D && p < N) ? __ldg(src + (size_t)d * N + p) * s : 0.0f;
+      for (int i = 1; i < 8; ++i) m = fmaxf(m, pmax[i][tx]);
+      const float s = norm_mul(__float_as_uint(m));
+      pscale[tx] = s;
+      if (p < N) inv_s[p] = 1.0f / s;  // exact: a power of two
+    }
+    __syncthreads();
   }
-  __syncthreads();
   // the lo halves of the 128 B row pair with the other map's hi halves: A = [lo | hi], B = [hi | lo]
   const int off_lo = which ? 64 : 0, off_hi = which ? 0 : 64;
+  for (int kb = 0; kb < Dp / 64; ++kb) {
+    const int d0 = kb * 64;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int pl = ty + 8 * i, p = p0 + pl, d = d0 + 2 * tx;
-    if (p < N) {
-      const float x0 = tile[2 * tx][pl], x1 = tile[2 * tx + 1][pl];
-      const __half2 h2 = __floats2half2_rn(x0, x1);
-      *reinterpret_cast<__half2 *>(hi + (size_t)p * Dp + d) = h2;
-      const float h0 = __low2float(h2), h1 = __high2float(h2);
-      uint8_t *row = p8 + (size_t)p * Dp * 2 + (size_t)blockIdx.y * 128 + 2 * tx;
-      *reinterpret_cast<uint16_t *>(row + off_lo) =
-          __nv_cvt_float2_to_fp8x2(make_float2((x0 - h0) * 16.0f, (x1 - h1) * 16.0f), __NV_SATFINITE, __NV_E4M3);
-      *reinterpret_cast<uint16_t *>(row + off_hi) =
-          __nv_cvt_float2_to_fp8x2(make_float2(h0 * 0.0625f, h1 * 0.0625f), __NV_SATFINITE, __NV_E4M3);
+    for (int i = 0; i < 8; ++i) {
+      const int d = d0 + ty + 8 * i, p = p0 + tx;
+      tile[ty + 8 * i][tx] = (d < D && p < N) ? __ldg(src + (size_t)d * N + p) * pscale[tx] : 0.0f;
     }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pl = ty + 8 * i, p = p0 + pl, d = d0 + 2 * tx;
+      if (p < N) {
+        const float x0 = tile[2 * tx][pl], x1 = tile[2 * tx + 1][pl];
+        const __half2 h2 = __floats2half2_rn(x0, x1);
+        *reinterpret_cast<__half2 *>(hi + (size_t)p * Dp + d) = h2;
+        const float h0 = __low2float(h2), h1 = __high2float(h2);
+        uint8_t *row = p8 + (size_t)p * Dp * 2 + (size_t)kb * 128 + 2 * tx;
+        *reinterpret_cast<uint16_t *>(row + off_lo) =
+            __nv_cvt_float2_to_fp8x2(make_float2((x0 - h0) * 16.0f, (x1 - h1) * 16.0f), __NV_SATFINITE, __NV_E4M3);
+        *reinterpret_cast<uint16_t *>(row + off_hi) =
+            __nv_cvt_float2_to_fp8x2(make_float2(h0 * 0.0625f, h1 * 0.0625f), __NV_SATFINITE, __NV_E4M3);
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -753,14 +765,14 @@ size_t build_tc_workspace_bytes(int B, int D, int h, int w, int precision) {
   if (B <= 0 || D <= 0 || h <= 0 || w <= 0) return 0;
   const size_t per_map = (size_t)B * h * w * round_up64(D) * 2;  // bf16
   const size_t aligned = (per_map + 255) / 256 * 256;
-  if (precision == RC_PREC_FP16_FP8)  // + the magnitudes: [2B] final, [2B][kAmaxParts] partial
-    return aligned * 4 + ((size_t)2 * B * (1 + tc::kAmaxParts) * 4 + 255) / 256 * 256;
+  if (precision == RC_PREC_FP16_FP8)  // + 1 / (normalisation) of every pixel of both maps
+    return aligned * 4 + ((size_t)2 * B * h * w * 4 + 255) / 256 * 256;
   return aligned * 2 * (precision == RC_PREC_BF16X3 ? 2 : 1);
 }
 
 static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
                                int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
-                               bool tiled, const unsigned *amax = nullptr);
+                               bool tiled, const float *inv_s = nullptr);
 
 static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, int h, int w, const LevelPtrs &lv,
                                 int L, int precision, float scale, void *ws, size_t ws_bytes, cudaStream_t st,
@@ -793,12 +805,11 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
 
   const dim3 grid((unsigned)((N + 31) / 32), (unsigned)(Dp / 64), (unsigned)(2 * B));
   if (f8) {
-    unsigned *amax = reinterpret_cast<unsigned *>(base + 4 * per_map), *part = amax + 2 * B;
-    RC_CUDA(launch_pdl(absmax_kernel, dim3(kAmaxParts, (unsigned)(2 * B)), dim3(256), 0, st, f1, f2, part, (long long)D * N));
-    RC_CUDA(launch_pdl(prep_f16f8_kernel, grid, dim3(256), 0, st, f1, f2, reinterpret_cast<__half *>(a_hi),
-                       reinterpret_cast<uint8_t *>(a_lo), reinterpret_cast<__half *>(b_hi), reinterpret_cast<uint8_t *>(b_lo),
-                       (const unsigned *)part, amax, B, D, Dp, N));
-    return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled, amax);
+    float *inv_s = reinterpret_cast<float *>(base + 4 * per_map);  // [2][B][N]
+    RC_CUDA(launch_pdl(prep_f16f8_kernel, dim3((unsigned)((N + 31) / 32), (unsigned)(2 * B)), dim3(256), 0, st, f1, f2,
+                       reinterpret_cast<__half *>(a_hi), reinterpret_cast<uint8_t *>(a_lo), reinterpret_cast<__half *>(b_hi),
+                       reinterpret_cast<uint8_t *>(b_lo), inv_s, inv_s + (size_t)B * N, D, Dp, N));
+    return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled, inv_s);
   }
   RC_CUDA(launch_pdl(prep_kernel, grid, dim3(256), 0, st, f1, f2, a_hi, a_lo, b_hi, b_lo, D, Dp, N, x3 ? 1 : 0));
   return build_from_operands(a_hi, a_lo, b_hi, b_lo, B, Dp, h, w, lv, L, precision, scale, st, tiled);
@@ -808,7 +819,7 @@ static int launch_build_tc_impl(const float *f1, const float *f2, int B, int D, 
 // layout prepass above writes, and what rc_fnet_conv1x1_prep (fnet_head.cu) emits straight from the encoder.
 static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bfloat16 *b_hi, __nv_bfloat16 *b_lo, int B,
                                int Dp, int h, int w, const LevelPtrs &lv, int L, int precision, float scale, cudaStream_t st,
-                               bool tiled, const unsigned *amax) {
+                               bool tiled, const float *inv_s) {
   using namespace tc;
   const int N = h * w;
   const bool f8 = precision == RC_PREC_FP16_FP8;
@@ -840,7 +851,8 @@ static int build_from_operands(__nv_bfloat16 *a_hi, __nv_bfloat16 *a_lo, __nv_bf
   P.nt_y = (h + PH - 1) / PH;
   P.total_tiles = (long long)B * P.m_tiles * P.nt_x * P.nt_y;
   P.scale = scale;
-  P.amax = amax;
+  P.inv_sa = inv_s;
+  P.inv_sb = inv_s ? inv_s + (size_t)B * N : nullptr;
   P.lv = lv;
   P.vec_mask = 0;
   for (int l = 0; l < 4 && l < L; ++l) {
